@@ -1,0 +1,115 @@
+/* niftyb200 -- C ABI of the B200-native correlated-field / metric-CG hot path.
+ *
+ * This is the drop-in boundary.  The reference (NIFTy 8.5,
+ * pure Python) reaches its native arithmetic through exactly four callables,
+ *   ducc_dispatch.fftn / ifftn / hartley / vdot       (src/ducc_dispatch.py:66-86)
+ * bound to ducc0's pybind11 API (src/ducc_dispatch.py:61-64):
+ *   ducc0.fft.c2c(a, axes=, forward=, inorm=, nthreads=)
+ *   ducc0.fft.genuine_hartley(a, axes=, nthreads=) / genuine_fht(...)
+ *   ducc0.misc.vdot(a, b)
+ * Each entry point below names the reference call it replaces.  Everything is
+ * extern "C", plain pointers and sizes; all array pointers are DEVICE pointers unless
+ * the name ends in `_host`.  Functions return 0 on success, a negative code otherwise;
+ * nb2_last_error() gives the message of the last failure on the calling thread.
+ * `stream` is a cudaStream_t passed as void* (NULL = default stream); calls are
+ * asynchronous with respect to the host unless stated otherwise.
+ */
+#ifndef NIFTYB200_H
+#define NIFTYB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NB2_F32 0
+#define NB2_F64 1
+
+/* Hartley conventions of nifty8.config "hartley_convention" (src/config.py:3-5,
+ * src/ducc_dispatch.py:46-50,75-78): 0 = "non_canonical_hartley" (Re F + Im F, default),
+ * 1 = "canonical_hartley" (Re F - Im F). */
+#define NB2_HARTLEY_NONCANONICAL 0
+#define NB2_HARTLEY_CANONICAL 1
+
+#define NB2_OK 0
+#define NB2_ERR_ARG (-1)
+#define NB2_ERR_CUDA (-2)
+#define NB2_ERR_UNSUPPORTED (-3)
+
+typedef struct nb2_plan nb2_plan;
+
+/* Point-wise operator fused into the first load (prologue) or last store (epilogue) of a
+ * transform.  value' = value * amp(k) * scale [* mul[i]] + add_scalar [+ add[i]];
+ * if `dot` is set, sum_i dot[i]*value'[i] is reduced in fp64 into *dot_out.
+ * mul/add/add_scalar/dot are honoured in the epilogue only.
+ *   amp_mode 0: no amplitude
+ *   amp_mode 1: amp = table indexed by ksq = sum_j min(k_j, N_j-k_j)^2 over the transformed
+ *               axes (isotropic grids; replaces PowerDistributor's gather through the int64
+ *               pindex, src/operators/distributors.py:114-119, src/domains/power_space.py:170-198);
+ *               fast path only
+ *   amp_mode 2: amp = full-size factor field of one batch item (any grid) */
+typedef struct nb2_pointop {
+    int32_t amp_mode;
+    int32_t reserved;
+    const void* amp;
+    double scale;
+    const void* mul;
+    const void* add;
+    double add_scalar;
+    const void* dot;
+    double* dot_out;
+} nb2_pointop;
+
+int nb2_version(void);
+const char* nb2_last_error(void);
+/* number of SMs of the current device (148 on B200) */
+int nb2_sm_count(void);
+
+/* Plan for transforms over `axes` of a C-contiguous array of `shape`.
+ * Replaces the per-call planning inside ducc0.fft.* (src/ducc_dispatch.py:62-78). */
+int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* axes, int dtype, nb2_plan** plan);
+int nb2_plan_destroy(nb2_plan* plan);
+/* 1 if the plan runs on the power-of-two fast path (3 fused passes), 0 for the generic path */
+int nb2_plan_is_fast(const nb2_plan* plan);
+/* number of entries an amp_mode-1 table must have: 1 + sum_j (N_j/2)^2 ; 0 if not fast */
+int64_t nb2_plan_ksq_size(const nb2_plan* plan);
+
+/* Genuine (non-separable) Hartley transform, unnormalised, with optional fused point-wise
+ * operators.  Replaces ducc_dispatch.hartley (src/ducc_dispatch.py:75-78,46-50) and, with
+ * pro/epi, the correlated-field hot tail ht(azm*corr*xi)+offset
+ * (src/library/correlated_fields.py:801-818, src/re/correlated_field.py:690-693) and its
+ * adjoint.  `in` is not modified unless in == out (in-place is allowed). */
+int nb2_hartley(nb2_plan* plan, const void* in, void* out, int convention, const nb2_pointop* pro,
+                const nb2_pointop* epi, void* stream);
+
+/* Complex-to-complex FFT, out = scale * FFT(in); forward != 0 -> exp(-i..), else exp(+i..).
+ * Replaces ducc_dispatch.fftn / ifftn (src/ducc_dispatch.py:66-72; ifftn = backward, scale 1/N).
+ * `in`/`out`: interleaved complex of the plan's precision. */
+int nb2_c2c(nb2_plan* plan, const void* in, void* out, int forward, double scale, void* stream);
+
+/* sum_i a[i]*b[i] over n real scalars (complex data: pass 2n and conjugate on the caller's
+ * side), fp64 accumulation, deterministic.  Replaces ducc_dispatch.vdot
+ * (src/ducc_dispatch.py:81-86).  *out_dev is a device double. */
+int nb2_vdot(int dtype, int64_t n, const void* a, const void* b, double* out_dev, void* stream);
+
+/* y = a*x + b*y.  The vector updates of ConjugateGradient (src/minimization/
+ * conjugate_gradient.py:101,124) and re `_cg` (src/re/conjugate_gradient.py:169,205). */
+int nb2_axpby(int dtype, int64_t n, double a, const void* x, double b, void* y, void* stream);
+
+/* Fused CG step.  mode 0: x -= alpha d; r -= alpha q.  mode 1: r = q - b (exact residual of a
+ * reset step, q = A x).  Then sums_dev[0..2] = (r.r, x.r, x.b) in fp64.
+ * (src/minimization/conjugate_gradient.py:100-109, src/minimization/quadratic_energy.py:35-37,
+ *  src/re/conjugate_gradient.py:169-191) */
+int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, const void* q, const void* b,
+                  void* x, void* r, double* sums_dev, void* stream);
+
+/* Host-buffer convenience wrappers (numpy drop-in path): copy in, transform, copy out,
+ * synchronous. */
+int nb2_hartley_host(nb2_plan* plan, const void* in_host, void* out_host, int convention, double scale);
+int nb2_c2c_host(nb2_plan* plan, const void* in_host, void* out_host, int forward, double scale);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NIFTYB200_H */

@@ -1,0 +1,629 @@
+// niftyb200 -- C ABI implementation (see include/niftyb200.h).
+//
+// Built with nvcc for sm_100a into libniftyb200.so.  With -DNB2_EMU (host compiler) the
+// same file builds the sequential thread emulator used by the CPU-only index tests.
+#include <algorithm>
+#include <cmath>
+#include <new>
+
+#include "../../include/niftyb200.h"
+#include "nb2_generic.cuh"
+#include "nb2_launch.cuh"
+#include "nb2_passes.cuh"
+#include "nb2_vector.cuh"
+
+using namespace nb2;
+
+namespace {
+
+constexpr int kMaxDim = 8;
+constexpr size_t kSmemLimit = 200 * 1024;
+constexpr int kVecThreads = 256;
+
+struct Ctx {
+    double* partials = nullptr;  // reduction scratch for the vector kernels
+    long long npartials = 0;
+    int sms = 0;
+};
+Ctx& ctx() {
+    static thread_local Ctx c;
+    return c;
+}
+int ensure_ctx() {
+    Ctx& c = ctx();
+    if (!c.partials) {
+        c.sms = rt_sm_count();
+        c.npartials = (long long)c.sms * 8 * 4;
+        if (rt_malloc((void**)&c.partials, c.npartials * sizeof(double))) return NB2_ERR_CUDA;
+    }
+    return 0;
+}
+long long vec_grid(long long n) {
+    Ctx& c = ctx();
+    const long long want = (n + kVecThreads - 1) / kVecThreads;
+    return std::max(1ll, std::min(want, (long long)c.sms * 8));
+}
+
+}  // namespace
+
+struct nb2_plan {
+    int ndim = 0, naxes = 0, dtype = 0;
+    long long shape[kMaxDim] = {0};
+    int axes[kMaxDim] = {0};
+    long long total = 1;
+    bool fast = false;
+    // fast path geometry: (batch, N0, N1, N2)
+    Geom g{};
+    void* tw0 = nullptr;  // strided axis-0 table (N0 entries)
+    void* tw1 = nullptr;  // strided axis-1 table (N1 entries)
+    void* twr = nullptr;  // row table (N2 entries)
+    double* partials = nullptr;
+    long long npartials = 0;
+    // generic path
+    void* roots[kMaxDim] = {nullptr};  // cplx<double>[n] per transformed axis
+    void* work0 = nullptr;
+    void* work1 = nullptr;  // complex scratch
+};
+
+namespace {
+
+template <typename T>
+int upload_table(void** dev, long long n, long long denom) {
+    std::vector<cplx<T>> h(n);
+    const long double tau = 6.283185307179586476925286766559005768394L;
+    for (long long j = 0; j < n; ++j) {
+        // exact octant reduction keeps the table accurate to the last bit of T
+        const long double a = tau * (long double)j / (long double)denom;
+        h[j].re = (T)cosl(a);
+        h[j].im = (T)(-sinl(a));
+    }
+    if (rt_malloc(dev, n * sizeof(cplx<T>))) return NB2_ERR_CUDA;
+    return rt_h2d(*dev, h.data(), n * sizeof(cplx<T>), nullptr);
+}
+
+// ---------------------------------------------------------------- radix plans
+// log2(n) -> (R1, R2, R3)
+#define NB2_PLAN_SWITCH(LOGN, CALL)                 \
+    switch (LOGN) {                                 \
+        case 1: CALL(2, 1, 1); break;               \
+        case 2: CALL(4, 1, 1); break;               \
+        case 3: CALL(8, 1, 1); break;               \
+        case 4: CALL(16, 1, 1); break;              \
+        case 5: CALL(32, 1, 1); break;              \
+        case 6: CALL(8, 1, 8); break;               \
+        case 7: CALL(16, 1, 8); break;              \
+        case 8: CALL(16, 1, 16); break;             \
+        case 9: CALL(32, 1, 16); break;             \
+        case 10: CALL(32, 1, 32); break;            \
+        case 11: CALL(16, 8, 16); break;            \
+        case 12: CALL(16, 16, 16); break;           \
+        case 13: CALL(32, 16, 16); break;           \
+        default: rc = NB2_ERR_UNSUPPORTED; break;   \
+    }
+
+struct PlanDims { int r1, r2, r3; };
+PlanDims plan_dims(int logn) {
+    int rc = 0;
+    PlanDims d{0, 0, 0};
+#define NB2_GETDIMS(A, B, C) d = PlanDims{A, B, C}
+    NB2_PLAN_SWITCH(logn, NB2_GETDIMS)
+#undef NB2_GETDIMS
+    (void)rc;
+    return d;
+}
+int pitch_of(int logn) {
+    const PlanDims d = plan_dims(logn);
+    if (!d.r1) return 0;
+    return d.r1 * d.r2 * d.r3 + d.r1 * d.r2 + (d.r2 > 1 ? d.r1 : 0);
+}
+
+template <typename T>
+PointOp<T> to_pointop(const nb2_pointop* o, double* partials) {
+    PointOp<T> r;
+    r.amp_mode = o ? o->amp_mode : 0;
+    r.amp = o ? (const T*)o->amp : nullptr;
+    r.scale = o ? (T)o->scale : T(1);
+    r.mul = o ? (const T*)o->mul : nullptr;
+    r.add = o ? (const T*)o->add : nullptr;
+    r.add_scalar = o ? (T)o->add_scalar : T(0);
+    r.dot = o ? (const T*)o->dot : nullptr;
+    r.dot_partials = partials;
+    return r;
+}
+
+int round32(long long v) { return (int)std::max(32ll, ((v + 31) / 32) * 32); }
+
+// choose tile width for a strided pass over rows of `inner` complex elements
+template <typename T>
+int choose_logw(int logn, long long inner) {
+    const size_t col = size_t(pitch_of(logn)) * sizeof(cplx<T>);  // bytes per tile column
+    int logw = 0;
+    while ((1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= 72 * 1024) ++logw;
+    // prefer at least 64-byte row segments when they fit in shared memory
+    const int want = ilog2(64 / sizeof(cplx<T>));
+    while (logw < want && (1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= kSmemLimit) ++logw;
+    return logw;
+}
+
+template <typename T>
+int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st) {
+    const int logn = axis == 0 ? pl->g.logN0 : pl->g.logN1;
+    if (logn == 0) {  // nothing to transform; still apply prologue / copy
+        return NB2_ERR_ARG;
+    }
+    const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
+    const long long outer = axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
+    const int logw = choose_logw<T>(logn, inner);
+    int rc = 0;
+#define NB2_RUN_STRIDED(A, B, C)                                                              \
+    {                                                                                         \
+        typedef StridedPass<T, A, B, C> K;                                                    \
+        typename K::Params p;                                                                 \
+        p.in = (const cplx<T>*)in;                                                            \
+        p.out = (cplx<T>*)out;                                                                \
+        p.tw = (const cplx<T>*)(axis == 0 ? pl->tw0 : pl->tw1);                               \
+        p.inner = inner;                                                                      \
+        p.logw = logw;                                                                        \
+        p.tiles_per_outer = inner >> logw;                                                    \
+        p.axis = axis;                                                                        \
+        p.has_pro = pro ? 1 : 0;                                                              \
+        p.pro = to_pointop<T>(pro, nullptr);                                                  \
+        p.g = pl->g;                                                                          \
+        const size_t smem = K::smem_bytes(logw);                                              \
+        if (smem > kSmemLimit) {                                                              \
+            rc = NB2_ERR_UNSUPPORTED;                                                         \
+        } else {                                                                              \
+            const long long nb1 = (long long)(B * C) << logw;                                 \
+            const int maxt = K::MAX_THREADS;                                \
+            const int nthreads = std::min(maxt, round32(nb1));                                \
+            rc = rt_launch<K>(outer * p.tiles_per_outer, nthreads, smem, st, p);              \
+        }                                                                                     \
+    }
+    NB2_PLAN_SWITCH(logn, NB2_RUN_STRIDED)
+#undef NB2_RUN_STRIDED
+    return rc;
+}
+
+template <typename T>
+int choose_G(int logm, long long Q) {
+    const size_t row = size_t(pitch_of(logm)) * sizeof(cplx<T>);
+    int G = 1;
+    while (G < 16 && 2 * G <= Q && size_t(4 * G) * row <= 72 * 1024) G *= 2;
+    return G;
+}
+
+template <typename T>
+int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
+             rt_stream st) {
+    const int logm = pl->g.logM;
+    const RowPairs rp = row_pairs(pl->g);
+    const int G = choose_G<T>(logm, rp.Q);
+    const long long ctas_per_item = (rp.Q + G - 1) / G;
+    const long long grid = ctas_per_item * pl->g.batch;
+    const bool want_dot = epi && epi->dot;
+    if (want_dot) {
+        if (!epi->dot_out) {
+            last_error() = "nb2_pointop.dot set without dot_out";
+            return NB2_ERR_ARG;
+        }
+        if (grid > pl->npartials) {
+            rt_sync(st);
+            rt_free(pl->partials);
+            pl->partials = nullptr;
+            pl->npartials = 0;
+            if (rt_malloc((void**)&pl->partials, grid * sizeof(double))) return NB2_ERR_CUDA;
+            pl->npartials = grid;
+        }
+    }
+    int rc = 0;
+#define NB2_RUN_ROWS(A, B, C)                                                                 \
+    {                                                                                         \
+        typedef RowPass<T, A, B, C> K;                                                        \
+        typename K::Params p;                                                                 \
+        p.in = (const cplx<T>*)in;                                                            \
+        p.out = (T*)out;                                                                      \
+        p.tw = (const cplx<T>*)pl->twr;                                                       \
+        p.g = pl->g;                                                                          \
+        p.ctas_per_item = ctas_per_item;                                                      \
+        p.G = G;                                                                              \
+        p.conv = conv;                                                                        \
+        p.has_pro = pro ? 1 : 0;                                                              \
+        p.pro = to_pointop<T>(pro, nullptr);                                                  \
+        p.epi = to_pointop<T>(epi, pl->partials);                                             \
+        const long long nb1 = (long long)2 * G * B * C;                                       \
+        const int maxt = K::MAX_THREADS;                                    \
+        const int nthreads = std::min(maxt, round32(nb1));                                    \
+        const size_t smem = K::smem_bytes(G, nthreads);                                       \
+        if (smem > kSmemLimit)                                                                \
+            rc = NB2_ERR_UNSUPPORTED;                                                         \
+        else                                                                                  \
+            rc = rt_launch<K>(grid, nthreads, smem, st, p);                                   \
+    }
+    NB2_PLAN_SWITCH(logm, NB2_RUN_ROWS)
+#undef NB2_RUN_ROWS
+    if (rc) return rc;
+    if (want_dot) {
+        FinalReduce::Params fp;
+        fp.partials = pl->partials;
+        fp.nparts = grid;
+        fp.nv = 1;
+        fp.out = epi->dot_out;
+        rc = rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
+    }
+    return rc;
+}
+
+template <typename T>
+int hartley_fast(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
+                 rt_stream st) {
+    const void* cur = in;
+    const nb2_pointop* p = pro;
+    int rc;
+    if (pl->g.logN0 > 0) {
+        if ((rc = run_strided<T>(pl, 0, cur, out, p, st))) return rc;
+        cur = out;
+        p = nullptr;
+    }
+    if (pl->g.logN1 > 0) {
+        if ((rc = run_strided<T>(pl, 1, cur, out, p, st))) return rc;
+        cur = out;
+        p = nullptr;
+    }
+    return run_rows<T>(pl, cur, out, conv, p, epi, st);
+}
+
+// ---------------------------------------------------------------- generic path
+template <typename T>
+int ensure_work(nb2_plan* pl) {
+    if (!pl->work0) {
+        if (rt_malloc(&pl->work0, pl->total * sizeof(cplx<T>))) return NB2_ERR_CUDA;
+        if (rt_malloc(&pl->work1, pl->total * sizeof(cplx<T>))) return NB2_ERR_CUDA;
+    }
+    return 0;
+}
+
+// transform work buffer `a` over all plan axes; result pointer returned in *res (a or b)
+template <typename T>
+int generic_axes(nb2_plan* pl, cplx<T>* a, cplx<T>* b, int forward, rt_stream st, cplx<T>** res) {
+    for (int t = 0; t < pl->naxes; ++t) {
+        const int ax = pl->axes[t];
+        typename NaiveDft<T>::Params p;
+        p.in = a;
+        p.out = b;
+        p.root = (const cplx<double>*)pl->roots[t];
+        p.n = pl->shape[ax];
+        p.outer = 1;
+        p.inner = 1;
+        for (int i = 0; i < ax; ++i) p.outer *= pl->shape[i];
+        for (int i = ax + 1; i < pl->ndim; ++i) p.inner *= pl->shape[i];
+        p.forward = forward;
+        p.nctas = vec_grid(pl->total);
+        if (p.n > 1) {
+            int rc = rt_launch<NaiveDft<T>>(p.nctas, kVecThreads, 0, st, p);
+            if (rc) return rc;
+            std::swap(a, b);
+        }
+    }
+    *res = a;
+    return 0;
+}
+
+template <typename T>
+int eltwise(nb2_plan* pl, const T* in, T* out, const nb2_pointop* op, rt_stream st) {
+    if (op->amp_mode == 1) {
+        last_error() = "amp_mode 1 (ksq table) requires the power-of-two fast path";
+        return NB2_ERR_UNSUPPORTED;
+    }
+    const long long grid = vec_grid(pl->total);
+    if (op->dot && grid > pl->npartials) {
+        rt_sync(st);
+        rt_free(pl->partials);
+        pl->partials = nullptr;
+        if (rt_malloc((void**)&pl->partials, grid * sizeof(double))) return NB2_ERR_CUDA;
+        pl->npartials = grid;
+    }
+    typename Eltwise<T>::Params p;
+    p.in = in;
+    p.out = out;
+    p.op = to_pointop<T>(op, pl->partials);
+    p.n = pl->total;
+    // amp field spans the trailing block that contains all transformed axes
+    p.item = 1;
+    for (int i = pl->axes[0]; i < pl->ndim; ++i) p.item *= pl->shape[i];
+    p.nctas = grid;
+    int rc = rt_launch<Eltwise<T>>(grid, kVecThreads, Eltwise<T>::smem_bytes(kVecThreads), st, p);
+    if (rc) return rc;
+    if (op->dot) {
+        if (!op->dot_out) {
+            last_error() = "nb2_pointop.dot set without dot_out";
+            return NB2_ERR_ARG;
+        }
+        FinalReduce::Params fp;
+        fp.partials = pl->partials;
+        fp.nparts = grid;
+        fp.nv = 1;
+        fp.out = op->dot_out;
+        rc = rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
+    }
+    return rc;
+}
+
+template <typename T>
+int hartley_generic(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro,
+                    const nb2_pointop* epi, rt_stream st) {
+    int rc;
+    if ((rc = ensure_work<T>(pl))) return rc;
+    const long long grid = vec_grid(pl->total);
+    const T* src = (const T*)in;
+    if (pro) {
+        if ((rc = eltwise<T>(pl, (const T*)in, (T*)out, pro, st))) return rc;
+        src = (const T*)out;
+    }
+    typename RealToCplx<T>::Params rp;
+    rp.in = src;
+    rp.out = (cplx<T>*)pl->work0;
+    rp.n = pl->total;
+    rp.nctas = grid;
+    if ((rc = rt_launch<RealToCplx<T>>(grid, kVecThreads, 0, st, rp))) return rc;
+    cplx<T>* res = nullptr;
+    if ((rc = generic_axes<T>(pl, (cplx<T>*)pl->work0, (cplx<T>*)pl->work1, 1, st, &res))) return rc;
+    typename CplxToHartley<T>::Params hp;
+    hp.in = res;
+    hp.out = (T*)out;
+    hp.scale = T(1);
+    hp.conv = conv;
+    hp.n = pl->total;
+    hp.nctas = grid;
+    if ((rc = rt_launch<CplxToHartley<T>>(grid, kVecThreads, 0, st, hp))) return rc;
+    if (epi) rc = eltwise<T>(pl, (const T*)out, (T*)out, epi, st);
+    return rc;
+}
+
+template <typename T>
+int c2c_impl(nb2_plan* pl, const void* in, void* out, int forward, double scale, rt_stream st) {
+    int rc;
+    if ((rc = ensure_work<T>(pl))) return rc;
+    if ((rc = rt_d2d(pl->work0, in, pl->total * sizeof(cplx<T>), st))) return rc;
+    cplx<T>* res = nullptr;
+    if ((rc = generic_axes<T>(pl, (cplx<T>*)pl->work0, (cplx<T>*)pl->work1, forward, st, &res))) return rc;
+    typename CplxScale<T>::Params sp;
+    sp.in = res;
+    sp.out = (cplx<T>*)out;
+    sp.scale = (T)scale;
+    sp.n = pl->total;
+    sp.nctas = vec_grid(pl->total);
+    return rt_launch<CplxScale<T>>(sp.nctas, kVecThreads, 0, st, sp);
+}
+
+}  // namespace
+
+// ================================================================== extern "C"
+extern "C" {
+
+int nb2_version(void) { return 100; }
+const char* nb2_last_error(void) { return last_error().c_str(); }
+int nb2_sm_count(void) { return rt_sm_count(); }
+
+int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* axes, int dtype, nb2_plan** out) {
+    if (!out || !shape || ndim < 1 || ndim > kMaxDim || naxes < 0 || naxes > ndim ||
+        (dtype != NB2_F32 && dtype != NB2_F64)) {
+        last_error() = "nb2_plan_create: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (ensure_ctx()) return NB2_ERR_CUDA;
+    nb2_plan* pl = new (std::nothrow) nb2_plan();
+    if (!pl) return NB2_ERR_ARG;
+    pl->ndim = ndim;
+    pl->dtype = dtype;
+    for (int i = 0; i < ndim; ++i) {
+        if (shape[i] < 1) {
+            delete pl;
+            last_error() = "nb2_plan_create: non-positive extent";
+            return NB2_ERR_ARG;
+        }
+        pl->shape[i] = shape[i];
+        pl->total *= shape[i];
+    }
+    std::vector<int> ax;
+    if (!axes || naxes == 0) {
+        for (int i = 0; i < ndim; ++i) ax.push_back(i);
+    } else {
+        for (int i = 0; i < naxes; ++i) {
+            int a = axes[i] < 0 ? axes[i] + ndim : axes[i];
+            if (a < 0 || a >= ndim || std::find(ax.begin(), ax.end(), a) != ax.end()) {
+                delete pl;
+                last_error() = "nb2_plan_create: invalid or repeated axis";
+                return NB2_ERR_ARG;
+            }
+            ax.push_back(a);
+        }
+    }
+    std::sort(ax.begin(), ax.end());
+    pl->naxes = (int)ax.size();
+    for (int i = 0; i < pl->naxes; ++i) pl->axes[i] = ax[i];
+
+    // ---- fast path eligibility: trailing 1..3 axes, powers of two, last >= 4
+    bool fast = pl->naxes >= 1 && pl->naxes <= 3;
+    for (int i = 0; fast && i < pl->naxes; ++i) {
+        if (pl->axes[i] != ndim - pl->naxes + i) fast = false;
+        if (!is_pow2(pl->shape[pl->axes[i]])) fast = false;
+    }
+    if (fast && pl->shape[ndim - 1] < 4) fast = false;
+    if (fast) {
+        long long n[3] = {1, 1, 1};
+        for (int i = 0; i < pl->naxes; ++i) n[3 - pl->naxes + i] = pl->shape[pl->axes[i]];
+        pl->g.logN0 = ilog2(n[0]);
+        pl->g.logN1 = ilog2(n[1]);
+        pl->g.logM = ilog2(n[2]) - 1;
+        pl->g.batch = 1;
+        for (int i = 0; i < ndim - pl->naxes; ++i) pl->g.batch *= pl->shape[i];
+        const size_t es = dtype == NB2_F32 ? sizeof(cplx<float>) : sizeof(cplx<double>);
+        if (pl->g.logN0 > 13 || pl->g.logN1 > 13 || pl->g.logM > 13 || pl->g.logM < 1) fast = false;
+        if (fast && pl->g.logN0 && size_t(pitch_of(pl->g.logN0)) * es > kSmemLimit) fast = false;
+        if (fast && pl->g.logN1 && size_t(pitch_of(pl->g.logN1)) * es > kSmemLimit) fast = false;
+        if (fast && size_t(2 * pitch_of(pl->g.logM)) * es + 2048 > kSmemLimit) fast = false;
+    }
+    pl->fast = fast;
+    int rc = 0;
+    if (fast) {
+        if (dtype == NB2_F32) {
+            if (pl->g.logN0) rc |= upload_table<float>(&pl->tw0, 1ll << pl->g.logN0, 1ll << pl->g.logN0);
+            if (pl->g.logN1) rc |= upload_table<float>(&pl->tw1, 1ll << pl->g.logN1, 1ll << pl->g.logN1);
+            rc |= upload_table<float>(&pl->twr, 2ll << pl->g.logM, 2ll << pl->g.logM);
+        } else {
+            if (pl->g.logN0) rc |= upload_table<double>(&pl->tw0, 1ll << pl->g.logN0, 1ll << pl->g.logN0);
+            if (pl->g.logN1) rc |= upload_table<double>(&pl->tw1, 1ll << pl->g.logN1, 1ll << pl->g.logN1);
+            rc |= upload_table<double>(&pl->twr, 2ll << pl->g.logM, 2ll << pl->g.logM);
+        }
+    }
+    for (int t = 0; t < pl->naxes && !rc; ++t) {
+        const long long n = pl->shape[pl->axes[t]];
+        rc |= upload_table<double>(&pl->roots[t], n, n);
+    }
+    if (rc) {
+        nb2_plan_destroy(pl);
+        return NB2_ERR_CUDA;
+    }
+    *out = pl;
+    return NB2_OK;
+}
+
+int nb2_plan_destroy(nb2_plan* pl) {
+    if (!pl) return NB2_OK;
+    rt_free(pl->tw0);
+    rt_free(pl->tw1);
+    rt_free(pl->twr);
+    rt_free(pl->partials);
+    rt_free(pl->work0);
+    rt_free(pl->work1);
+    for (int t = 0; t < kMaxDim; ++t) rt_free(pl->roots[t]);
+    delete pl;
+    return NB2_OK;
+}
+
+int nb2_plan_is_fast(const nb2_plan* pl) { return pl && pl->fast ? 1 : 0; }
+
+int64_t nb2_plan_ksq_size(const nb2_plan* pl) {
+    if (!pl || !pl->fast) return 0;
+    const long long h0 = (1ll << pl->g.logN0) / 2, h1 = (1ll << pl->g.logN1) / 2, h2 = 1ll << pl->g.logM;
+    return 1 + h0 * h0 + h1 * h1 + h2 * h2;
+}
+
+int nb2_hartley(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
+                void* stream) {
+    if (!pl || !in || !out || (conv != 0 && conv != 1)) {
+        last_error() = "nb2_hartley: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    rt_stream st = (rt_stream)stream;
+    if (pl->fast)
+        return pl->dtype == NB2_F32 ? hartley_fast<float>(pl, in, out, conv, pro, epi, st)
+                                    : hartley_fast<double>(pl, in, out, conv, pro, epi, st);
+    return pl->dtype == NB2_F32 ? hartley_generic<float>(pl, in, out, conv, pro, epi, st)
+                                : hartley_generic<double>(pl, in, out, conv, pro, epi, st);
+}
+
+int nb2_c2c(nb2_plan* pl, const void* in, void* out, int forward, double scale, void* stream) {
+    if (!pl || !in || !out) {
+        last_error() = "nb2_c2c: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    rt_stream st = (rt_stream)stream;
+    return pl->dtype == NB2_F32 ? c2c_impl<float>(pl, in, out, forward, scale, st)
+                                : c2c_impl<double>(pl, in, out, forward, scale, st);
+}
+
+int nb2_vdot(int dtype, int64_t n, const void* a, const void* b, double* out_dev, void* stream) {
+    if (n < 0 || !out_dev || (n > 0 && (!a || !b))) {
+        last_error() = "nb2_vdot: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (ensure_ctx()) return NB2_ERR_CUDA;
+    rt_stream st = (rt_stream)stream;
+    const long long grid = vec_grid(n);
+    int rc;
+    if (dtype == NB2_F32) {
+        Dot<float>::Params p{(const float*)a, (const float*)b, n, ctx().partials, grid};
+        rc = rt_launch<Dot<float>>(grid, kVecThreads, Dot<float>::smem_bytes(kVecThreads), st, p);
+    } else if (dtype == NB2_F64) {
+        Dot<double>::Params p{(const double*)a, (const double*)b, n, ctx().partials, grid};
+        rc = rt_launch<Dot<double>>(grid, kVecThreads, Dot<double>::smem_bytes(kVecThreads), st, p);
+    } else {
+        return NB2_ERR_ARG;
+    }
+    if (rc) return rc;
+    FinalReduce::Params fp{ctx().partials, grid, 1, out_dev};
+    return rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
+}
+
+int nb2_axpby(int dtype, int64_t n, double a, const void* x, double b, void* y, void* stream) {
+    if (n < 0 || (n > 0 && (!x || !y))) {
+        last_error() = "nb2_axpby: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (ensure_ctx()) return NB2_ERR_CUDA;
+    rt_stream st = (rt_stream)stream;
+    const long long grid = vec_grid(n);
+    if (dtype == NB2_F32) {
+        Axpby<float>::Params p{(const float*)x, (float*)y, (float)a, (float)b, n, grid};
+        return rt_launch<Axpby<float>>(grid, kVecThreads, 0, st, p);
+    } else if (dtype == NB2_F64) {
+        Axpby<double>::Params p{(const double*)x, (double*)y, a, b, n, grid};
+        return rt_launch<Axpby<double>>(grid, kVecThreads, 0, st, p);
+    }
+    return NB2_ERR_ARG;
+}
+
+int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, const void* q, const void* b,
+                  void* x, void* r, double* sums_dev, void* stream) {
+    if (n < 0 || !sums_dev || (mode != 0 && mode != 1) || !x || !r || !q || !b || (mode == 0 && !d)) {
+        last_error() = "nb2_cg_update: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (ensure_ctx()) return NB2_ERR_CUDA;
+    rt_stream st = (rt_stream)stream;
+    const long long grid = vec_grid(n);
+    int rc;
+    if (dtype == NB2_F32) {
+        CgUpdate<float>::Params p{(float*)x, (float*)r, (const float*)d, (const float*)q, (const float*)b,
+                                  (float)alpha, mode, n, ctx().partials, grid};
+        rc = rt_launch<CgUpdate<float>>(grid, kVecThreads, CgUpdate<float>::smem_bytes(kVecThreads), st, p);
+    } else if (dtype == NB2_F64) {
+        CgUpdate<double>::Params p{(double*)x, (double*)r, (const double*)d, (const double*)q, (const double*)b,
+                                   alpha, mode, n, ctx().partials, grid};
+        rc = rt_launch<CgUpdate<double>>(grid, kVecThreads, CgUpdate<double>::smem_bytes(kVecThreads), st, p);
+    } else {
+        return NB2_ERR_ARG;
+    }
+    if (rc) return rc;
+    FinalReduce::Params fp{ctx().partials, grid, 3, sums_dev};
+    return rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
+}
+
+int nb2_hartley_host(nb2_plan* pl, const void* in_host, void* out_host, int conv, double scale) {
+    if (!pl || !in_host || !out_host) return NB2_ERR_ARG;
+    const size_t es = pl->dtype == NB2_F32 ? 4 : 8;
+    void* buf = nullptr;
+    if (rt_malloc(&buf, pl->total * es)) return NB2_ERR_CUDA;
+    int rc = rt_h2d(buf, in_host, pl->total * es, nullptr);
+    nb2_pointop epi{};
+    epi.scale = scale;
+    if (!rc) rc = nb2_hartley(pl, buf, buf, conv, nullptr, scale == 1.0 ? nullptr : &epi, nullptr);
+    if (!rc) rc = rt_d2h(out_host, buf, pl->total * es, nullptr);
+    rt_free(buf);
+    return rc;
+}
+
+int nb2_c2c_host(nb2_plan* pl, const void* in_host, void* out_host, int forward, double scale) {
+    if (!pl || !in_host || !out_host) return NB2_ERR_ARG;
+    const size_t es = pl->dtype == NB2_F32 ? 8 : 16;
+    void* buf = nullptr;
+    if (rt_malloc(&buf, pl->total * es)) return NB2_ERR_CUDA;
+    int rc = rt_h2d(buf, in_host, pl->total * es, nullptr);
+    if (!rc) rc = nb2_c2c(pl, buf, buf, forward, scale, nullptr);
+    if (!rc) rc = rt_d2h(out_host, buf, pl->total * es, nullptr);
+    rt_free(buf);
+    return rc;
+}
+
+}  // extern "C"

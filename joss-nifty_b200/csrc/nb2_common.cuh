@@ -1,0 +1,115 @@
+// niftyb200 -- common definitions shared by every kernel.
+//
+// All kernels are written as a sequence of *phases* separated by block barriers.
+// A phase is a plain `NB2_HD` function of (params, block id, thread id, #threads, smem).
+// On the device the phases of a kernel are executed by the generic launcher in
+// nb2_launch.cuh with `__syncthreads()` between them.  The same phase functions can be
+// compiled by a host C++ compiler (-DNB2_EMU) and executed by a sequential thread
+// emulator; this is TEST INFRASTRUCTURE used to check the index arithmetic on machines
+// without a GPU (tests/emu) and is never part of the shipped library.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <cmath>
+
+#if defined(__CUDACC__)
+#define NB2_HD __host__ __device__ __forceinline__
+#define NB2_D __device__ __forceinline__
+#define NB2_HDC __host__ __device__ constexpr
+#else
+#define NB2_HD inline
+#define NB2_D inline
+#define NB2_HDC constexpr
+#endif
+
+#if defined(__CUDA_ARCH__)
+#define NB2_UNROLL _Pragma("unroll")
+#else
+#define NB2_UNROLL
+#endif
+
+namespace nb2 {
+
+// ---------------------------------------------------------------- complex numbers
+template <typename T>
+struct alignas(2 * sizeof(T)) cplx {
+    T re, im;
+};
+
+template <typename T> NB2_HD cplx<T> mk(T a, T b) { cplx<T> r; r.re = a; r.im = b; return r; }
+template <typename T> NB2_HD cplx<T> operator+(cplx<T> a, cplx<T> b) { return mk<T>(a.re + b.re, a.im + b.im); }
+template <typename T> NB2_HD cplx<T> operator-(cplx<T> a, cplx<T> b) { return mk<T>(a.re - b.re, a.im - b.im); }
+template <typename T> NB2_HD cplx<T> operator*(cplx<T> a, cplx<T> b) {
+    return mk<T>(a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re);
+}
+template <typename T> NB2_HD cplx<T> operator*(cplx<T> a, T s) { return mk<T>(a.re * s, a.im * s); }
+template <typename T> NB2_HD cplx<T> conj(cplx<T> a) { return mk<T>(a.re, -a.im); }
+// multiply by -i (forward quarter turn) / +i
+template <typename T> NB2_HD cplx<T> mul_mi(cplx<T> a) { return mk<T>(a.im, -a.re); }
+template <typename T> NB2_HD cplx<T> mul_pi(cplx<T> a) { return mk<T>(-a.im, a.re); }
+
+// ---------------------------------------------------------------- small helpers
+NB2_HD int ilog2(unsigned long long v) { int l = 0; while (v > 1) { v >>= 1; ++l; } return l; }
+NB2_HD bool is_pow2(long long v) { return v > 0 && (v & (v - 1)) == 0; }
+
+// Hartley sign: +1 -> "non_canonical_hartley" (Re F + Im F, the reference default,
+// src/ducc_dispatch.py:46-50), -1 -> "canonical_hartley" (Re F - Im F).
+enum : int { NB2_NONCANONICAL = 0, NB2_CANONICAL = 1 };
+
+// ---------------------------------------------------------------- cache-hinted global access
+// Streaming data is touched exactly once per pass: keep it out of L1.
+template <typename V> NB2_HD V ld_stream(const V* p) {
+#if defined(__CUDA_ARCH__)
+    return __ldcs(p);
+#else
+    return *p;
+#endif
+}
+template <typename V> NB2_HD void st_stream(V* p, V v) {
+#if defined(__CUDA_ARCH__)
+    __stcs(p, v);
+#else
+    *p = v;
+#endif
+}
+template <typename V> NB2_HD V ld_ro(const V* p) {
+#if defined(__CUDA_ARCH__)
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+
+#if defined(__CUDACC__)
+template <typename T> struct vec2_of;
+template <> struct vec2_of<float> { using type = float2; };
+template <> struct vec2_of<double> { using type = double2; };
+#endif
+
+template <typename T> NB2_HD cplx<T> ldc_stream(const cplx<T>* p) {
+#if defined(__CUDA_ARCH__)
+    typename vec2_of<T>::type v = __ldcs(reinterpret_cast<const typename vec2_of<T>::type*>(p));
+    return mk<T>(v.x, v.y);
+#else
+    return *p;
+#endif
+}
+template <typename T> NB2_HD void stc_stream(cplx<T>* p, cplx<T> v) {
+#if defined(__CUDA_ARCH__)
+    typename vec2_of<T>::type w; w.x = v.re; w.y = v.im;
+    __stcs(reinterpret_cast<typename vec2_of<T>::type*>(p), w);
+#else
+    *p = v;
+#endif
+}
+template <typename T> NB2_HD cplx<T> ldc_ro(const cplx<T>* p) {
+#if defined(__CUDA_ARCH__)
+    typename vec2_of<T>::type v = __ldg(reinterpret_cast<const typename vec2_of<T>::type*>(p));
+    return mk<T>(v.x, v.y);
+#else
+    return *p;
+#endif
+}
+
+}  // namespace nb2

@@ -1,0 +1,114 @@
+// niftyb200 -- generic-size path (correctness-first): any length, any subset of axes.
+//
+// Used for everything the power-of-two fast path does not cover (odd lengths such as the
+// reference tests' (10,), (12,9), (15,27); transforms over non-trailing axes; complex c2c
+// for ducc_dispatch.fftn/ifftn, src/ducc_dispatch.py:66-72).  One O(n) direct DFT sum per
+// output element and axis, accumulated in fp64 with an fp64 root table.  Not
+// roofline-graded.
+#pragma once
+
+#include "nb2_common.cuh"
+
+namespace nb2 {
+
+// out[o, k, i] = sum_j in[o, j, i] * root[(j k) mod n]^(+-1)
+template <typename T>
+struct NaiveDft {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 256;
+    struct Params {
+        const cplx<T>* in;
+        cplx<T>* out;
+        const cplx<double>* root;  // root[j] = exp(-2 pi i j / n)
+        long long outer, n, inner;
+        int forward;
+        long long nctas;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+        const long long total = p.outer * p.n * p.inner, stride = p.nctas * nthreads;
+        for (long long e = bid * nthreads + tid; e < total; e += stride) {
+            const long long i = e % p.inner, k = (e / p.inner) % p.n, o = e / (p.inner * p.n);
+            const cplx<T>* src = p.in + o * p.n * p.inner + i;
+            double sr = 0, si = 0;
+            long long ph = 0;
+            for (long long j = 0; j < p.n; ++j) {
+                const cplx<T> v = src[j * p.inner];
+                cplx<double> w = p.root[ph];
+                if (!p.forward) w.im = -w.im;
+                sr += double(v.re) * w.re - double(v.im) * w.im;
+                si += double(v.re) * w.im + double(v.im) * w.re;
+                ph += k;
+                if (ph >= p.n) ph -= p.n;
+            }
+            p.out[e] = mk<T>(T(sr), T(si));
+        }
+    }
+};
+
+// real -> complex (imag = 0), with optional scale
+template <typename T>
+struct RealToCplx {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 256;
+    struct Params {
+        const T* in;
+        cplx<T>* out;
+        long long n, nctas;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+        const long long stride = p.nctas * nthreads;
+        for (long long e = bid * nthreads + tid; e < p.n; e += stride) p.out[e] = mk<T>(p.in[e], T(0));
+    }
+};
+
+// complex -> Hartley combine:  out = (re +/- im) * scale     (src/ducc_dispatch.py:46-50)
+template <typename T>
+struct CplxToHartley {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 256;
+    struct Params {
+        const cplx<T>* in;
+        T* out;
+        T scale;
+        int conv;
+        long long n, nctas;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+        const long long stride = p.nctas * nthreads;
+        for (long long e = bid * nthreads + tid; e < p.n; e += stride) {
+            const cplx<T> v = p.in[e];
+            p.out[e] = (p.conv == NB2_CANONICAL ? v.re - v.im : v.re + v.im) * p.scale;
+        }
+    }
+};
+
+// complex scale / copy: out = in * scale
+template <typename T>
+struct CplxScale {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 256;
+    struct Params {
+        const cplx<T>* in;
+        cplx<T>* out;
+        T scale;
+        long long n, nctas;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+        const long long stride = p.nctas * nthreads;
+        for (long long e = bid * nthreads + tid; e < p.n; e += stride) p.out[e] = p.in[e] * p.scale;
+    }
+};
+
+}  // namespace nb2

@@ -1,0 +1,158 @@
+// niftyb200 -- kernel launcher and the tiny runtime shim.
+//
+// Device build (nvcc): every kernel struct K (Params, NPHASES, enabled(ph), phase<PH>(),
+// smem_bytes) is run by `nb2_kernel<K>`: its phases in order with __syncthreads() between
+// them.  Emulator build (-DNB2_EMU, host compiler, TEST INFRASTRUCTURE ONLY -- see
+// tests/emu): the same phases are executed sequentially for every (block, thread).
+#pragma once
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "nb2_common.cuh"
+
+#if !defined(NB2_EMU)
+#include <cuda_runtime.h>
+#endif
+
+namespace nb2 {
+
+inline std::string& last_error() {
+    static thread_local std::string e;
+    return e;
+}
+
+#if !defined(NB2_EMU)
+// ------------------------------------------------------------------ device runtime
+#define NB2_CUDA_OK(call)                                                                      \
+    do {                                                                                       \
+        cudaError_t err__ = (call);                                                            \
+        if (err__ != cudaSuccess) {                                                            \
+            nb2::last_error() = std::string(#call) + ": " + cudaGetErrorString(err__);        \
+            return -2;                                                                         \
+        }                                                                                      \
+    } while (0)
+
+typedef cudaStream_t rt_stream;
+
+template <class K, int PH, bool IN_RANGE = (PH < K::NPHASES)>
+struct PhaseStep {
+    __device__ __forceinline__ static void run(const typename K::Params& p, char* smem, bool first) {
+        bool f = first;
+        if (K::enabled(PH)) {
+            if (!f) __syncthreads();
+            K::template phase<PH>(p, (long long)blockIdx.x, (int)threadIdx.x, (int)blockDim.x, smem);
+            f = false;
+        }
+        PhaseStep<K, PH + 1>::run(p, smem, f);
+    }
+};
+template <class K, int PH>
+struct PhaseStep<K, PH, false> {
+    __device__ __forceinline__ static void run(const typename K::Params&, char*, bool) {}
+};
+
+template <class K>
+__global__ void __launch_bounds__(K::MAX_THREADS) nb2_kernel(const typename K::Params p) {
+    extern __shared__ __align__(16) char nb2_smem[];
+    PhaseStep<K, 0>::run(p, nb2_smem, true);
+}
+
+template <class K>
+inline int rt_launch(long long grid, int nthreads, size_t smem, rt_stream stream, const typename K::Params& p) {
+    if (grid <= 0) return 0;
+    if (grid > 2147483647ll) {
+        last_error() = "grid too large";
+        return -1;
+    }
+    if (smem > 48 * 1024) {
+        static thread_local size_t configured = 0;  // per kernel instantiation
+        if (smem > configured) {
+            NB2_CUDA_OK(cudaFuncSetAttribute(nb2_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            configured = smem;
+        }
+    }
+    nb2_kernel<K><<<(unsigned)grid, nthreads, smem, stream>>>(p);
+    NB2_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+inline int rt_malloc(void** p, size_t bytes) {
+    NB2_CUDA_OK(cudaMalloc(p, bytes ? bytes : 1));
+    return 0;
+}
+inline int rt_free(void* p) {
+    if (p) NB2_CUDA_OK(cudaFree(p));
+    return 0;
+}
+inline int rt_h2d(void* dst, const void* src, size_t bytes, rt_stream s) {
+    NB2_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s));
+    NB2_CUDA_OK(cudaStreamSynchronize(s));
+    return 0;
+}
+inline int rt_d2h(void* dst, const void* src, size_t bytes, rt_stream s) {
+    NB2_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
+    NB2_CUDA_OK(cudaStreamSynchronize(s));
+    return 0;
+}
+inline int rt_d2d(void* dst, const void* src, size_t bytes, rt_stream s) {
+    NB2_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, s));
+    return 0;
+}
+inline int rt_sync(rt_stream s) {
+    NB2_CUDA_OK(cudaStreamSynchronize(s));
+    return 0;
+}
+inline int rt_sm_count() {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+}
+
+#else
+// ------------------------------------------------------------------ sequential emulator (tests only)
+typedef void* rt_stream;
+
+template <class K, int PH, bool IN_RANGE = (PH < K::NPHASES)>
+struct EmuStep {
+    static void run(const typename K::Params& p, long long bid, int nthreads, char* smem) {
+        if (K::enabled(PH))
+            for (int tid = 0; tid < nthreads; ++tid) K::template phase<PH>(p, bid, tid, nthreads, smem);
+        EmuStep<K, PH + 1>::run(p, bid, nthreads, smem);
+    }
+};
+template <class K, int PH>
+struct EmuStep<K, PH, false> {
+    static void run(const typename K::Params&, long long, int, char*) {}
+};
+
+template <class K>
+inline int rt_launch(long long grid, int nthreads, size_t smem, rt_stream, const typename K::Params& p) {
+    std::vector<char> buf(smem + 64);
+    char* base = buf.data();
+    base += (64 - (reinterpret_cast<uintptr_t>(base) & 63)) & 63;
+    for (long long bid = 0; bid < grid; ++bid) {
+        std::memset(base, 0xAB, smem);  // poison: catches reads of unwritten shared memory
+        EmuStep<K, 0>::run(p, bid, nthreads, base);
+    }
+    return 0;
+}
+inline int rt_malloc(void** p, size_t bytes) {
+    *p = std::malloc(bytes ? bytes : 1);
+    return *p ? 0 : -2;
+}
+inline int rt_free(void* p) {
+    std::free(p);
+    return 0;
+}
+inline int rt_h2d(void* d, const void* s, size_t n, rt_stream) { std::memcpy(d, s, n); return 0; }
+inline int rt_d2h(void* d, const void* s, size_t n, rt_stream) { std::memcpy(d, s, n); return 0; }
+inline int rt_d2d(void* d, const void* s, size_t n, rt_stream) { std::memmove(d, s, n); return 0; }
+inline int rt_sync(rt_stream) { return 0; }
+inline int rt_sm_count() { return 4; }
+#endif
+
+}  // namespace nb2

@@ -1,0 +1,400 @@
+// niftyb200 -- the two FFT pass kernels of the power-of-two fast path.
+//
+// Genuine multi-D Hartley transform of a real (batch, N0, N1, N2) array
+// (reference semantics: src/ducc_dispatch.py:46-50,75-78  H = Re F +/- Im F of the JOINT FFT):
+//
+//   1. the real array is *viewed* as complex with M = N2/2 elements per row
+//      (z[m] = x[2m] + i x[2m+1]; no data movement),
+//   2. StridedPass: complex FFT along axis 0, then along axis 1 (tiles of `w` contiguous
+//      complex columns staged through shared memory, in place),
+//   3. RowPass: complex FFT along the contiguous axis for a row (k0,k1) together with its
+//      mirror row (-k0,-k1), then the "untangle" step recovers the spectrum of the real
+//      data (even/odd split) and writes H[k] = Re F[k] +/- Im F[k] for the full rows.
+//
+// Every axis therefore costs exactly one read and one write of the field (2*N*s bytes), the
+// nominal-sweep model of SURVEY.md section 8(d).  All passes may run in place.
+//
+// Each pass is an N = R1*R2*R3 point FFT done in up to three register-radix steps
+// (digits n = n3 + R3*(n2 + R2*n1), k = k1 + R1*(k2 + R2*k3)); R2 == 1 means two steps,
+// R2 == R3 == 1 a single step.
+#pragma once
+
+#include "nb2_common.cuh"
+#include "nb2_pointwise.cuh"
+#include "nb2_radix.cuh"
+
+namespace nb2 {
+
+// shared-memory slot of logical row L (padded so that every step is bank-conflict free)
+template <int R2, int R3> NB2_HD int slot_of(int L) {
+    return L + L / R3 + (R2 > 1 ? L / (R2 * R3) : 0);
+}
+template <int R1, int R2, int R3> constexpr int slot_pitch() {
+    return R1 * R2 * R3 + R1 * R2 + (R2 > 1 ? R1 : 0);
+}
+
+// ============================================================================ StridedPass
+template <typename T, int R1, int R2, int R3>
+struct StridedPass {
+    static constexpr int N = R1 * R2 * R3;
+    static constexpr int MM = R2 * R3;
+    static constexpr bool SINGLE = (MM == 1);
+    static constexpr int NPHASES = 3;
+    static constexpr int MAX_THREADS = (R1 >= 32 || R3 >= 32) ? 256 : 512;
+
+    struct Params {
+        const cplx<T>* in;
+        cplx<T>* out;
+        const cplx<T>* tw;          // tw[j] = exp(-2 pi i j / N), j in [0, N)
+        long long inner;            // complex elements between consecutive rows
+        long long tiles_per_outer;  // inner >> logw
+        int logw;                   // log2(tile width)
+        int axis;                   // 0 or 1: which coordinate the transformed row index is
+        int has_pro;
+        PointOp<T> pro;
+        Geom g;
+    };
+
+    static size_t smem_bytes(int logw) {
+        return SINGLE ? 0 : (size_t(slot_pitch<R1, R2, R3>()) << logw) * sizeof(cplx<T>);
+    }
+    NB2_HDC static bool enabled(int ph) { return ph == 0 || (ph == 1 && R2 > 1) || (ph == 2 && R3 > 1); }
+
+    NB2_HD static long long tile_base(const Params& p, long long bid) {
+        const long long o = bid / p.tiles_per_outer, tile = bid - o * p.tiles_per_outer;
+        return o * N * p.inner + (tile << p.logw);
+    }
+
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
+        const int w = 1 << p.logw;
+        const long long base = tile_base(p, bid);
+        if (PH == 0) {
+            const int nb = MM << p.logw;
+            for (int b = tid; b < nb; b += nthreads) {
+                const int c = b & (w - 1), r = b >> p.logw;
+                const cplx<T>* src = p.in + base + c + (long long)r * p.inner;
+                cplx<T> x[R1];
+                NB2_UNROLL
+                for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + (long long)n1 * MM * p.inner);
+                if (p.has_pro) {
+                    long long k0, k1, m;
+                    decode(p.g, base + c, k0, k1, m);
+                    const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
+                    // fixed part of ksq: the non-transformed coordinates
+                    const long long fx = p.axis == 0 ? sq_mirror(k1, p.g.logN1) : sq_mirror(k0, p.g.logN0);
+                    const long long fe = fx + sq_mirror(2 * m, p.g.logM + 1);
+                    const long long fo = fx + sq_mirror(2 * m + 1, p.g.logM + 1);
+                    const int logNrow = p.axis == 0 ? p.g.logN0 : p.g.logN1;
+                    NB2_UNROLL
+                    for (int n1 = 0; n1 < R1; ++n1) {
+                        const long long row = r + (long long)n1 * MM;
+                        T ae, ao;
+                        if (p.pro.amp_mode == 1) {
+                            const long long fr = sq_mirror(row, logNrow);
+                            ae = ld_ro(p.pro.amp + fe + fr) * p.pro.scale;
+                            ao = ld_ro(p.pro.amp + fo + fr) * p.pro.scale;
+                        } else if (p.pro.amp_mode == 2) {
+                            const long long lin = (base + c + row * p.inner) & itemmask;
+                            const cplx<T> f = ldc_stream(reinterpret_cast<const cplx<T>*>(p.pro.amp) + lin);
+                            ae = f.re * p.pro.scale;
+                            ao = f.im * p.pro.scale;
+                        } else {
+                            ae = ao = p.pro.scale;
+                        }
+                        x[n1].re *= ae;
+                        x[n1].im *= ao;
+                    }
+                }
+                fft_reg<R1, true>(x);
+                NB2_UNROLL
+                for (int k1 = 0; k1 < R1; ++k1) {
+                    cplx<T> v = x[brev<R1>(k1)];
+                    if (!SINGLE && k1 != 0) v = v * ldc_ro(p.tw + r * k1);
+                    if (SINGLE) {
+                        stc_stream(p.out + base + c + (long long)k1 * p.inner, v);
+                    } else {
+                        smem[(slot_of<R2, R3>(k1 * MM + r) << p.logw) + c] = v;
+                    }
+                }
+            }
+        } else if (PH == 1) {
+            if (R2 > 1) {
+                const int nb = (R1 * R3) << p.logw;
+                for (int b = tid; b < nb; b += nthreads) {
+                    const int c = b & (w - 1), t = b >> p.logw;
+                    const int n3 = t % R3, k1 = t / R3;
+                    cplx<T> x[R2];
+                    NB2_UNROLL
+                    for (int n2 = 0; n2 < R2; ++n2)
+                        x[n2] = smem[(slot_of<R2, R3>(k1 * MM + n2 * R3 + n3) << p.logw) + c];
+                    fft_reg<R2, true>(x);
+                    NB2_UNROLL
+                    for (int k2 = 0; k2 < R2; ++k2) {
+                        cplx<T> v = x[brev<R2>(k2)];
+                        if (k2 != 0) v = v * ldc_ro(p.tw + R1 * n3 * k2);
+                        smem[(slot_of<R2, R3>(k1 * MM + k2 * R3 + n3) << p.logw) + c] = v;
+                    }
+                }
+            }
+        } else {
+            if (R3 > 1) {
+                const int nb = (R1 * R2) << p.logw;
+                for (int b = tid; b < nb; b += nthreads) {
+                    const int c = b & (w - 1), t = b >> p.logw;
+                    const int k2 = t % R2, k1 = t / R2;
+                    cplx<T> x[R3];
+                    NB2_UNROLL
+                    for (int n3 = 0; n3 < R3; ++n3)
+                        x[n3] = smem[(slot_of<R2, R3>(k1 * MM + k2 * R3 + n3) << p.logw) + c];
+                    fft_reg<R3, true>(x);
+                    cplx<T>* dst = p.out + base + c + (long long)(k1 + R1 * k2) * p.inner;
+                    NB2_UNROLL
+                    for (int k3 = 0; k3 < R3; ++k3)
+                        stc_stream(dst + (long long)k3 * (R1 * R2) * p.inner, x[brev<R3>(k3)]);
+                }
+            }
+        }
+    }
+};
+
+// ============================================================================ RowPass
+// Row enumeration: canonical representatives of the mirror pairs {(k0,k1), (-k0,-k1)}.
+struct RowPairs {
+    long long nmid, h, Q;  // Q pairs per batch item
+};
+NB2_HD RowPairs row_pairs(const Geom& g) {
+    const long long N0 = 1ll << g.logN0, N1 = 1ll << g.logN1;
+    RowPairs rp;
+    rp.h = N1 / 2 + 1;
+    rp.nmid = N0 >= 2 ? (N0 / 2 - 1) * N1 : 0;
+    rp.Q = rp.nmid + (N0 >= 2 ? 2 : 1) * rp.h;
+    return rp;
+}
+
+struct RowSlot {
+    bool valid, dup;
+    long long k0, k1, row;  // row: linear row index over (batch, N0, N1)
+};
+
+template <typename T, int R1, int R2, int R3>
+struct RowPass {
+    static constexpr int M = R1 * R2 * R3;
+    static constexpr int MM = R2 * R3;
+    static constexpr int PITCH = slot_pitch<R1, R2, R3>();
+    static constexpr int NPHASES = 6;
+    static constexpr int MAX_THREADS = (R1 >= 32 || R3 >= 32) ? 256 : 512;
+
+    struct Params {
+        const cplx<T>* in;
+        T* out;
+        const cplx<T>* tw;  // tw[j] = exp(-2 pi i j / (2M)), j in [0, 2M)
+        Geom g;
+        long long ctas_per_item;
+        int G;     // mirror pairs per CTA (2G rows)
+        int conv;  // NB2_NONCANONICAL / NB2_CANONICAL
+        int has_pro;
+        PointOp<T> pro;
+        PointOp<T> epi;
+    };
+
+    static size_t smem_bytes(int G, int nthreads) {
+        return size_t(2 * G) * PITCH * sizeof(cplx<T>) + size_t(nthreads) * sizeof(double);
+    }
+    NB2_HDC static bool enabled(int ph) {
+        return ph == 0 || (ph == 1 && R2 > 1) || (ph == 2 && MM > 1) || ph >= 3;
+    }
+
+    NB2_HD static RowSlot slot_info(const Params& p, long long bid, int s) {
+        const RowPairs rp = row_pairs(p.g);
+        const long long item = p.g.batch == 1 ? 0 : bid / p.ctas_per_item;
+        const long long q = (bid - item * p.ctas_per_item) * p.G + (s >> 1);
+        const long long N0 = 1ll << p.g.logN0, N1 = 1ll << p.g.logN1;
+        RowSlot rs;
+        rs.valid = q < rp.Q;
+        rs.dup = false;
+        rs.k0 = rs.k1 = rs.row = 0;
+        if (!rs.valid) return rs;
+        long long k0, k1;
+        if (q < rp.nmid) {
+            k0 = 1 + (q >> p.g.logN1);
+            k1 = q & (N1 - 1);
+        } else {
+            const long long qq = q - rp.nmid;
+            k0 = (qq / rp.h) ? N0 / 2 : 0;
+            k1 = qq % rp.h;
+        }
+        const long long k0m = (N0 - k0) & (N0 - 1), k1m = (N1 - k1) & (N1 - 1);
+        if (s & 1) {
+            rs.dup = (k0m == k0 && k1m == k1);
+            k0 = k0m;
+            k1 = k1m;
+        }
+        rs.k0 = k0;
+        rs.k1 = k1;
+        rs.row = (item * N0 + k0) * N1 + k1;
+        return rs;
+    }
+
+    NB2_HD static int slot_of_k(int k) {
+        const int k1 = k % R1, rest = k / R1;
+        const int k2 = rest % R2, k3 = rest / R2;
+        return slot_of<R2, R3>(k1 * MM + k2 * R3 + k3);
+    }
+
+    template <typename OP>
+    NB2_HD static T apply_epi(const OP& e, const Geom& g, T h, long long k0, long long k1, long long k2,
+                              long long item, long long idx, double& acc) {
+        T v = h * amp_factor(e, g, k0, k1, k2, item);
+        if (e.mul) v *= ld_stream(e.mul + idx);
+        v += e.add_scalar;
+        if (e.add) v += ld_stream(e.add + idx);
+        if (e.dot) acc += double(ld_stream(e.dot + idx)) * double(v);
+        return v;
+    }
+
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
+        double* red = reinterpret_cast<double*>(smem_raw + size_t(2 * p.G) * PITCH * sizeof(cplx<T>));
+        const int nslots = 2 * p.G;
+        if (PH == 0) {
+            const int nb = nslots * MM;
+            int prev_s = -1;
+            RowSlot rs{};
+            for (int b = tid; b < nb; b += nthreads) {
+                const int r = b % MM, s = b / MM;
+                if (s != prev_s) {
+                    rs = slot_info(p, bid, s);
+                    prev_s = s;
+                }
+                if (!rs.valid) continue;
+                const cplx<T>* src = p.in + rs.row * M + r;
+                cplx<T> x[R1];
+                NB2_UNROLL
+                for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + n1 * MM);
+                if (p.has_pro) {
+                    const long long N0N1 = 1ll << (p.g.logN0 + p.g.logN1);
+                    const long long rowitem = rs.row & (N0N1 - 1);
+                    const long long f01 = sq_mirror(rs.k0, p.g.logN0) + sq_mirror(rs.k1, p.g.logN1);
+                    NB2_UNROLL
+                    for (int n1 = 0; n1 < R1; ++n1) {
+                        const long long m = r + n1 * MM;
+                        T ae, ao;
+                        if (p.pro.amp_mode == 1) {
+                            ae = ld_ro(p.pro.amp + f01 + sq_mirror(2 * m, p.g.logM + 1)) * p.pro.scale;
+                            ao = ld_ro(p.pro.amp + f01 + sq_mirror(2 * m + 1, p.g.logM + 1)) * p.pro.scale;
+                        } else if (p.pro.amp_mode == 2) {
+                            const cplx<T> f =
+                                ldc_stream(reinterpret_cast<const cplx<T>*>(p.pro.amp) + rowitem * M + m);
+                            ae = f.re * p.pro.scale;
+                            ao = f.im * p.pro.scale;
+                        } else {
+                            ae = ao = p.pro.scale;
+                        }
+                        x[n1].re *= ae;
+                        x[n1].im *= ao;
+                    }
+                }
+                fft_reg<R1, true>(x);
+                cplx<T>* dst = smem + s * PITCH;
+                NB2_UNROLL
+                for (int k1 = 0; k1 < R1; ++k1) {
+                    cplx<T> v = x[brev<R1>(k1)];
+                    // W_M^(r k1) = W_2M^(2 r k1)
+                    if (MM > 1 && k1 != 0) v = v * ldc_ro(p.tw + 2 * r * k1);
+                    dst[slot_of<R2, R3>(k1 * MM + r)] = v;
+                }
+            }
+        } else if (PH == 1) {
+            if (R2 > 1) {
+                const int nb = nslots * R1 * R3;
+                for (int b = tid; b < nb; b += nthreads) {
+                    const int n3 = b % R3, k1 = (b / R3) % R1, s = b / (R3 * R1);
+                    cplx<T>* row = smem + s * PITCH;
+                    cplx<T> x[R2];
+                    NB2_UNROLL
+                    for (int n2 = 0; n2 < R2; ++n2) x[n2] = row[slot_of<R2, R3>(k1 * MM + n2 * R3 + n3)];
+                    fft_reg<R2, true>(x);
+                    NB2_UNROLL
+                    for (int k2 = 0; k2 < R2; ++k2) {
+                        cplx<T> v = x[brev<R2>(k2)];
+                        // W_MM^(n3 k2) = W_2M^(2 R1 n3 k2)
+                        if (k2 != 0) v = v * ldc_ro(p.tw + 2 * R1 * n3 * k2);
+                        row[slot_of<R2, R3>(k1 * MM + k2 * R3 + n3)] = v;
+                    }
+                }
+            }
+        } else if (PH == 2) {
+            if (MM > 1) {
+                const int nb = nslots * R1 * R2;
+                for (int b = tid; b < nb; b += nthreads) {
+                    const int k2 = b % R2, k1 = (b / R2) % R1, s = b / (R2 * R1);
+                    cplx<T>* row = smem + s * PITCH;
+                    cplx<T> x[R3];
+                    NB2_UNROLL
+                    for (int n3 = 0; n3 < R3; ++n3) x[n3] = row[slot_of<R2, R3>(k1 * MM + k2 * R3 + n3)];
+                    fft_reg<R3, true>(x);
+                    NB2_UNROLL
+                    for (int k3 = 0; k3 < R3; ++k3) row[slot_of<R2, R3>(k1 * MM + k2 * R3 + k3)] = x[brev<R3>(k3)];
+                }
+            }
+        } else if (PH == 3) {
+            // untangle + Hartley combine + epilogue
+            double acc = 0.0;
+            const int nb = nslots * M;
+            const long long itemrows = 1ll << (p.g.logN0 + p.g.logN1);
+            const T sgn = p.conv == NB2_CANONICAL ? T(-1) : T(1);
+            int prev_s = -1;
+            RowSlot rs{};
+            for (int b = tid; b < nb; b += nthreads) {
+                const int k = b % M, s = b / M;
+                if (s != prev_s) {
+                    rs = slot_info(p, bid, s);
+                    prev_s = s;
+                }
+                if (!rs.valid || rs.dup) continue;
+                const cplx<T> a = smem[s * PITCH + slot_of_k(k)];
+                const cplx<T> bb = conj(smem[(s ^ 1) * PITCH + slot_of_k((M - k) & (M - 1))]);
+                const cplx<T> E = a + bb;              // 2 * even-sample spectrum
+                const cplx<T> O = mul_mi(a - bb);      // 2 * odd-sample spectrum
+                const cplx<T> WO = ldc_ro(p.tw + k) * O;
+                const cplx<T> F1 = E + WO, F2 = E - WO;  // 2 F[k], 2 F[k + M]
+                const T h1 = T(0.5) * (F1.re + sgn * F1.im), h2 = T(0.5) * (F2.re + sgn * F2.im);
+                const long long idx = rs.row * (2 * M) + k;
+                const long long item = (rs.row & (itemrows - 1)) * (2 * M) + k;
+                const T o1 = apply_epi(p.epi, p.g, h1, rs.k0, rs.k1, k, item, idx, acc);
+                const T o2 = apply_epi(p.epi, p.g, h2, rs.k0, rs.k1, k + M, item + M, idx + M, acc);
+                st_stream(p.out + idx, o1);
+                st_stream(p.out + idx + M, o2);
+            }
+            if (p.epi.dot) red[tid] = acc;
+        } else if (PH == 4) {
+            if (p.epi.dot && tid < 32) {
+                double s = 0.0;
+                for (int j = tid; j < nthreads; j += 32) s += red[j];
+#if defined(__CUDA_ARCH__)
+                NB2_UNROLL
+                for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+                if (tid == 0) p.epi.dot_partials[bid] = s;
+#else
+                red[tid] = s;
+#endif
+            }
+        } else {
+#if !defined(__CUDA_ARCH__)
+            if (p.epi.dot && tid == 0) {
+                // same pairing tree as the shuffle reduction above
+                double v[32];
+                for (int j = 0; j < 32; ++j) v[j] = j < nthreads ? red[j] : 0.0;
+                for (int off = 16; off > 0; off >>= 1)
+                    for (int j = 0; j < off; ++j) v[j] += v[j + off];
+                p.epi.dot_partials[bid] = v[0];
+            }
+#endif
+        }
+    }
+};
+
+}  // namespace nb2

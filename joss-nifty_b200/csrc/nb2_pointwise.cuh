@@ -1,0 +1,66 @@
+// niftyb200 -- pointwise prologue / epilogue operators fused into the FFT passes.
+//
+// The correlated-field hot tail (reference: src/library/correlated_fields.py:801-818,
+// src/re/correlated_field.py:690-693) multiplies the harmonic-space excitation by the
+// amplitude gathered through the mode-length index (PowerDistributor,
+// src/operators/distributors.py:114-119) before the Hartley transform, and scales by the
+// harmonic volume factor / adds the offset after it.  Here these ride on the first load and
+// the last store of the transform.
+//
+// The reference's int64 `pindex` array (src/domains/power_space.py:170-198) is replaced, for
+// isotropic grids, by a table indexed with the integer squared mode length
+//   ksq = sum_j min(k_j, N_j - k_j)^2        (src/domains/rg_space.py:105-116,130-141)
+// (amp_mode 1); anything else uses a precomputed full-size factor field (amp_mode 2).
+#pragma once
+
+#include "nb2_common.cuh"
+
+namespace nb2 {
+
+template <typename T>
+struct PointOp {
+    int amp_mode;        // 0: none, 1: table[ksq], 2: full-size field (one batch item, broadcast over batch)
+    const T* amp;        // table or field
+    T scale;             // multiplies the value (volume factor, azm, ...)
+    const T* mul;        // optional element-wise multiplier (full array incl. batch), epilogue only
+    const T* add;        // optional element-wise addend, epilogue only
+    T add_scalar;        // epilogue only (offset_mean)
+    const T* dot;        // optional: accumulate sum(dot[i] * out[i]) in fp64, epilogue only
+    double* dot_partials;  // one slot per CTA (deterministic two-level reduction)
+};
+
+// Geometry of the (batch, N0, N1, N2) real array; N2 = 2*M, all powers of two.
+struct Geom {
+    int logN0, logN1, logM;   // log2 of N0, N1 and M = N2/2
+    long long batch;
+};
+
+NB2_HD long long sq_mirror(long long k, int logN) {
+    const long long N = 1ll << logN;
+    const long long km = k < N - k ? k : N - k;
+    return km * km;
+}
+
+// complex linear index -> (k0, k1, m)
+NB2_HD void decode(const Geom& g, long long lin, long long& k0, long long& k1, long long& m) {
+    m = lin & ((1ll << g.logM) - 1);
+    lin >>= g.logM;
+    k1 = lin & ((1ll << g.logN1) - 1);
+    lin >>= g.logN1;
+    k0 = lin & ((1ll << g.logN0) - 1);
+}
+
+// amplitude factor for the real element with coordinates (k0, k1, k2); `item` is the real
+// linear index inside one batch item (used by amp_mode 2).
+template <typename T>
+NB2_HD T amp_factor(const PointOp<T>& op, const Geom& g, long long k0, long long k1, long long k2,
+                    long long item) {
+    if (op.amp_mode == 1) {
+        const long long ksq = sq_mirror(k0, g.logN0) + sq_mirror(k1, g.logN1) + sq_mirror(k2, g.logM + 1);
+        return ld_ro(op.amp + ksq) * op.scale;
+    }
+    if (op.amp_mode == 2) return ld_ro(op.amp + item) * op.scale;
+    return op.scale;
+}
+
+}  // namespace nb2

@@ -1,0 +1,251 @@
+// niftyb200 -- streaming vector kernels: fused conjugate-gradient updates with
+// deterministic fp64 dot-product reductions, and the element-wise helpers of the
+// generic (non power-of-two) path.
+//
+// Reference recurrences: ConjugateGradient.__call__ (src/minimization/conjugate_gradient.py:
+// 84-124), QuadraticEnergy (src/minimization/quadratic_energy.py:35-37), re `_cg`
+// (src/re/conjugate_gradient.py:146-205).  Per iteration the reference sweeps the vectors
+// ~10 times (every Field op allocates); here one kernel does  x -= a d, r -= a q  and the
+// three sums  r.r, x.r, x.b  from which both stacks' energies follow:
+//   numpy stack  E = 0.5 x.(r + b) - b.x      re stack  E = ((r - j)/2).x
+//
+// Reductions: per-thread fp64 accumulators -> warp shuffle -> one partial per CTA ->
+// a single-CTA final pass.  No floating-point atomics, so results are bit-reproducible
+// run to run (the property the reference's pairwise-tree allreduce provides,
+// src/utilities.py:331-390).
+#pragma once
+
+#include "nb2_common.cuh"
+#include "nb2_pointwise.cuh"
+
+namespace nb2 {
+
+// Block reduction of NV fp64 values per thread.  `red` holds NV * nthreads doubles.
+// phase A (end of the accumulating phase): red[v * nthreads + tid] = acc[v]
+// phase B: warp 0 folds, phase C: (emulator only) final tree.
+template <int NV>
+NB2_HD void block_reduce_B(double* red, int tid, int nthreads, double* out /* NV values */) {
+    if (tid < 32) {
+        for (int v = 0; v < NV; ++v) {
+            double s = 0.0;
+            for (int j = tid; j < nthreads; j += 32) s += red[v * nthreads + j];
+#if defined(__CUDA_ARCH__)
+            NB2_UNROLL
+            for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+            if (tid == 0) out[v] = s;
+#else
+            red[v * nthreads + tid] = s;
+#endif
+        }
+    }
+}
+template <int NV>
+NB2_HD void block_reduce_C(double* red, int tid, int nthreads, double* out) {
+#if !defined(__CUDA_ARCH__)
+    if (tid == 0) {
+        for (int v = 0; v < NV; ++v) {
+            double t[32];
+            for (int j = 0; j < 32; ++j) t[j] = j < nthreads ? red[v * nthreads + j] : 0.0;
+            for (int off = 16; off > 0; off >>= 1)
+                for (int j = 0; j < off; ++j) t[j] += t[j + off];
+            out[v] = t[0];
+        }
+    }
+#endif
+}
+
+// ---------------------------------------------------------------- fused CG update
+// mode 0:  x -= alpha d ; r -= alpha q ; sums          (conjugate_gradient.py:100-101)
+// mode 1:  r  = q - b ; sums   (exact residual after a reset step, q = A x; :103-105)
+// sums[0] = r.r, sums[1] = x.r, sums[2] = x.b      (after the update)
+template <typename T>
+struct CgUpdate {
+    static constexpr int NPHASES = 3;
+    static constexpr int MAX_THREADS = 256;
+    struct Params {
+        T* x;
+        T* r;
+        const T* d;
+        const T* q;
+        const T* b;
+        T alpha;
+        int mode;
+        long long n;
+        double* partials;  // 3 per CTA
+        long long nctas;
+    };
+    static size_t smem_bytes(int nthreads) { return size_t(3) * nthreads * sizeof(double); }
+    NB2_HDC static bool enabled(int) { return true; }
+
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        double* red = reinterpret_cast<double*>(smem_raw);
+        if (PH == 0) {
+            double s0 = 0, s1 = 0, s2 = 0;
+            const long long stride = p.nctas * nthreads;
+            for (long long i = bid * nthreads + tid; i < p.n; i += stride) {
+                T xv, rv;
+                if (p.mode == 0) {
+                    xv = ld_stream(p.x + i) - p.alpha * ld_stream(p.d + i);
+                    rv = ld_stream(p.r + i) - p.alpha * ld_stream(p.q + i);
+                    st_stream(p.x + i, xv);
+                } else {
+                    xv = ld_stream(p.x + i);
+                    rv = ld_stream(p.q + i) - ld_stream(p.b + i);
+                }
+                st_stream(p.r + i, rv);
+                const T bv = ld_stream(p.b + i);
+                s0 += double(rv) * double(rv);
+                s1 += double(xv) * double(rv);
+                s2 += double(xv) * double(bv);
+            }
+            red[tid] = s0;
+            red[nthreads + tid] = s1;
+            red[2 * nthreads + tid] = s2;
+        } else if (PH == 1) {
+            block_reduce_B<3>(red, tid, nthreads, p.partials + 3 * bid);
+        } else {
+            block_reduce_C<3>(red, tid, nthreads, p.partials + 3 * bid);
+        }
+    }
+};
+
+// ---------------------------------------------------------------- y = a*x + b*y  (+ optional dot(y_new, z))
+// covers  d = beta d + r  (conjugate_gradient.py:124),  x -= alpha d  and plain copies/scales.
+template <typename T>
+struct Axpby {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 256;
+    struct Params {
+        const T* x;
+        T* y;
+        T a, b;
+        long long n;
+        long long nctas;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+        const long long stride = p.nctas * nthreads;
+        for (long long i = bid * nthreads + tid; i < p.n; i += stride) {
+            const T xv = ld_stream(p.x + i);
+            const T yv = p.b == T(0) ? T(0) : p.b * ld_stream(p.y + i);
+            st_stream(p.y + i, p.a * xv + yv);
+        }
+    }
+};
+
+// ---------------------------------------------------------------- dot(a, b) partials (a, b real; complex data are passed as 2n reals)
+template <typename T>
+struct Dot {
+    static constexpr int NPHASES = 3;
+    static constexpr int MAX_THREADS = 256;
+    struct Params {
+        const T* a;
+        const T* b;
+        long long n;
+        double* partials;  // 1 per CTA
+        long long nctas;
+    };
+    static size_t smem_bytes(int nthreads) { return size_t(nthreads) * sizeof(double); }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        double* red = reinterpret_cast<double*>(smem_raw);
+        if (PH == 0) {
+            double s = 0;
+            const long long stride = p.nctas * nthreads;
+            for (long long i = bid * nthreads + tid; i < p.n; i += stride)
+                s += double(ld_stream(p.a + i)) * double(ld_stream(p.b + i));
+            red[tid] = s;
+        } else if (PH == 1) {
+            block_reduce_B<1>(red, tid, nthreads, p.partials + bid);
+        } else {
+            block_reduce_C<1>(red, tid, nthreads, p.partials + bid);
+        }
+    }
+};
+
+// ---------------------------------------------------------------- final reduction of per-CTA partials (single CTA)
+// out[v] = sum_c partials[c * nv + v], fixed order.
+struct FinalReduce {
+    static constexpr int NPHASES = 3;
+    static constexpr int MAX_THREADS = 256;
+    struct Params {
+        const double* partials;
+        long long nparts;
+        int nv;  // <= 4
+        double* out;
+    };
+    static size_t smem_bytes(int nthreads) { return size_t(4) * nthreads * sizeof(double); }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long, int tid, int nthreads, char* smem_raw) {
+        double* red = reinterpret_cast<double*>(smem_raw);
+        if (PH == 0) {
+            for (int v = 0; v < 4; ++v) {
+                double s = 0;
+                if (v < p.nv)
+                    for (long long c = tid; c < p.nparts; c += nthreads) s += p.partials[c * p.nv + v];
+                red[v * nthreads + tid] = s;
+            }
+        } else if (PH == 1) {
+            double tmp[4];
+            block_reduce_B<4>(red, tid, nthreads, tmp);
+#if defined(__CUDA_ARCH__)
+            if (tid == 0)
+                for (int v = 0; v < p.nv; ++v) p.out[v] = tmp[v];
+#endif
+        } else {
+#if !defined(__CUDA_ARCH__)
+            double tmp[4];
+            block_reduce_C<4>(red, tid, nthreads, tmp);
+            if (tid == 0)
+                for (int v = 0; v < p.nv; ++v) p.out[v] = tmp[v];
+#endif
+        }
+    }
+};
+
+// ---------------------------------------------------------------- generic element-wise op (generic path pro/epilogue)
+// out[i] = in[i] * amp * [mul[i]] + add_scalar + [add[i]] ; optional dot partials.
+// Only amp_mode 0 and 2 are meaningful here (no coordinates).
+template <typename T>
+struct Eltwise {
+    static constexpr int NPHASES = 3;
+    static constexpr int MAX_THREADS = 256;
+    struct Params {
+        const T* in;
+        T* out;
+        PointOp<T> op;
+        long long n, item;  // item: elements of one batch item (amp field size)
+        long long nctas;
+    };
+    static size_t smem_bytes(int nthreads) { return size_t(nthreads) * sizeof(double); }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        double* red = reinterpret_cast<double*>(smem_raw);
+        if (PH == 0) {
+            double s = 0;
+            const long long stride = p.nctas * nthreads;
+            for (long long i = bid * nthreads + tid; i < p.n; i += stride) {
+                T v = p.in[i] * p.op.scale;
+                if (p.op.amp_mode == 2) v *= p.op.amp[i % p.item];
+                if (p.op.mul) v *= p.op.mul[i];
+                v += p.op.add_scalar;
+                if (p.op.add) v += p.op.add[i];
+                if (p.op.dot) s += double(p.op.dot[i]) * double(v);
+                p.out[i] = v;
+            }
+            red[tid] = s;
+        } else if (PH == 1) {
+            if (p.op.dot) block_reduce_B<1>(red, tid, nthreads, p.op.dot_partials + bid);
+        } else {
+            if (p.op.dot) block_reduce_C<1>(red, tid, nthreads, p.op.dot_partials + bid);
+        }
+    }
+};
+
+}  // namespace nb2

@@ -1,0 +1,100 @@
+"""ctypes binding of ``libniftyb200.so`` (C ABI: ``include/niftyb200.h``).
+
+There is no CPU fallback: if the CUDA library is missing or cannot be loaded, every
+entry point of this package raises.  (The CPU-only unit tests inject the sequential
+thread *emulator* build of the same sources through :func:`use_library_for_testing`;
+that build lives in ``tests/emu`` and is never shipped or loaded by this package on
+its own.)
+"""
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_double, c_int, c_int32, c_int64, c_void_p
+
+F32, F64 = 0, 1
+NONCANONICAL, CANONICAL = 0, 1
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+DEFAULT_PATH = os.path.join(_HERE, "libniftyb200.so")
+
+
+class PointOp(ctypes.Structure):
+    """``nb2_pointop`` (include/niftyb200.h)."""
+
+    _fields_ = [
+        ("amp_mode", c_int32),
+        ("reserved", c_int32),
+        ("amp", c_void_p),
+        ("scale", c_double),
+        ("mul", c_void_p),
+        ("add", c_void_p),
+        ("add_scalar", c_double),
+        ("dot", c_void_p),
+        ("dot_out", c_void_p),
+    ]
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+class Library:
+    """Loaded shared library with typed entry points."""
+
+    SYMBOLS = {
+        "nb2_version": (c_int, []),
+        "nb2_last_error": (c_char_p, []),
+        "nb2_sm_count": (c_int, []),
+        "nb2_plan_create": (c_int, [c_int, POINTER(c_int64), c_int, POINTER(c_int32), c_int, POINTER(c_void_p)]),
+        "nb2_plan_destroy": (c_int, [c_void_p]),
+        "nb2_plan_is_fast": (c_int, [c_void_p]),
+        "nb2_plan_ksq_size": (c_int64, [c_void_p]),
+        "nb2_hartley": (c_int, [c_void_p, c_void_p, c_void_p, c_int, POINTER(PointOp), POINTER(PointOp), c_void_p]),
+        "nb2_c2c": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double, c_void_p]),
+        "nb2_vdot": (c_int, [c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
+        "nb2_axpby": (c_int, [c_int, c_int64, c_double, c_void_p, c_double, c_void_p, c_void_p]),
+        "nb2_cg_update": (c_int, [c_int, c_int64, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p]),
+        "nb2_hartley_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double]),
+        "nb2_c2c_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double]),
+    }
+
+    def __init__(self, path, device_type):
+        if not os.path.exists(path):
+            raise NativeError(
+                f"niftyb200: native library not found at {path}; build it with "
+                "`python -c 'import __graft_entry__ as g; g.build()'` (there is no CPU fallback)")
+        self.path = path
+        self.device_type = device_type  # torch device type the pointers must live on
+        self.cdll = ctypes.CDLL(path)
+        for name, (res, args) in self.SYMBOLS.items():
+            fn = getattr(self.cdll, name)
+            fn.restype = res
+            fn.argtypes = args
+            setattr(self, name, fn)
+
+    def check(self, rc, what):
+        if rc != 0:
+            msg = self.nb2_last_error()
+            raise NativeError(f"niftyb200: {what} failed (code {rc}): {msg.decode() if msg else ''}")
+
+
+_lib = None
+
+
+def get():
+    """Return the CUDA library, loading it on first use.  Raises if unavailable."""
+    global _lib
+    if _lib is None:
+        import torch
+        if not torch.cuda.is_available():
+            raise NativeError("niftyb200: no CUDA device available (there is no CPU fallback)")
+        _lib = Library(DEFAULT_PATH, "cuda")
+    return _lib
+
+
+def use_library_for_testing(path, device_type="cpu"):
+    """TESTS ONLY: route calls to another build of the same C ABI (the emulator)."""
+    global _lib
+    _lib = Library(path, device_type) if path is not None else None
+    return _lib
