@@ -2,23 +2,13 @@
 //
 // Built with nvcc for sm_100a into libniftyb200.so.  With -DNB2_EMU (host compiler) the
 // same file builds the sequential thread emulator used by the CPU-only index tests.
-#include <algorithm>
-#include <cmath>
-#include <new>
-
-#include "../../include/niftyb200.h"
 #include "nb2_generic.cuh"
-#include "nb2_launch.cuh"
-#include "nb2_passes.cuh"
+#include "nb2_plan.h"
 #include "nb2_vector.cuh"
 
 using namespace nb2;
 
 namespace {
-
-constexpr int kMaxDim = 8;
-constexpr size_t kSmemLimit = 200 * 1024;
-constexpr int kVecThreads = 256;
 
 struct Ctx {
     double* partials = nullptr;  // reduction scratch for the vector kernels
@@ -46,25 +36,36 @@ long long vec_grid(long long n) {
 
 }  // namespace
 
-struct nb2_plan {
-    int ndim = 0, naxes = 0, dtype = 0;
-    long long shape[kMaxDim] = {0};
-    int axes[kMaxDim] = {0};
-    long long total = 1;
-    bool fast = false;
-    // fast path geometry: (batch, N0, N1, N2)
-    Geom g{};
-    void* tw0 = nullptr;  // strided axis-0 table (N0 entries)
-    void* tw1 = nullptr;  // strided axis-1 table (N1 entries)
-    void* twr = nullptr;  // row table (N2 entries)
-    double* partials = nullptr;
-    long long npartials = 0;
-    // generic path
-    void* roots[kMaxDim] = {nullptr};  // cplx<double>[n] per transformed axis
-    void* work0 = nullptr;
-    void* work1 = nullptr;  // complex scratch
-};
 
+namespace nb2 {
+PlanDims plan_dims(int logn) {
+    switch (logn) {
+        case 1: return {2, 1, 1};
+        case 2: return {4, 1, 1};
+        case 3: return {8, 1, 1};
+        case 4: return {16, 1, 1};
+        case 5: return {32, 1, 1};
+        case 6: return {8, 1, 8};
+        case 7: return {16, 1, 8};
+        case 8: return {16, 1, 16};
+        case 9: return {32, 1, 16};
+        case 10: return {32, 1, 32};
+        case 11: return {16, 8, 16};
+        case 12: return {16, 16, 16};
+        case 13: return {32, 16, 16};
+        default: return {0, 0, 0};
+    }
+}
+int pitch_of(int logn) {
+    const PlanDims d = plan_dims(logn);
+    if (!d.r1) return 0;
+    return d.r1 * d.r2 * d.r3 + d.r1 * d.r2 + (d.r2 > 1 ? d.r1 : 0);
+}
+int launch_final_reduce(const double* partials, long long nparts, int nv, double* out, rt_stream st) {
+    FinalReduce::Params fp{partials, nparts, nv, out};
+    return rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
+}
+}  // namespace nb2
 namespace {
 
 template <typename T>
@@ -79,178 +80,6 @@ int upload_table(void** dev, long long n, long long denom) {
     }
     if (rt_malloc(dev, n * sizeof(cplx<T>))) return NB2_ERR_CUDA;
     return rt_h2d(*dev, h.data(), n * sizeof(cplx<T>), nullptr);
-}
-
-// ---------------------------------------------------------------- radix plans
-// log2(n) -> (R1, R2, R3)
-#define NB2_PLAN_SWITCH(LOGN, CALL)                 \
-    switch (LOGN) {                                 \
-        case 1: CALL(2, 1, 1); break;               \
-        case 2: CALL(4, 1, 1); break;               \
-        case 3: CALL(8, 1, 1); break;               \
-        case 4: CALL(16, 1, 1); break;              \
-        case 5: CALL(32, 1, 1); break;              \
-        case 6: CALL(8, 1, 8); break;               \
-        case 7: CALL(16, 1, 8); break;              \
-        case 8: CALL(16, 1, 16); break;             \
-        case 9: CALL(32, 1, 16); break;             \
-        case 10: CALL(32, 1, 32); break;            \
-        case 11: CALL(16, 8, 16); break;            \
-        case 12: CALL(16, 16, 16); break;           \
-        case 13: CALL(32, 16, 16); break;           \
-        default: rc = NB2_ERR_UNSUPPORTED; break;   \
-    }
-
-struct PlanDims { int r1, r2, r3; };
-PlanDims plan_dims(int logn) {
-    int rc = 0;
-    PlanDims d{0, 0, 0};
-#define NB2_GETDIMS(A, B, C) d = PlanDims{A, B, C}
-    NB2_PLAN_SWITCH(logn, NB2_GETDIMS)
-#undef NB2_GETDIMS
-    (void)rc;
-    return d;
-}
-int pitch_of(int logn) {
-    const PlanDims d = plan_dims(logn);
-    if (!d.r1) return 0;
-    return d.r1 * d.r2 * d.r3 + d.r1 * d.r2 + (d.r2 > 1 ? d.r1 : 0);
-}
-
-template <typename T>
-PointOp<T> to_pointop(const nb2_pointop* o, double* partials) {
-    PointOp<T> r;
-    r.amp_mode = o ? o->amp_mode : 0;
-    r.amp = o ? (const T*)o->amp : nullptr;
-    r.scale = o ? (T)o->scale : T(1);
-    r.mul = o ? (const T*)o->mul : nullptr;
-    r.add = o ? (const T*)o->add : nullptr;
-    r.add_scalar = o ? (T)o->add_scalar : T(0);
-    r.dot = o ? (const T*)o->dot : nullptr;
-    r.dot_partials = partials;
-    return r;
-}
-
-int round32(long long v) { return (int)std::max(32ll, ((v + 31) / 32) * 32); }
-
-// choose tile width for a strided pass over rows of `inner` complex elements
-template <typename T>
-int choose_logw(int logn, long long inner) {
-    const size_t col = size_t(pitch_of(logn)) * sizeof(cplx<T>);  // bytes per tile column
-    int logw = 0;
-    while ((1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= 72 * 1024) ++logw;
-    // prefer at least 64-byte row segments when they fit in shared memory
-    const int want = ilog2(64 / sizeof(cplx<T>));
-    while (logw < want && (1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= kSmemLimit) ++logw;
-    return logw;
-}
-
-template <typename T>
-int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st) {
-    const int logn = axis == 0 ? pl->g.logN0 : pl->g.logN1;
-    if (logn == 0) {  // nothing to transform; still apply prologue / copy
-        return NB2_ERR_ARG;
-    }
-    const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
-    const long long outer = axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
-    const int logw = choose_logw<T>(logn, inner);
-    int rc = 0;
-#define NB2_RUN_STRIDED(A, B, C)                                                              \
-    {                                                                                         \
-        typedef StridedPass<T, A, B, C> K;                                                    \
-        typename K::Params p;                                                                 \
-        p.in = (const cplx<T>*)in;                                                            \
-        p.out = (cplx<T>*)out;                                                                \
-        p.tw = (const cplx<T>*)(axis == 0 ? pl->tw0 : pl->tw1);                               \
-        p.inner = inner;                                                                      \
-        p.logw = logw;                                                                        \
-        p.tiles_per_outer = inner >> logw;                                                    \
-        p.axis = axis;                                                                        \
-        p.has_pro = pro ? 1 : 0;                                                              \
-        p.pro = to_pointop<T>(pro, nullptr);                                                  \
-        p.g = pl->g;                                                                          \
-        const size_t smem = K::smem_bytes(logw);                                              \
-        if (smem > kSmemLimit) {                                                              \
-            rc = NB2_ERR_UNSUPPORTED;                                                         \
-        } else {                                                                              \
-            const long long nb1 = (long long)(B * C) << logw;                                 \
-            const int maxt = K::MAX_THREADS;                                \
-            const int nthreads = std::min(maxt, round32(nb1));                                \
-            rc = rt_launch<K>(outer * p.tiles_per_outer, nthreads, smem, st, p);              \
-        }                                                                                     \
-    }
-    NB2_PLAN_SWITCH(logn, NB2_RUN_STRIDED)
-#undef NB2_RUN_STRIDED
-    return rc;
-}
-
-template <typename T>
-int choose_G(int logm, long long Q) {
-    const size_t row = size_t(pitch_of(logm)) * sizeof(cplx<T>);
-    int G = 1;
-    while (G < 16 && 2 * G <= Q && size_t(4 * G) * row <= 72 * 1024) G *= 2;
-    return G;
-}
-
-template <typename T>
-int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
-             rt_stream st) {
-    const int logm = pl->g.logM;
-    const RowPairs rp = row_pairs(pl->g);
-    const int G = choose_G<T>(logm, rp.Q);
-    const long long ctas_per_item = (rp.Q + G - 1) / G;
-    const long long grid = ctas_per_item * pl->g.batch;
-    const bool want_dot = epi && epi->dot;
-    if (want_dot) {
-        if (!epi->dot_out) {
-            last_error() = "nb2_pointop.dot set without dot_out";
-            return NB2_ERR_ARG;
-        }
-        if (grid > pl->npartials) {
-            rt_sync(st);
-            rt_free(pl->partials);
-            pl->partials = nullptr;
-            pl->npartials = 0;
-            if (rt_malloc((void**)&pl->partials, grid * sizeof(double))) return NB2_ERR_CUDA;
-            pl->npartials = grid;
-        }
-    }
-    int rc = 0;
-#define NB2_RUN_ROWS(A, B, C)                                                                 \
-    {                                                                                         \
-        typedef RowPass<T, A, B, C> K;                                                        \
-        typename K::Params p;                                                                 \
-        p.in = (const cplx<T>*)in;                                                            \
-        p.out = (T*)out;                                                                      \
-        p.tw = (const cplx<T>*)pl->twr;                                                       \
-        p.g = pl->g;                                                                          \
-        p.ctas_per_item = ctas_per_item;                                                      \
-        p.G = G;                                                                              \
-        p.conv = conv;                                                                        \
-        p.has_pro = pro ? 1 : 0;                                                              \
-        p.pro = to_pointop<T>(pro, nullptr);                                                  \
-        p.epi = to_pointop<T>(epi, pl->partials);                                             \
-        const long long nb1 = (long long)2 * G * B * C;                                       \
-        const int maxt = K::MAX_THREADS;                                    \
-        const int nthreads = std::min(maxt, round32(nb1));                                    \
-        const size_t smem = K::smem_bytes(G, nthreads);                                       \
-        if (smem > kSmemLimit)                                                                \
-            rc = NB2_ERR_UNSUPPORTED;                                                         \
-        else                                                                                  \
-            rc = rt_launch<K>(grid, nthreads, smem, st, p);                                   \
-    }
-    NB2_PLAN_SWITCH(logm, NB2_RUN_ROWS)
-#undef NB2_RUN_ROWS
-    if (rc) return rc;
-    if (want_dot) {
-        FinalReduce::Params fp;
-        fp.partials = pl->partials;
-        fp.nparts = grid;
-        fp.nv = 1;
-        fp.out = epi->dot_out;
-        rc = rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
-    }
-    return rc;
 }
 
 template <typename T>

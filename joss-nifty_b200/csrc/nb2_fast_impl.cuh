@@ -1,0 +1,146 @@
+// niftyb200 -- host-side dispatch of the two fast-path pass kernels (template definitions).
+#pragma once
+
+#include "nb2_passes.cuh"
+#include "nb2_plan.h"
+#include "nb2_vector.cuh"
+
+namespace nb2 {
+
+// ---------------------------------------------------------------- radix plans
+// log2(n) -> (R1, R2, R3)
+#define NB2_PLAN_SWITCH(LOGN, CALL)                 \
+    switch (LOGN) {                                 \
+        case 1: CALL(2, 1, 1); break;               \
+        case 2: CALL(4, 1, 1); break;               \
+        case 3: CALL(8, 1, 1); break;               \
+        case 4: CALL(16, 1, 1); break;              \
+        case 5: CALL(32, 1, 1); break;              \
+        case 6: CALL(8, 1, 8); break;               \
+        case 7: CALL(16, 1, 8); break;              \
+        case 8: CALL(16, 1, 16); break;             \
+        case 9: CALL(32, 1, 16); break;             \
+        case 10: CALL(32, 1, 32); break;            \
+        case 11: CALL(16, 8, 16); break;            \
+        case 12: CALL(16, 16, 16); break;           \
+        case 13: CALL(32, 16, 16); break;           \
+        default: rc = NB2_ERR_UNSUPPORTED; break;   \
+    }
+
+// choose tile width for a strided pass over rows of `inner` complex elements
+template <typename T>
+int choose_logw(int logn, long long inner) {
+    const size_t col = size_t(pitch_of(logn)) * sizeof(cplx<T>);  // bytes per tile column
+    int logw = 0;
+    while ((1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= 72 * 1024) ++logw;
+    // prefer at least 64-byte row segments when they fit in shared memory
+    const int want = ilog2(64 / sizeof(cplx<T>));
+    while (logw < want && (1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= kSmemLimit) ++logw;
+    return logw;
+}
+
+template <typename T>
+int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st) {
+    const int logn = axis == 0 ? pl->g.logN0 : pl->g.logN1;
+    if (logn == 0) {  // nothing to transform; still apply prologue / copy
+        return NB2_ERR_ARG;
+    }
+    const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
+    const long long outer = axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
+    const int logw = choose_logw<T>(logn, inner);
+    int rc = 0;
+#define NB2_RUN_STRIDED(A, B, C)                                                              \
+    {                                                                                         \
+        typedef StridedPass<T, A, B, C> K;                                                    \
+        typename K::Params p;                                                                 \
+        p.in = (const cplx<T>*)in;                                                            \
+        p.out = (cplx<T>*)out;                                                                \
+        p.tw = (const cplx<T>*)(axis == 0 ? pl->tw0 : pl->tw1);                               \
+        p.inner = inner;                                                                      \
+        p.logw = logw;                                                                        \
+        p.tiles_per_outer = inner >> logw;                                                    \
+        p.axis = axis;                                                                        \
+        p.has_pro = pro ? 1 : 0;                                                              \
+        p.pro = to_pointop<T>(pro, nullptr);                                                  \
+        p.g = pl->g;                                                                          \
+        const size_t smem = K::smem_bytes(logw);                                              \
+        if (smem > kSmemLimit) {                                                              \
+            rc = NB2_ERR_UNSUPPORTED;                                                         \
+        } else {                                                                              \
+            const long long nb1 = (long long)(B * C) << logw;                                 \
+            const int maxt = K::MAX_THREADS;                                \
+            const int nthreads = std::min(maxt, round32(nb1));                                \
+            rc = rt_launch<K>(outer * p.tiles_per_outer, nthreads, smem, st, p);              \
+        }                                                                                     \
+    }
+    NB2_PLAN_SWITCH(logn, NB2_RUN_STRIDED)
+#undef NB2_RUN_STRIDED
+    return rc;
+}
+
+template <typename T>
+int choose_G(int logm, long long Q) {
+    const size_t row = size_t(pitch_of(logm)) * sizeof(cplx<T>);
+    int G = 1;
+    while (G < 16 && 2 * G <= Q && size_t(4 * G) * row <= 72 * 1024) G *= 2;
+    return G;
+}
+
+template <typename T>
+int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
+             rt_stream st) {
+    const int logm = pl->g.logM;
+    const RowPairs rp = row_pairs(pl->g);
+    const int G = choose_G<T>(logm, rp.Q);
+    const long long ctas_per_item = (rp.Q + G - 1) / G;
+    const long long grid = ctas_per_item * pl->g.batch;
+    const bool want_dot = epi && epi->dot;
+    if (want_dot) {
+        if (!epi->dot_out) {
+            last_error() = "nb2_pointop.dot set without dot_out";
+            return NB2_ERR_ARG;
+        }
+        if (grid > pl->npartials) {
+            rt_sync(st);
+            rt_free(pl->partials);
+            pl->partials = nullptr;
+            pl->npartials = 0;
+            if (rt_malloc((void**)&pl->partials, grid * sizeof(double))) return NB2_ERR_CUDA;
+            pl->npartials = grid;
+        }
+    }
+    int rc = 0;
+#define NB2_RUN_ROWS(A, B, C)                                                                 \
+    {                                                                                         \
+        typedef RowPass<T, A, B, C> K;                                                        \
+        typename K::Params p;                                                                 \
+        p.in = (const cplx<T>*)in;                                                            \
+        p.out = (T*)out;                                                                      \
+        p.tw = (const cplx<T>*)pl->twr;                                                       \
+        p.g = pl->g;                                                                          \
+        p.ctas_per_item = ctas_per_item;                                                      \
+        p.G = G;                                                                              \
+        p.conv = conv;                                                                        \
+        p.has_pro = pro ? 1 : 0;                                                              \
+        p.pro = to_pointop<T>(pro, nullptr);                                                  \
+        p.epi = to_pointop<T>(epi, pl->partials);                                             \
+        const long long nb1 = (long long)2 * G * B * C;                                       \
+        const int maxt = K::MAX_THREADS;                                    \
+        const int nthreads = std::min(maxt, round32(nb1));                                    \
+        const size_t smem = K::smem_bytes(G, nthreads);                                       \
+        if (smem > kSmemLimit)                                                                \
+            rc = NB2_ERR_UNSUPPORTED;                                                         \
+        else                                                                                  \
+            rc = rt_launch<K>(grid, nthreads, smem, st, p);                                   \
+    }
+    NB2_PLAN_SWITCH(logm, NB2_RUN_ROWS)
+#undef NB2_RUN_ROWS
+    if (rc) return rc;
+    if (want_dot) {
+        rc = launch_final_reduce(pl->partials, grid, 1, epi->dot_out, st);
+    }
+    return rc;
+}
+
+
+}  // namespace nb2

@@ -1,0 +1,67 @@
+// niftyb200 -- plan object and host-side helpers shared by the translation units.
+#pragma once
+
+#include <algorithm>
+#include <cmath>
+#include <new>
+
+#include "../../include/niftyb200.h"
+#include "nb2_launch.cuh"
+#include "nb2_pointwise.cuh"
+
+namespace nb2 {
+constexpr int kMaxDim = 8;
+constexpr size_t kSmemLimit = 200 * 1024;
+constexpr int kVecThreads = 256;
+}  // namespace nb2
+
+struct nb2_plan {
+    int ndim = 0, naxes = 0, dtype = 0;
+    long long shape[nb2::kMaxDim] = {0};
+    int axes[nb2::kMaxDim] = {0};
+    long long total = 1;
+    bool fast = false;
+    // fast path geometry: (batch, N0, N1, N2)
+    nb2::Geom g{};
+    void* tw0 = nullptr;  // strided axis-0 table (N0 entries)
+    void* tw1 = nullptr;  // strided axis-1 table (N1 entries)
+    void* twr = nullptr;  // row table (N2 entries)
+    double* partials = nullptr;
+    long long npartials = 0;
+    // generic path
+    void* roots[nb2::kMaxDim] = {nullptr};  // cplx<double>[n] per transformed axis
+    void* work0 = nullptr;
+    void* work1 = nullptr;  // complex scratch
+};
+
+
+namespace nb2 {
+
+struct PlanDims { int r1, r2, r3; };
+PlanDims plan_dims(int logn);
+int pitch_of(int logn);
+inline int round32(long long v) { return (int)std::max(32ll, ((v + 31) / 32) * 32); }
+
+template <typename T>
+PointOp<T> to_pointop(const nb2_pointop* o, double* partials) {
+    PointOp<T> r;
+    r.amp_mode = o ? o->amp_mode : 0;
+    r.amp = o ? (const T*)o->amp : nullptr;
+    r.scale = o ? (T)o->scale : T(1);
+    r.mul = o ? (const T*)o->mul : nullptr;
+    r.add = o ? (const T*)o->add : nullptr;
+    r.add_scalar = o ? (T)o->add_scalar : T(0);
+    r.dot = o ? (const T*)o->dot : nullptr;
+    r.dot_partials = partials;
+    return r;
+}
+
+// fast-path passes (explicitly instantiated for float and double in nb2_fast_*.cu)
+template <typename T>
+int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st);
+template <typename T>
+int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
+             rt_stream st);
+int launch_final_reduce(const double* partials, long long nparts, int nv, double* out, rt_stream st);
+
+}  // namespace nb2

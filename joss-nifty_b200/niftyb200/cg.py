@@ -1,0 +1,415 @@
+"""Conjugate-gradient solvers with fused device kernels.
+
+Two interfaces, matching the two reference stacks:
+
+* :class:`ConjugateGradient` + :class:`QuadraticEnergy` + iteration controllers -- numpy stack
+  (``/root/reference/src/minimization/conjugate_gradient.py:48-126``,
+  ``src/minimization/quadratic_energy.py:25-78``,
+  ``src/minimization/iteration_controllers.py:148-221,356-423``);
+* :func:`cg` / :func:`static_cg` -- NIFTy.re (``src/re/conjugate_gradient.py:77-216,219-389``).
+
+Vectors are device tensors.  Per iteration: one metric apply (the curvature ``d.q`` is fused
+into its last store when the operator offers ``apply_with_curvature``), ONE fused kernel for
+``x -= a d, r -= a q`` together with the sums ``r.r, x.r, x.b`` (fp64, deterministic), one
+kernel for ``d = b d + r``.  The stopping logic is evaluated on the host in fp64 from those
+three sums, line by line as in the reference, so iteration counts and status/info codes match.
+"""
+
+import time
+from collections import namedtuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from .transforms import _TORCH_REAL, _ptr, _stream, vdot_device
+
+CONVERGED, CONTINUE, ERROR = 0, 1, 2   # IterationController.{CONVERGED,CONTINUE,ERROR}
+N_RESET = 20                           # re/conjugate_gradient.py:18
+
+
+# ---------------------------------------------------------------- fused vector kernels
+class _Vec:
+    def __init__(self, like):
+        self.lib = _lib.get()
+        if like.dtype not in _TORCH_REAL:
+            raise TypeError("CG vectors must be float32 or float64 tensors")
+        self.code, self.n = _TORCH_REAL[like.dtype], like.numel()
+        self.sums = torch.zeros(3, dtype=torch.float64, device=like.device)
+
+    def update(self, mode, alpha, d, q, b, x, r):
+        """mode 0: x -= alpha d, r -= alpha q; mode 1: r = q - b.  Returns (r.r, x.r, x.b)."""
+        lib = self.lib
+        rc = lib.nb2_cg_update(self.code, self.n, mode, float(alpha), _ptr(lib, d), _ptr(lib, q), _ptr(lib, b),
+                               _ptr(lib, x), _ptr(lib, r), _ptr(lib, self.sums), _stream(x))
+        lib.check(rc, "nb2_cg_update")
+        s = self.sums.cpu()
+        return float(s[0]), float(s[1]), float(s[2])
+
+    def axpby(self, a, x, b, y):
+        """y = a x + b y"""
+        lib = self.lib
+        lib.check(lib.nb2_axpby(self.code, self.n, float(a), _ptr(lib, x), float(b), _ptr(lib, y), _stream(y)),
+                  "nb2_axpby")
+        return y
+
+
+def _apply_with_curv(A, d, q):
+    if hasattr(A, "apply_with_curvature"):
+        q, curv = A.apply_with_curvature(d, out=q)
+        return q, float(curv.cpu())
+    res = A(d)
+    if res.data_ptr() != q.data_ptr():
+        q.copy_(res)
+    return q, float(vdot_device(d, q).cpu())
+
+
+def _apply(A, x, out):
+    try:
+        res = A(x, out=out)
+    except TypeError:
+        res = A(x)
+    if res.data_ptr() != out.data_ptr():
+        out.copy_(res)
+    return out
+
+
+# ================================================================ numpy-stack interface
+class QuadraticEnergy:
+    """``E(x) = 0.5 x^T A x - b^T x`` (quadratic_energy.py:25-78) on device tensors."""
+
+    def __init__(self, position, A, b, _grad=None, _value=None, _gradnorm=None):
+        self.position, self._A, self._b = position, A, b
+        if _grad is not None:
+            self.gradient = _grad
+            Ax = _grad if b is None else _grad + b
+        else:
+            Ax = A(position)
+            self.gradient = Ax if b is None else Ax - b
+        if _value is None:
+            _value = 0.5 * float(vdot_device(position, Ax).cpu())
+            if b is not None:
+                _value -= float(vdot_device(b, position).cpu())
+        self.value = _value
+        self._gradnorm = _gradnorm
+
+    def at(self, position):
+        return QuadraticEnergy(position, self._A, self._b)
+
+    def at_with_grad(self, position, grad):
+        return QuadraticEnergy(position, self._A, self._b, grad)
+
+    @property
+    def gradient_norm(self):
+        if self._gradnorm is None:
+            self._gradnorm = float(np.sqrt(float(vdot_device(self.gradient, self.gradient).cpu())))
+        return self._gradnorm
+
+    def apply_metric(self, x):
+        return self._A(x)
+
+    @property
+    def metric(self):
+        return self._A
+
+
+class _EnergyView:
+    """What an iteration controller looks at (value, gradient_norm), from the fused sums."""
+
+    __slots__ = ("value", "gradient_norm")
+
+    def __init__(self, value, gradient_norm):
+        self.value, self.gradient_norm = value, gradient_norm
+
+
+class IterationController:
+    CONVERGED, CONTINUE, ERROR = CONVERGED, CONTINUE, ERROR
+
+
+class GradientNormController(IterationController):
+    """``iteration_controllers.py:148-221``."""
+
+    def __init__(self, tol_abs_gradnorm=None, tol_rel_gradnorm=None, convergence_level=1, iteration_limit=None,
+                 name=None):
+        self._tol_abs_gradnorm, self._tol_rel_gradnorm = tol_abs_gradnorm, tol_rel_gradnorm
+        self._convergence_level, self._iteration_limit, self._name = convergence_level, iteration_limit, name
+
+    def start(self, energy):
+        self._itcount, self._ccount = -1, 0
+        if self._tol_rel_gradnorm is not None:
+            self._tol_rel_gradnorm_now = self._tol_rel_gradnorm * energy.gradient_norm
+        return self.check(energy)
+
+    def check(self, energy):
+        self._itcount += 1
+        inclvl = False
+        if self._tol_abs_gradnorm is not None and energy.gradient_norm <= self._tol_abs_gradnorm:
+            inclvl = True
+        if self._tol_rel_gradnorm is not None and energy.gradient_norm <= self._tol_rel_gradnorm_now:
+            inclvl = True
+        self._ccount = self._ccount + 1 if inclvl else max(0, self._ccount - 1)
+        if self._iteration_limit is not None and self._itcount >= self._iteration_limit:
+            return CONVERGED
+        if self._ccount >= self._convergence_level:
+            return CONVERGED
+        return CONTINUE
+
+
+class AbsDeltaEnergyController(IterationController):
+    """``iteration_controllers.py:356-423``."""
+
+    def __init__(self, deltaE, convergence_level=1, iteration_limit=None, name=None):
+        self._deltaE, self._convergence_level = deltaE, convergence_level
+        self._iteration_limit, self._name = iteration_limit, name
+
+    def start(self, energy):
+        self._itcount, self._ccount, self._Eold = -1, 0, 0.0
+        return self.check(energy)
+
+    def check(self, energy):
+        self._itcount += 1
+        Eval = energy.value
+        diff = abs(self._Eold - Eval)
+        inclvl = self._itcount > 0 and diff < self._deltaE
+        self._Eold = Eval
+        self._ccount = self._ccount + 1 if inclvl else max(0, self._ccount - 1)
+        if self._iteration_limit is not None and self._itcount >= self._iteration_limit:
+            return CONVERGED
+        if self._ccount >= self._convergence_level:
+            return CONVERGED
+        return CONTINUE
+
+
+class ConjugateGradient:
+    """``ConjugateGradient`` (conjugate_gradient.py:27-126): same constructor, same call,
+    same return ``(energy, status)``; ``nit`` of the last call is kept in ``self.nit``."""
+
+    def __init__(self, controller, nreset=20):
+        self._controller, self._nreset = controller, nreset
+        self.nit = 0
+
+    def __call__(self, energy, preconditioner=None):
+        controller = self._controller
+        self.nit = 0
+        status = controller.start(energy)
+        if status != CONTINUE:
+            return energy, status
+        A, b = energy._A, energy._b
+        if b is None:
+            b = torch.zeros_like(energy.position)
+        vec = _Vec(energy.position)
+        x = energy.position.clone()
+        r = energy.gradient.clone()
+        d = r.clone() if preconditioner is None else preconditioner(r).clone()
+        q = torch.empty_like(x)
+        previous_gamma = float(vdot_device(r, d).cpu())
+        if np.isnan(previous_gamma):
+            return energy, ERROR
+        if previous_gamma == 0:
+            return energy, CONVERGED
+
+        def mk_energy(value, gamma_rr):
+            return QuadraticEnergy(x, A, energy._b, _grad=r, _value=value, _gradnorm=float(np.sqrt(gamma_rr)))
+
+        ii = 0
+        while True:
+            q, curv = _apply_with_curv(A, d, q)                       # :84-85
+            if np.isnan(curv) or curv == 0.0:                          # :86-91
+                return energy, ERROR
+            alpha = previous_gamma / curv
+            if alpha < 0:                                              # :93-96
+                return energy, ERROR
+            ii += 1
+            self.nit += 1
+            if ii < self._nreset:                                      # :99-101
+                rr, xr, xb = vec.update(0, alpha, d, q, b, x, r)
+            else:                                                      # :102-105 exact residual
+                vec.axpby(-alpha, d, 1.0, x)
+                q = _apply(A, x, q)
+                rr, xr, xb = vec.update(1, 0.0, d, q, b, x, r)
+                ii = 0
+            value = 0.5 * (xr + xb) - xb                               # quadratic_energy.py:35-37
+            energy = mk_energy(value, rr)
+            if preconditioner is None:
+                s, gamma = r, rr
+            else:
+                s = preconditioner(r)
+                gamma = float(vdot_device(r, s).cpu())
+            if np.isnan(gamma) or gamma < 0:                           # :110-115
+                return energy, ERROR
+            if gamma == 0:
+                return energy, CONVERGED
+            status = controller.check(energy)                          # :120
+            if status != CONTINUE:
+                return energy, status
+            vec.axpby(1.0, s, max(0.0, gamma / previous_gamma), d)     # :124
+            previous_gamma = gamma
+
+
+# ================================================================ NIFTy.re interface
+CGResults = namedtuple("CGResults", "x nit nfev info success")
+
+
+def _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord, tol, atol):
+    """re/conjugate_gradient.py:93-107."""
+    norm_ord = 2 if norm_ord is None else norm_ord
+    maxiter_fallback = 20 * j.numel()
+    miniter = min(6, maxiter if maxiter is not None else maxiter_fallback) if miniter is None else miniter
+    maxiter = max(min(200, maxiter_fallback), miniter) if maxiter is None else maxiter
+    if absdelta is None and resnorm is None:
+        resnorm = max(tol * float(torch.linalg.vector_norm(j.reshape(-1).double(), ord=norm_ord).cpu()), atol)
+    fi = np.finfo(np.float32 if j.dtype == torch.float32 else np.float64)
+    return norm_ord, miniter, maxiter, resnorm, 6.0 * fi.eps, 6.0 * fi.tiny
+
+
+def _norm(r, rr, norm_ord):
+    if norm_ord == 2:
+        return float(np.sqrt(rr))
+    return float(torch.linalg.vector_norm(r.reshape(-1).double(), ord=norm_ord).cpu())
+
+
+def _cg_setup(mat, j, x0):
+    vec = _Vec(j)
+    q = torch.empty_like(j)
+    if x0 is None:
+        pos = torch.zeros_like(j)
+        r = -j
+        energy, nfev = 0.0, 0
+        gamma = float(vdot_device(r, r).cpu())
+    else:
+        pos = x0.clone()
+        q = _apply(mat, pos, q)
+        r = torch.empty_like(j)
+        rr, xr, xb = vec.update(1, 0.0, pos, q, j, pos, r)       # r = mat(x0) - j
+        energy, nfev, gamma = 0.5 * (xr - xb), 1, rr             # vdot((r - j)/2, pos)  :118-121
+    d = r.clone()
+    return vec, pos, r, d, q, energy, nfev, gamma
+
+
+def cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5, atol=0.0, miniter=None,
+       maxiter=None, name=None, time_threshold=None, _raise_nonposdef=True, history=None):
+    """``nifty8.re.conjugate_gradient.cg`` / ``_cg`` (re/conjugate_gradient.py:29-42,77-216).
+
+    Returns ``(x, CGResults)`` like the public ``cg`` (``:29-42``: ``return cg_res.x, cg_res.info``
+    is the reference's public signature; the full record is returned here for inspection)."""
+    res = _cg(mat, j, x0, absdelta=absdelta, resnorm=resnorm, norm_ord=norm_ord, tol=tol, atol=atol,
+              miniter=miniter, maxiter=maxiter, name=name, time_threshold=time_threshold,
+              _raise_nonposdef=_raise_nonposdef, history=history)
+    return res.x, res.info
+
+
+def _cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5, atol=0.0, miniter=None,
+        maxiter=None, name=None, time_threshold=None, _raise_nonposdef=True, history=None):
+    norm_ord, miniter, maxiter, resnorm, eps, tiny = _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord,
+                                                               tol, atol)
+    vec, pos, r, d, q, energy, nfev, previous_gamma = _cg_setup(mat, j, x0)
+    info, i = -1, 0
+    if previous_gamma == 0:
+        return CGResults(pos, 0, nfev, 0, True)
+    for i in range(1, maxiter + 1):
+        q, curv = _apply_with_curv(mat, d, q)                          # :147-150
+        nfev += 1
+        if curv == 0.0:                                                # :151-156
+            if _raise_nonposdef:
+                raise ValueError("zero curvature in conjugate gradient")
+            info = 0
+            break
+        elif curv < 0.0:                                               # :157-167
+            if _raise_nonposdef:
+                raise ValueError("negative curvature in conjugate gradient")
+            if i > 1:
+                info = 0
+                break
+            pos = previous_gamma / (-curv) * j
+            info = 0
+            break
+        alpha = previous_gamma / curv
+        if i % N_RESET == 0:                                           # :170-172
+            vec.axpby(-alpha, d, 1.0, pos)
+            q = _apply(mat, pos, q)
+            nfev += 1
+            gamma, xr, xb = vec.update(1, 0.0, d, q, j, pos, r)
+        else:                                                          # :169,174
+            gamma, xr, xb = vec.update(0, alpha, d, q, j, pos, r)
+        if time_threshold is not None and time.time() > time_threshold:  # :176-178
+            info = i
+            break
+        if gamma >= 0.0 and gamma <= tiny:                             # :179-183
+            info = 0
+            break
+        if resnorm is not None:                                        # :184-188
+            if _norm(r, gamma, norm_ord) < resnorm and i >= miniter:
+                info = 0
+                break
+        new_energy = 0.5 * (xr - xb)                                   # :191
+        energy_diff = energy - new_energy
+        if history is not None:
+            history.append(new_energy)
+        if energy_diff < -eps * abs(new_energy):                       # :192-200
+            if _raise_nonposdef:
+                raise ValueError("WARNING: energy increased in conjugate gradient")
+            info = i
+            break
+        if absdelta is not None and energy_diff < absdelta and i >= miniter:   # :201-203
+            info = 0
+            break
+        energy = new_energy
+        vec.axpby(1.0, r, max(0.0, gamma / previous_gamma), d)         # :205
+        previous_gamma = gamma
+    info = i if info == -1 else info
+    return CGResults(pos, i, nfev, info, info == 0)
+
+
+def static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5, atol=0.0, miniter=None,
+              maxiter=None, name=None, history=None, **kwargs):
+    """``static_cg`` (re/conjugate_gradient.py:45-51): returns ``(x, info)``."""
+    res = _static_cg(mat, j, x0, absdelta=absdelta, resnorm=resnorm, norm_ord=norm_ord, tol=tol, atol=atol,
+                     miniter=miniter, maxiter=maxiter, name=name, history=history)
+    return res.x, res.info
+
+
+def _static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5, atol=0.0, miniter=None,
+               maxiter=None, name=None, history=None, **kwargs):
+    """``_static_cg`` (re/conjugate_gradient.py:219-389): the body of ``cg_single_step``
+    (``:266-338``) with the same ``info`` bookkeeping (-2 running, -1 error, 0 converged,
+    i > 0 iteration limit); the while-loop runs on the host, the state stays on the device."""
+    norm_ord, miniter, maxiter, resnorm, eps, tiny = _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord,
+                                                               tol, atol)
+    vec, pos, r, d, q, energy, nfev, gamma = _cg_setup(mat, j, x0)
+    info, i = (0 if gamma == 0.0 else -2), 0
+    while info < -1:
+        previous_gamma, previous_energy = gamma, energy
+        i += 1
+        q, curv = _apply_with_curv(mat, d, q)                          # :270-271
+        if curv == 0.0:
+            info = -1
+        with np.errstate(divide="ignore", invalid="ignore"):
+            alpha = float(np.float64(previous_gamma) / np.float64(curv))
+        if alpha < 0.0:                                                # :276-279
+            info = -1
+        if i % N_RESET == 0:                                           # :281-290
+            vec.axpby(-alpha, d, 1.0, pos)
+            q = _apply(mat, pos, q)
+            gamma, xr, xb = vec.update(1, 0.0, d, q, j, pos, r)
+        else:
+            gamma, xr, xb = vec.update(0, alpha, d, q, j, pos, r)
+        if gamma >= 0.0 and gamma <= tiny and info != -1:              # :292-294
+            info = 0
+        if resnorm is not None:                                        # :295-301
+            if _norm(r, gamma, norm_ord) < resnorm and i >= miniter and info != -1:
+                info = 0
+        energy = 0.5 * (xr - xb)                                       # :303
+        energy_diff = previous_energy - energy
+        if history is not None:
+            history.append(energy)
+        if energy_diff < -eps * abs(energy):                           # :305-307
+            info = -1
+        if absdelta is not None and energy_diff < absdelta and i >= miniter and info != -1:   # :308-312
+            info = 0
+        if i >= maxiter and info != -1:                                # :313
+            info = i
+        with np.errstate(divide="ignore", invalid="ignore"):
+            beta = max(0.0, float(np.float64(gamma) / np.float64(previous_gamma)))
+        vec.axpby(1.0, r, beta, d)                                     # :315
+    nfev += i + i // N_RESET
+    return CGResults(pos, i, nfev, info, info == 0)

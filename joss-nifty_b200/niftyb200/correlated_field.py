@@ -1,0 +1,299 @@
+"""Correlated-field model with the hot tail on the GPU.
+
+Interface follows ``nifty8.re.correlated_field.CorrelatedFieldMaker``
+(``/root/reference/src/re/correlated_field.py:311-704``) -- ``add_fluctuations``,
+``add_fluctuations_matern``, ``set_amplitude_total_offset``, ``finalize`` -- and
+``SimpleCorrelatedField`` of the numpy stack
+(``src/library/correlated_fields_simple.py:38-170``).  Parameters are a dict
+``{prefix+"xi", prefix+"zeromode", prefix+"fluctuations", ...}`` of standard-normal
+excitations exactly as in the reference (``finalize`` ``:640-704``).
+
+What runs where:
+* O(n_bins) amplitude chain (integrated Wiener process, normalisation; ``:277-304``,
+  ``src/re/gauss_markov.py:105-121``): fp64 torch ops on the device (cold path,
+  SURVEY.md section 8f N1),
+* hot tail ``offset + (1/V) hartley(azm * amp[pindex] * xi)`` (``:690-693``) and its adjoint:
+  one fused 3-pass CUDA transform (:mod:`niftyb200.transforms`), the gather riding on the
+  first load, scale/offset on the last store.
+"""
+
+import math
+
+import numpy as np
+import torch
+
+from . import _lib, config
+from .geometry import RGGrid
+from .transforms import Plan, PointOp, device as _device
+
+
+# ---------------------------------------------------------------- priors (re/num/stats_distributions.py:41-88)
+def lognormal_moments(mean, std):
+    if mean <= 0.0:
+        raise ValueError(f"`mean` must be greater zero; got {mean!r}")
+    if std <= 0.0:
+        raise ValueError(f"`std` must be greater zero; got {std!r}")
+    logstd = math.sqrt(math.log1p((std / mean) ** 2))
+    return math.log(mean) - 0.5 * logstd ** 2, logstd
+
+
+def normal_prior(mean, std):
+    return lambda xi: mean + std * xi
+
+
+def lognormal_prior(mean, std):
+    lm, ls = lognormal_moments(mean, std)
+    return lambda xi: torch.exp(lm + ls * xi)
+
+
+def _prior(spec, kind):
+    if spec is None or callable(spec):
+        return spec
+    if len(spec) != 2:
+        raise TypeError(f"prior specification must be (mean, std); got {spec!r}")
+    return (lognormal_prior if kind == "lognormal" else normal_prior)(*spec)
+
+
+# ---------------------------------------------------------------- amplitude chain (torch, fp64)
+def _integrated_wiener_process(xi, sigma, dt, asperity):
+    """``integrated_wiener_process`` (src/re/gauss_markov.py:105-121) with x0 = 0;
+    returns the integrated component only."""
+    amp = sigma * torch.sqrt(dt)
+    dev = amp * xi[:, 1]                                       # increments of the rate
+    lvl = amp * xi[:, 0] * torch.sqrt(dt * dt / 12.0 + (0.0 if asperity is None else asperity))
+    lvl = lvl + 0.5 * dt * dev
+    zero = torch.zeros(1, dtype=xi.dtype, device=xi.device)
+    rate = torch.cumsum(torch.cat((zero, dev)), 0)
+    lvl = torch.cat((zero, lvl + dt * rate[:-1]))
+    return torch.cumsum(lvl, 0)
+
+
+class _Fluctuations:
+    def __init__(self, grid, kind, priors, prefix, np_kind):
+        self.grid, self.kind, self.priors, self.prefix, self.np_kind = grid, kind, priors, prefix, np_kind.lower()
+        if self.np_kind not in ("amplitude", "power"):
+            raise ValueError(f"invalid kind specified {np_kind!r}")
+
+    def domain(self):
+        d, pf, g = {}, self.prefix, self.grid
+        if self.kind == "nonparametric":
+            d[pf + "fluctuations"] = ()
+            d[pf + "loglogavgslope"] = ()
+            if self.priors["flexibility"] is not None and g.log_volume.numel() > 0:
+                d[pf + "flexibility"] = ()
+                if self.priors["asperity"] is not None:
+                    d[pf + "asperity"] = ()
+                d[pf + "spectrum"] = (int(g.log_volume.numel()), 2)
+        else:
+            for k in ("scale", "cutoff", "loglogslope"):
+                d[pf + k] = ()
+        return d
+
+    def amplitude(self, p):
+        """Un-normalised amplitude per power bin (fp64 device tensor)."""
+        g, pr, pf = self.grid, self.priors, self.prefix
+        totvol = g.total_volume
+        mult = g.mode_multiplicity.to(torch.float64)
+        if self.kind == "nonparametric":
+            # non_parametric_amplitude.correlate (re/correlated_field.py:277-304)
+            flu = pr["fluctuations"](p[pf + "fluctuations"])
+            slope = pr["loglogavgslope"](p[pf + "loglogavgslope"])
+            rel = g.relative_log_mode_lengths
+            ln_spec = slope * rel
+            if pr["flexibility"] is not None and g.log_volume.numel() > 0:
+                flx = pr["flexibility"](p[pf + "flexibility"])
+                asp = pr["asperity"](p[pf + "asperity"]) if pr["asperity"] is not None else None
+                tw = _integrated_wiener_process(p[pf + "spectrum"], flx, g.log_volume, asp)
+                tw = torch.cat((torch.zeros(1, dtype=tw.dtype, device=tw.device), tw))
+                ln_spec = ln_spec + (tw - tw[-1] * (rel / rel[-1]))       # _remove_slope :144-147
+            spec = torch.exp(ln_spec)
+            if self.np_kind == "amplitude":
+                norm = torch.sqrt(torch.sum(mult[1:] * spec[1:] ** 2)) / math.sqrt(totvol)
+                amp = flu * (math.sqrt(totvol) / norm) * spec
+            else:
+                norm = torch.sqrt(torch.sum(mult[1:] * spec[1:])) / math.sqrt(totvol)
+                amp = flu * (math.sqrt(totvol) / norm) * torch.sqrt(spec)
+        else:
+            # matern_amplitude.correlate (re/correlated_field.py:186-213)
+            scale = pr["scale"](p[pf + "scale"])
+            cutoff = pr["cutoff"](p[pf + "cutoff"])
+            slope = pr["loglogslope"](p[pf + "loglogslope"])
+            spec = torch.exp(0.25 * slope * torch.log1p((g.mode_lengths / cutoff) ** 2))
+            norm = 1.0
+            if pr["renormalize_amplitude"]:
+                pw = 4 if self.np_kind == "amplitude" else 2
+                norm = torch.sqrt(torch.sum(mult[1:] * spec[1:] ** pw)) / math.sqrt(totvol)
+            amp = scale * (math.sqrt(totvol) / norm) * spec
+            if self.np_kind == "power":
+                amp = torch.cat((amp[:1], torch.sqrt(amp[1:])))
+        amp = amp.clone()
+        amp[0] = totvol if not (self.kind == "matern" and self.np_kind == "power") else math.sqrt(totvol)
+        return amp
+
+
+class CorrelatedFieldMaker:
+    """``nifty8.re.CorrelatedFieldMaker`` (re/correlated_field.py:311-704) for the GPU backend."""
+
+    def __init__(self, prefix, dtype=torch.float64):
+        self._prefix = prefix
+        self._azm = None
+        self._offset_mean = None
+        self._fluctuations = []
+        self._dtype = dtype
+
+    def set_amplitude_total_offset(self, offset_mean, offset_std):
+        """``:548-575``; ``offset_std`` = (mean, std) of a log-normal prior or a callable."""
+        zm = offset_std
+        if not callable(zm):
+            if zm is None or len(zm) != 2:
+                raise TypeError(f"`offset_std` of invalid type {type(zm)!r}")
+            zm = lognormal_prior(*zm)
+        self._offset_mean = float(offset_mean)
+        self._azm = zm
+
+    def add_fluctuations(self, shape, distances, fluctuations, loglogavgslope, flexibility=None,
+                         asperity=None, prefix="", harmonic_type="fourier", non_parametric_kind="amplitude"):
+        """``:343-450``."""
+        if harmonic_type.lower() != "fourier":
+            raise NotImplementedError("only harmonic_type='fourier' (regular grids) is on the GPU path")
+        grid = RGGrid(shape, distances, _device())
+        pri = dict(fluctuations=_prior(fluctuations, "lognormal"), loglogavgslope=_prior(loglogavgslope, "normal"),
+                   flexibility=_prior(flexibility, "lognormal"), asperity=_prior(asperity, "lognormal"))
+        self._fluctuations.append(_Fluctuations(grid, "nonparametric", pri, self._prefix + prefix,
+                                                non_parametric_kind))
+
+    def add_fluctuations_matern(self, shape, distances, scale, cutoff, loglogslope, renormalize_amplitude,
+                                prefix="", harmonic_type="fourier", non_parametric_kind="amplitude"):
+        """``:452-546``."""
+        if harmonic_type.lower() != "fourier":
+            raise NotImplementedError("only harmonic_type='fourier' (regular grids) is on the GPU path")
+        grid = RGGrid(shape, distances, _device())
+        pri = dict(scale=_prior(scale, "lognormal"), cutoff=_prior(cutoff, "lognormal"),
+                   loglogslope=_prior(loglogslope, "normal"), renormalize_amplitude=bool(renormalize_amplitude))
+        self._fluctuations.append(_Fluctuations(grid, "matern", pri, self._prefix + prefix, non_parametric_kind))
+
+    @property
+    def azm(self):
+        if self._azm is None:
+            raise NotImplementedError("You need to set the `amplitude_total_offset` first")
+        return self._azm
+
+    def finalize(self):
+        """``:640-704``."""
+        if not self._fluctuations:
+            raise NotImplementedError("add fluctuations first")
+        _ = self.azm
+        return CorrelatedField(self._prefix, self._offset_mean, self._azm, list(self._fluctuations), self._dtype)
+
+
+class Tables:
+    """Everything the hot tail needs for one expansion point: device-resident."""
+
+    def __init__(self, amp_mode, amp, azm, amps):
+        self.amp_mode, self.amp, self.azm, self.amps = amp_mode, amp, float(azm), amps
+
+
+class CorrelatedField:
+    """Finalised model: ``cf(p)`` == ``correlated_field(p)`` (re/correlated_field.py:690-693)."""
+
+    def __init__(self, prefix, offset_mean, azm, fluctuations, dtype):
+        self.prefix, self.offset_mean, self._azm, self.fl, self.dtype = prefix, offset_mean, azm, fluctuations, dtype
+        self.grids = [f.grid for f in self.fl]
+        self.shape = tuple(s for g in self.grids for s in g.shape)
+        self.domain = {prefix + "xi": self.shape, prefix + "zeromode": ()}
+        for f in self.fl:
+            self.domain.update(f.domain())
+        self.axes, n = [], 0
+        for g in self.grids:
+            self.axes.append(tuple(range(n, n + len(g.shape))))
+            n += len(g.shape)
+        self.device = _device()
+        self.plans = [Plan(self.shape, ax, dtype) for ax in self.axes]
+        self.single = len(self.grids) == 1
+        # joint harmonic volume factor prod_g 1/V_g (re/correlated_field.py:654,663-668)
+        self.dvol = float(np.prod([1.0 / g.total_volume for g in self.grids]))
+
+    # ---- parameters ---------------------------------------------------------------
+    def _as_dev(self, v, dtype=torch.float64):
+        if isinstance(v, torch.Tensor):
+            return v.to(device=self.device, dtype=dtype)
+        return torch.as_tensor(np.asarray(v), dtype=dtype).to(self.device)
+
+    def init(self, seed=0, dtype=None):
+        """Standard-normal excitations for every parameter (``Model.init``)."""
+        gen = np.random.default_rng(seed)
+        return {k: gen.standard_normal(shp) for k, shp in self.domain.items()}
+
+    def azm(self, p):
+        return self._azm(self._as_dev(p[self.prefix + "zeromode"]))
+
+    def normalized_amplitudes(self, p):
+        """``get_normalized_amplitudes`` (``:598-611``): ``amp.at[1:].mul(1/azm)``, fp64, device."""
+        pd = {k: self._as_dev(v) for k, v in p.items() if not k.endswith("xi")}
+        azm = self._azm(pd[self.prefix + "zeromode"])
+        out = []
+        for f in self.fl:
+            a = f.amplitude(pd)
+            out.append(torch.cat((a[:1], a[1:] / azm)))
+        return out, azm
+
+    def tables(self, p):
+        """Device tables for the expansion point ``p`` (cold path, once per nonlinear step)."""
+        amps, azm = self.normalized_amplitudes(p)
+        return self.tables_from_amplitudes(amps, float(azm))
+
+    def tables_from_amplitudes(self, amps, azm):
+        amps = [self._as_dev(a) for a in amps]
+        if self.single and self.grids[0].isotropic and self.plans[0].is_fast:
+            return Tables(1, self.grids[0].ksq_table(amps[0], self.dtype), azm, amps)
+        full = None
+        for a, g in zip(amps, self.grids):
+            e = g.expand(a, torch.float64)
+            full = e if full is None else torch.tensordot(full, e, dims=0)    # outer_amplitude :681-688
+        return Tables(2, full.to(self.dtype).contiguous(), azm, amps)
+
+    # ---- hot tail ---------------------------------------------------------------------
+    def apply_xi(self, xi, tab, out=None, convention=None, offset=None, mul=None):
+        """``offset + prod_g (1/V_g) hartley_g(azm * amp[pindex] * xi)`` on device tensors."""
+        off = self.offset_mean if offset is None else offset
+        pro = PointOp(tab.amp_mode, tab.amp, tab.azm)
+        if self.single:
+            return self.plans[0].hartley(xi, out=out, convention=convention, pro=pro,
+                                         epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))
+        cur = self.plans[0].hartley(xi, out=out, convention=convention, pro=pro)
+        for pl in self.plans[1:-1]:
+            cur = pl.hartley(cur, out=cur, convention=convention)
+        return self.plans[-1].hartley(cur, out=cur, convention=convention,
+                                      epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))
+
+    def adjoint_xi(self, ybar, tab, out=None, convention=None, add=None, dot=None, dot_out=None):
+        """xi-block of the VJP: ``azm * amp[pindex] * prod_g (1/V_g) hartley_g(ybar)`` (Hartley is
+        symmetric: harmonic_operators.py:213-217).  Optional fused ``+ add`` and ``dot``."""
+        epi = PointOp(tab.amp_mode, tab.amp, tab.azm * self.dvol, add=add, dot=dot, dot_out=dot_out)
+        if self.single:
+            return self.plans[0].hartley(ybar, out=out, convention=convention, epi=epi)
+        cur = self.plans[-1].hartley(ybar, out=out, convention=convention)
+        for pl in reversed(self.plans[1:-1]):
+            cur = pl.hartley(cur, out=cur, convention=convention)
+        return self.plans[0].hartley(cur, out=cur, convention=convention, epi=epi)
+
+    def __call__(self, p, convention=None):
+        """Full model evaluation.  numpy in -> numpy out (host buffers, copies included);
+        torch device tensors in -> device tensor out."""
+        xi = p[self.prefix + "xi"]
+        host = not isinstance(xi, torch.Tensor)
+        tab = self.tables(p)
+        y = self.apply_xi(self._as_dev(xi, self.dtype).contiguous(), tab, convention=convention)
+        return y.cpu().numpy() if host else y
+
+
+def SimpleCorrelatedField(shape, distances, offset_mean, offset_std, fluctuations, flexibility, asperity,
+                          loglogavgslope, prefix="", dtype=torch.float64, non_parametric_kind="power"):
+    """Single-space correlated field (``src/library/correlated_fields_simple.py:38-170``;
+    same argument order).  The numpy stack parametrises the *power* spectrum
+    (``test/test_re/test_correlated_field.py:150``)."""
+    mk = CorrelatedFieldMaker(prefix, dtype=dtype)
+    mk.set_amplitude_total_offset(offset_mean, offset_std)
+    mk.add_fluctuations(shape, distances, fluctuations, loglogavgslope, flexibility, asperity,
+                        non_parametric_kind=non_parametric_kind)
+    return mk.finalize()

@@ -1,0 +1,68 @@
+"""The operator the conjugate gradient inverts: the MGVI / geoVI metric of a correlated field.
+
+``M t = J^T N^-1 J t + t`` (reference: ``ham_metric`` ``/root/reference/src/re/evi.py:108-109``;
+``LikelihoodWithModel.metric`` ``src/re/likelihood.py:568-576``; numpy stack
+``SamplingEnabler`` ``src/operators/sampling_enabler.py:59`` with ``SandwichOperator.make``
+``src/operators/sandwich_operator.py:42-76``).  For the xi block of a correlated field with a
+point-wise link and a diagonal likelihood this is
+
+    M t = A H diag(w) H A t + t,   A = diag(azm * amp[pindex]),  H = prod_g (1/V_g) Hartley_g,
+
+with ``w = f'(s)^2 / sigma^2`` (Gaussian, ``src/re/likelihood_impl.py:136-137``) or
+``w = lambda = exp(s)`` (Poissonian with exp link, ``:248-249``).
+
+One metric apply = two fused 3-pass transforms: the weight multiply rides on the last store
+of the forward transform, the amplitude multiply, the ``+ t`` and the CG curvature ``t.(M t)``
+on the last store of the adjoint transform.
+"""
+
+import torch
+
+from .transforms import PointOp
+
+
+def gaussian_weight(noise_cov_inv, link_derivative=None):
+    """``w = f'(s)^2 * N^-1`` (likelihood_impl.py:136-137)."""
+    return noise_cov_inv if link_derivative is None else noise_cov_inv * link_derivative ** 2
+
+
+def poisson_exp_weight(signal):
+    """``w = exp(s)`` for ``Poissonian`` with ``lambda = exp(s)`` (likelihood_impl.py:248-249)."""
+    return torch.exp(signal)
+
+
+class CFMetric:
+    """``mat(t) = A H w H A t + t`` on device tensors."""
+
+    def __init__(self, cf, tables, weight, convention=None):
+        self.cf, self.tab, self.convention = cf, tables, convention
+        if tuple(weight.shape) != cf.shape:
+            raise ValueError("weight must have the field's shape")
+        self.w = weight.to(device=cf.device, dtype=cf.dtype).contiguous()
+        self._u = torch.empty(cf.shape, dtype=cf.dtype, device=cf.device)
+        self._curv = torch.zeros((), dtype=torch.float64, device=cf.device)
+        self.shape, self.dtype, self.device = cf.shape, cf.dtype, cf.device
+        self.napply = 0
+
+    def forward_weighted(self, t, out):
+        """``w * H A t`` (offset excluded: this is the Jacobian)."""
+        return self.cf.apply_xi(t, self.tab, out=out, convention=self.convention, offset=0.0, mul=self.w)
+
+    def __call__(self, t, out=None):
+        self.napply += 1
+        u = self.forward_weighted(t, self._u)
+        return self.cf.adjoint_xi(u, self.tab, out=out, convention=self.convention, add=t)
+
+    def apply_with_curvature(self, t, out=None):
+        """Returns ``(M t, t.(M t))``; the dot product is fused into the last store.  The
+        curvature is a 0-d fp64 device tensor."""
+        self.napply += 1
+        u = self.forward_weighted(t, self._u)
+        q = self.cf.adjoint_xi(u, self.tab, out=out, convention=self.convention, add=t, dot=t,
+                               dot_out=self._curv)
+        return q, self._curv
+
+    def sample_rhs(self, white_data, white_prior, out=None):
+        """``j = J^T sqrt(w) eta + x0`` of ``draw_linear_residual`` (src/re/evi.py:114-125)."""
+        h = torch.sqrt(self.w) * white_data
+        return self.cf.adjoint_xi(h, self.tab, out=out, convention=self.convention, add=white_prior)

@@ -1,0 +1,264 @@
+"""Harmonic transforms at the ``ducc_dispatch`` seam, on the GPU.
+
+Mirrors the four callables the reference binds once at import
+(``/root/reference/src/ducc_dispatch.py:61-92``): ``fftn``, ``ifftn``, ``hartley``, ``vdot``
+with identical signatures and semantics (out of place, same shape, unnormalised forward,
+``ifftn`` scaled 1/N, Hartley convention read from the config at call time), plus
+device-resident variants that take/return ``torch`` CUDA tensors without host copies.
+"""
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib, config
+
+_TORCH_REAL = {torch.float32: _lib.F32, torch.float64: _lib.F64}
+_TORCH_CPLX = {torch.complex64: _lib.F32, torch.complex128: _lib.F64}
+_REAL_OF = {_lib.F32: torch.float32, _lib.F64: torch.float64}
+_CPLX_OF = {_lib.F32: torch.complex64, _lib.F64: torch.complex128}
+
+
+def _stream(t):
+    if t.device.type == "cuda":
+        return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+    return None
+
+
+def _ptr(lib, t, what="tensor"):
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{what}: expected a torch.Tensor, got {type(t).__name__}")
+    if t.device.type != lib.device_type:
+        raise ValueError(f"{what}: tensor lives on {t.device}, the native library needs {lib.device_type!r}")
+    if not t.is_contiguous():
+        raise ValueError(f"{what}: tensor must be contiguous")
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def device():
+    """torch device the native library operates on."""
+    lib = _lib.get()
+    return torch.device("cuda", torch.cuda.current_device()) if lib.device_type == "cuda" else torch.device("cpu")
+
+
+def _norm_axes(ndim, axes):
+    if axes is None:
+        return tuple(range(ndim))
+    if np.isscalar(axes):
+        axes = (int(axes),)
+    out = []
+    for a in axes:
+        a = int(a)
+        if a < -ndim or a >= ndim:
+            raise ValueError(f"axis {a} out of range for {ndim}-d array")
+        out.append(a % ndim)
+    if len(set(out)) != len(out):
+        raise ValueError("repeated axis")
+    return tuple(sorted(out))
+
+
+class PointOp:
+    """Python-side description of a fused point-wise operator (``nb2_pointop``).
+
+    Keeps references to the tensors so they stay alive while the kernel runs."""
+
+    def __init__(self, amp_mode=0, amp=None, scale=1.0, mul=None, add=None, add_scalar=0.0,
+                 dot=None, dot_out=None):
+        self.amp_mode, self.amp, self.scale = int(amp_mode), amp, float(scale)
+        self.mul, self.add, self.add_scalar = mul, add, float(add_scalar)
+        self.dot, self.dot_out = dot, dot_out
+
+    def to_c(self, lib):
+        c = _lib.PointOp()
+        c.amp_mode = self.amp_mode
+        c.amp = _ptr(lib, self.amp, "amp")
+        c.scale = self.scale
+        c.mul = _ptr(lib, self.mul, "mul")
+        c.add = _ptr(lib, self.add, "add")
+        c.add_scalar = self.add_scalar
+        c.dot = _ptr(lib, self.dot, "dot")
+        c.dot_out = _ptr(lib, self.dot_out, "dot_out")
+        return c
+
+
+class Plan:
+    """Transform plan over ``axes`` of a C-contiguous array of ``shape`` (``nb2_plan``)."""
+
+    def __init__(self, shape, axes=None, dtype=torch.float64):
+        self.lib = _lib.get()
+        self.shape = tuple(int(s) for s in shape)
+        self.axes = _norm_axes(len(self.shape), axes)
+        if dtype in _TORCH_CPLX:
+            dtype = _REAL_OF[_TORCH_CPLX[dtype]]
+        if dtype not in _TORCH_REAL:
+            raise TypeError(f"unsupported dtype {dtype}")
+        self.dtype = dtype
+        self.code = _TORCH_REAL[dtype]
+        sh = (ctypes.c_int64 * len(self.shape))(*self.shape)
+        ax = (ctypes.c_int32 * len(self.axes))(*self.axes)
+        h = ctypes.c_void_p()
+        self.lib.check(self.lib.nb2_plan_create(len(self.shape), sh, len(self.axes), ax, self.code,
+                                                ctypes.byref(h)), "nb2_plan_create")
+        self._h = h
+        self.is_fast = bool(self.lib.nb2_plan_is_fast(h))
+        self.ksq_size = int(self.lib.nb2_plan_ksq_size(h))
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                self.lib.nb2_plan_destroy(h)
+            except Exception:  # interpreter shutdown
+                pass
+
+    # ---- device API ---------------------------------------------------------------
+    def hartley(self, x, out=None, convention=None, pro=None, epi=None):
+        """Genuine Hartley transform of the real tensor ``x`` (device), optional fused ops.
+
+        ``out`` may be ``x`` itself (in place).  Returns ``out``."""
+        if tuple(x.shape) != self.shape or x.dtype != self.dtype:
+            raise ValueError(f"plan is for shape {self.shape} {self.dtype}, got {tuple(x.shape)} {x.dtype}")
+        if out is None:
+            out = torch.empty_like(x)
+        elif tuple(out.shape) != self.shape or out.dtype != self.dtype:
+            raise ValueError("output tensor does not match the plan")
+        conv = config.convention_code(convention)
+        cpro = pro.to_c(self.lib) if pro is not None else None
+        cepi = epi.to_c(self.lib) if epi is not None else None
+        rc = self.lib.nb2_hartley(self._h, _ptr(self.lib, x, "x"), _ptr(self.lib, out, "out"), conv,
+                                  ctypes.byref(cpro) if cpro is not None else None,
+                                  ctypes.byref(cepi) if cepi is not None else None, _stream(x))
+        self.lib.check(rc, "nb2_hartley")
+        return out
+
+    def c2c(self, z, forward=True, scale=1.0, out=None):
+        """Complex FFT of the complex tensor ``z`` (device) over the plan's axes."""
+        if tuple(z.shape) != self.shape or z.dtype != _CPLX_OF[self.code]:
+            raise ValueError("input tensor does not match the plan")
+        if out is None:
+            out = torch.empty_like(z)
+        rc = self.lib.nb2_c2c(self._h, _ptr(self.lib, z, "z"), _ptr(self.lib, out, "out"), 1 if forward else 0,
+                              float(scale), _stream(z))
+        self.lib.check(rc, "nb2_c2c")
+        return out
+
+
+_plan_cache = {}
+
+
+def get_plan(shape, axes, dtype):
+    lib = _lib.get()
+    key = (id(lib), tuple(shape), _norm_axes(len(shape), axes), dtype)
+    p = _plan_cache.get(key)
+    if p is None:
+        if len(_plan_cache) > 64:
+            _plan_cache.clear()
+        p = _plan_cache[key] = Plan(shape, axes, dtype)
+    return p
+
+
+def hartley_device(x, axes=None, out=None, convention=None, pro=None, epi=None):
+    """Device-resident ``hartley``: torch tensor in, torch tensor out, no host copies."""
+    return get_plan(x.shape, axes, x.dtype).hartley(x, out=out, convention=convention, pro=pro, epi=epi)
+
+
+# ---- numpy drop-ins (ducc_dispatch semantics) ------------------------------------
+def _to_device(a, dtype):
+    t = torch.from_numpy(np.ascontiguousarray(a, dtype=dtype))
+    dev = device()
+    return t if dev.type == "cpu" else t.to(dev)
+
+
+def hartley(a, axes=None):
+    """``ducc_dispatch.hartley`` (``src/ducc_dispatch.py:75-78``; fallback ``:46-50``).
+
+    Real ndarray in, new real ndarray of the same shape and dtype out; float32 stays
+    float32 (as in ducc0), everything else is computed in float64."""
+    a = np.asarray(a)
+    if np.iscomplexobj(a):
+        raise TypeError("hartley: input must be real (the operator splits complex fields, "
+                        "harmonic_operators.py:202-206)")
+    dt = np.float32 if a.dtype == np.float32 else np.float64
+    if a.size == 0:
+        return np.zeros(a.shape, dtype=dt)
+    if a.ndim == 0:
+        return a.astype(dt)
+    x = _to_device(a, dt)
+    y = hartley_device(x, axes)
+    return y.cpu().numpy()
+
+
+def _c2c(a, axes, forward):
+    a = np.asarray(a)
+    cdt = np.complex64 if a.dtype in (np.float32, np.complex64) else np.complex128
+    if a.size == 0:
+        return np.zeros(a.shape, dtype=cdt)
+    if a.ndim == 0:
+        return a.astype(cdt)
+    z = _to_device(a, cdt)
+    ax = _norm_axes(a.ndim, axes)
+    scale = 1.0
+    if not forward:
+        scale = 1.0 / float(np.prod([a.shape[i] for i in ax]))
+    rdt = torch.float32 if cdt == np.complex64 else torch.float64
+    out = get_plan(a.shape, ax, rdt).c2c(z, forward=forward, scale=scale)
+    return out.cpu().numpy()
+
+
+def fftn(a, axes=None):
+    """``ducc_dispatch.fftn`` (``src/ducc_dispatch.py:66-67``): unnormalised forward c2c."""
+    return _c2c(a, axes, True)
+
+
+def ifftn(a, axes=None):
+    """``ducc_dispatch.ifftn`` (``src/ducc_dispatch.py:70-72``): backward c2c scaled 1/N."""
+    return _c2c(a, axes, False)
+
+
+def vdot_device(a, b):
+    """sum(conj(a) * b) of two device tensors; returns a 0-d fp64/complex128 device tensor."""
+    lib = _lib.get()
+    if a.shape != b.shape:
+        raise ValueError("vdot: shape mismatch")
+    if a.is_complex() or b.is_complex():
+        a = a if a.is_complex() else a.to(torch.complex128 if a.dtype == torch.float64 else torch.complex64)
+        b = b if b.is_complex() else b.to(a.dtype)
+        ar, br = torch.view_as_real(a.contiguous()), torch.view_as_real(b.contiguous())
+        re = vdot_device(ar, br)
+        # Im(conj(a) b) = a.re b.im - a.im b.re
+        bsw = torch.stack((br[..., 1], -br[..., 0]), dim=-1).contiguous()
+        im = vdot_device(ar, bsw)
+        return torch.complex(re, im)
+    if a.dtype != b.dtype or a.dtype not in _TORCH_REAL:
+        a, b = a.to(torch.float64), b.to(torch.float64)
+    a, b = a.contiguous(), b.contiguous()
+    out = torch.empty((), dtype=torch.float64, device=a.device)
+    rc = lib.nb2_vdot(_TORCH_REAL[a.dtype], a.numel(), _ptr(lib, a, "a"), _ptr(lib, b, "b"),
+                      _ptr(lib, out, "out"), _stream(a))
+    lib.check(rc, "nb2_vdot")
+    return out
+
+
+def vdot(a, b):
+    """``ducc_dispatch.vdot`` (``src/ducc_dispatch.py:81-86``): conj(a).b as a Python scalar;
+    integer inputs are promoted to float64; accumulation is fp64."""
+    a, b = np.asarray(a), np.asarray(b)
+    if np.issubdtype(a.dtype, np.integer) or a.dtype == bool:
+        a = a.astype(np.float64)
+    if np.issubdtype(b.dtype, np.integer) or b.dtype == bool:
+        b = b.astype(np.float64)
+    if a.shape != b.shape:
+        raise ValueError("vdot: shape mismatch")
+    cplx = np.iscomplexobj(a) or np.iscomplexobj(b)
+    if a.size == 0:
+        return 0j if cplx else 0.0
+    if cplx:
+        ta, tb = _to_device(a, np.complex128), _to_device(b, np.complex128)
+    else:
+        dt = np.float32 if (a.dtype == np.float32 and b.dtype == np.float32) else np.float64
+        ta, tb = _to_device(a, dt), _to_device(b, dt)
+    r = vdot_device(ta, tb).cpu()
+    return complex(r) if cplx else float(r)

@@ -1,0 +1,271 @@
+"""Parity cases shared by the CPU (emulator) and GPU test files.
+
+Every function compares the niftyb200 path -- whichever native library the calling test's
+fixture selected -- against the CPU oracle (``oracle/``, pinned to the reference through
+``tests/golden``) or against the golden vectors directly.  Tolerances are the north-star
+ones: rel-L2 <= 1e-12 (fp64) / 1e-5 (fp32) for applies, identical CG iteration counts.
+"""
+
+import sys
+
+import numpy as np
+import torch
+
+import niftyb200 as nb
+from niftyb200.transforms import PointOp, device as nb_device, get_plan
+from oracle import cg as ocg
+from oracle import correlated_field as ocf
+from oracle import metric as om
+from oracle import transforms as otr
+
+cgm = sys.modules["niftyb200.cg"]
+CONVS = ("non_canonical_hartley", "canonical_hartley")
+TOL = {np.float64: 1e-12, np.float32: 1e-5}
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64 if not np.iscomplexobj(a) else np.complex128), np.asarray(b)
+    nrm = np.linalg.norm(b.ravel())
+    return np.linalg.norm((a - b).ravel()) / (nrm if nrm > 0 else 1.0)
+
+
+def dev(a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a if dtype is None else a.astype(dtype)))
+    return t.to(nb_device())
+
+
+def host(t):
+    return t.detach().cpu().numpy()
+
+
+# ---------------------------------------------------------------- transforms
+def check_hartley_golden(golden):
+    """ducc_dispatch.hartley/fftn/ifftn drop-ins == golden vectors made by the reference."""
+    g = golden["transforms"]
+    for n in range(int(g["ncases"])):
+        a = g[f"h{n}_in"]
+        axes = tuple(int(x) for x in g[f"h{n}_axes"])
+        axes = None if axes == (-1,) else axes
+        for c in CONVS:
+            nb.config.update("hartley_convention", c)
+            try:
+                assert rel(nb.hartley(a, axes), g[f"h{n}_{c}"]) <= 1e-12, (n, c)
+                out32 = nb.hartley(a.astype(np.float32), axes)
+                assert out32.dtype == np.float32
+                assert rel(out32, g[f"h{n}_{c}"]) <= 1e-5, (n, c)
+            finally:
+                nb.config.update("hartley_convention", CONVS[0])
+        if f"h{n}_cin" in g:
+            z = g[f"h{n}_cin"]
+            assert rel(nb.fftn(z, axes), g[f"h{n}_fftn"]) <= 1e-12
+            assert rel(nb.ifftn(z, axes), g[f"h{n}_ifftn"]) <= 1e-12
+
+
+def check_hartley_shapes(shapes, dtypes=(np.float64, np.float32), seed=42):
+    rng = np.random.default_rng(seed)
+    for shape, axes in shapes:
+        a64 = rng.normal(size=shape)
+        for dt in dtypes:
+            a = a64.astype(dt)
+            for c in CONVS:
+                ref = otr.hartley(a.astype(np.float64), axes, c)
+                nb.config.update("hartley_convention", c)
+                try:
+                    got = nb.hartley(a, axes)
+                finally:
+                    nb.config.update("hartley_convention", CONVS[0])
+                assert got.dtype == dt and got.shape == a.shape
+                assert rel(got, ref) <= TOL[dt], (shape, axes, dt, c, rel(got, ref))
+
+
+def check_inplace_and_roundtrip(shape, dt=np.float64):
+    """in-place execution == out-of-place; H(H(x)) = N x (test_fft_operator.py:38-60)."""
+    rng = np.random.default_rng(7)
+    a = rng.normal(size=shape).astype(dt)
+    x = dev(a)
+    plan = get_plan(x.shape, None, x.dtype)
+    y = plan.hartley(x)
+    x2 = x.clone()
+    plan.hartley(x2, out=x2)
+    assert torch.equal(y, x2)
+    assert torch.equal(x, dev(a)), "input modified by out-of-place transform"
+    back = plan.hartley(y, epi=PointOp(scale=1.0 / a.size))
+    assert rel(host(back), a) <= 10 * TOL[dt]
+
+
+def check_operator_golden(golden):
+    """HartleyOperator modes and volume factors (harmonic_operators.py:200-217)."""
+    g = golden["operator"]
+    for n in range(int(g["ncases"])):
+        x, dist = g[f"o{n}_in"], g[f"o{n}_dist"]
+        op = nb.HartleyOperator(nb.RGSpace(x.shape, tuple(dist)))
+        y = op.times(x)
+        assert rel(y, g[f"o{n}_times"]) <= 1e-12
+        assert rel(op.inverse_times(y), g[f"o{n}_inverse"]) <= 1e-12
+        assert rel(op.adjoint_times(x), g[f"o{n}_adjoint"]) <= 1e-12
+        assert rel(op.times(g[f"o{n}_cin"]), g[f"o{n}_ctimes"]) <= 1e-12
+
+
+def check_vdot():
+    rng = np.random.default_rng(5)
+    a, b = rng.normal(size=(37, 11)), rng.normal(size=(37, 11))
+    assert abs(nb.vdot(a, b) - np.vdot(a, b)) <= 1e-12 * abs(np.vdot(a, b)) + 1e-13
+    z, w = a + 1j * b, b - 2j * a
+    assert abs(nb.vdot(z, w) - np.vdot(z, w)) <= 1e-12 * abs(np.vdot(z, w))
+    i = np.arange(12)
+    assert nb.vdot(i, i) == float(np.vdot(i, i))       # ints promoted to f64 (ducc_dispatch.py:82-85)
+    a32, b32 = a.astype(np.float32), b.astype(np.float32)
+    ref = np.vdot(a32.astype(np.float64), b32.astype(np.float64))
+    assert abs(nb.vdot(a32, b32) - ref) <= 1e-12 * abs(ref) + 1e-12   # fp64 accumulation
+
+
+# ---------------------------------------------------------------- correlated field
+NP_KW = dict(fluctuations=(1., .5), loglogavgslope=(-3., .2), flexibility=(1., .2), asperity=(.5, 5e-2))
+
+
+def make_pair(shape, dist, dtype=torch.float64, offset=2.0, kw=NP_KW, kind="power"):
+    mk = nb.CorrelatedFieldMaker("", dtype=dtype)
+    mk.set_amplitude_total_offset(offset, (1e-1, 3e-2))
+    mk.add_fluctuations(shape, dist, **kw, non_parametric_kind=kind)
+    mo = ocf.CorrelatedFieldMaker("")
+    mo.set_amplitude_total_offset(offset, (1e-1, 3e-2))
+    mo.add_fluctuations(shape, dist, **kw, non_parametric_kind=kind)
+    return mk.finalize(), mo.finalize()
+
+
+def check_cf_golden(golden, names):
+    """Full model == golden output of the reference numpy stack, both conventions."""
+    from test_oracle_golden import CF_CASES, golden_pos, build_oracle_cf
+    g = golden["correlated_field"]
+    for name in names:
+        subs, off_mean, off_std = CF_CASES[name]
+        mk = nb.CorrelatedFieldMaker("")
+        mk.set_amplitude_total_offset(off_mean, off_std)
+        for i, (shape, dist, kw) in enumerate(subs):
+            mk.add_fluctuations(shape, dist, **kw, prefix="" if len(subs) == 1 else f"ax{i}",
+                                non_parametric_kind="power")
+        cf = mk.finalize()
+        co = build_oracle_cf(name)
+        for conv in CONVS:
+            tag = f"{name}_{conv}"
+            p = golden_pos(g, tag, co)
+            assert set(p) == set(cf.domain)
+            y = cf(p, convention=conv)
+            assert rel(y, g[f"{tag}_val"]) <= 1e-10, (tag, rel(y, g[f"{tag}_val"]))
+            tab = cf.tables(p)
+            xb = cf.adjoint_xi(dev(g[f"{tag}_ybar"]), tab, convention=conv)
+            assert rel(host(xb), g[f"{tag}_adj_xi"]) <= 1e-10, tag
+
+
+def check_cf_vs_oracle(shape, dist, dt=np.float64, expect_mode=None, seed=3):
+    tdt = torch.float64 if dt == np.float64 else torch.float32
+    cf, co = make_pair(shape, dist, tdt)
+    p = cf.init(seed)
+    p["xi"] = p["xi"].astype(dt)
+    tab = cf.tables(p)
+    if expect_mode is not None:
+        assert tab.amp_mode == expect_mode
+    amps_o, azm_o = co.normalized_amplitudes(p), co.azm(p)
+    for a, b in zip(tab.amps, amps_o):
+        assert rel(host(a), b) <= 1e-12
+    rng = np.random.default_rng(seed + 1)
+    for conv in CONVS:
+        y = cf(p, convention=conv)
+        assert y.dtype == dt
+        assert rel(y, co(p, conv)) <= TOL[dt], (shape, dt, conv, rel(y, co(p, conv)))
+        yb = rng.normal(size=shape).astype(dt)
+        xb = host(cf.adjoint_xi(dev(yb), tab, convention=conv))
+        ref = co.adjoint(amps_o, azm_o, yb.astype(np.float64), convention=conv)[0]
+        assert rel(xb, ref) <= TOL[dt], (shape, dt, conv, rel(xb, ref))
+    # adjointness <A x, y> == <x, A^T y>  (extra.py:156-167)
+    x = rng.normal(size=shape).astype(dt)
+    Ax = host(cf.apply_xi(dev(x), tab, offset=0.0)).astype(np.float64)
+    Aty = host(cf.adjoint_xi(dev(yb), tab)).astype(np.float64)
+    lhs, rhs = np.vdot(Ax, yb.astype(np.float64)), np.vdot(x.astype(np.float64), Aty)
+    assert abs(lhs - rhs) <= (1e-12 if dt == np.float64 else 1e-4) * max(abs(lhs), abs(rhs), 1e-30)
+
+
+def metric_pair(shape, dist, dt=np.float64, seed=11, kw=NP_KW):
+    tdt = torch.float64 if dt == np.float64 else torch.float32
+    cf, co = make_pair(shape, dist, tdt, kw=kw)
+    p = cf.init(seed)
+    tab = cf.tables(p)
+    amps_o, azm_o = co.normalized_amplitudes(p), co.azm(p)
+    rng = np.random.default_rng(seed + 1)
+    w = np.exp(0.3 * rng.normal(size=shape)).astype(dt)
+    M = nb.CFMetric(cf, tab, dev(w))
+    Mo = om.cf_metric_xi(co, amps_o, azm_o, w.astype(np.float64))
+    x0 = rng.normal(size=shape).astype(dt)
+    j = om.linear_sample_rhs(co, amps_o, azm_o, w.astype(np.float64), rng.normal(size=shape),
+                             x0.astype(np.float64)).astype(dt)
+    return M, Mo, j, x0
+
+
+def check_metric(shape, dist, dt=np.float64):
+    M, Mo, j, x0 = metric_pair(shape, dist, dt)
+    t = dev(x0)
+    q, curv = M.apply_with_curvature(t)
+    ref = Mo(x0.astype(np.float64))
+    assert rel(host(q), ref) <= TOL[dt]
+    c_ref = np.vdot(x0.astype(np.float64), host(q).astype(np.float64))
+    assert abs(float(curv.cpu()) - c_ref) <= 1e-12 * abs(c_ref)       # fused dot == dot of its own output
+    assert rel(host(M(t)), ref) <= TOL[dt]
+    # rhs of the linear sample (evi.py:114-125)
+    # symmetric positive definite
+    u, v = np.random.default_rng(0).normal(size=(2,) + tuple(shape)).astype(dt)
+    a = np.vdot(host(M(dev(u))).astype(np.float64), v.astype(np.float64))
+    b = np.vdot(u.astype(np.float64), host(M(dev(v))).astype(np.float64))
+    assert abs(a - b) <= (1e-11 if dt == np.float64 else 1e-4) * max(abs(a), abs(b))
+
+
+GENTLE_KW = dict(fluctuations=(1., .1), loglogavgslope=(-1.5, .1), flexibility=(1., .2), asperity=(.5, 5e-2))
+
+
+def check_cg_parity(shape, dist):
+    """Identical iteration counts / info codes and matching solutions vs the reference CGs."""
+    M, Mo, j, x0 = metric_pair(shape, dist, np.float64, kw=GENTLE_KW)
+    jt, xt = dev(j), dev(x0)
+    n = j.size
+    for kw in (dict(absdelta=1e-6 * n, maxiter=100), dict(resnorm=1e-6 * np.linalg.norm(j), maxiter=100),
+               dict(absdelta=1e-12, maxiter=27), dict()):
+        h1, h2 = [], []
+        r = cgm._cg(M, jt, xt, history=h1, **kw)
+        ro = ocg.cg_re(Mo, j, x0, history=h2, **kw)
+        assert (r.nit, r.info, r.nfev) == (ro.nit, ro.info, ro.nfev), (kw, r[1:], ro[1:])
+        assert rel(host(r.x), ro.x) <= 1e-9
+        np.testing.assert_allclose(h1, h2, rtol=1e-9)
+        s = cgm._static_cg(M, jt, xt, **kw)
+        so = ocg.static_cg_re(Mo, j, x0, **kw)
+        assert (s.nit, s.info, s.nfev) == (so.nit, so.info, so.nfev), (kw, s[1:], so[1:])
+        assert rel(host(s.x), so.x) <= 1e-9
+    # x0 = None branch
+    r, ro = cgm._cg(M, jt, None, absdelta=1e-7 * n), ocg.cg_re(Mo, j, None, absdelta=1e-7 * n)
+    assert (r.nit, r.info, r.nfev) == (ro.nit, ro.info, ro.nfev)
+    assert rel(host(r.x), ro.x) <= 1e-9
+    # numpy-stack interface
+    for mk in (lambda m: m.AbsDeltaEnergyController(1e-6 * n, iteration_limit=100),
+               lambda m: m.GradientNormController(tol_rel_gradnorm=1e-4, iteration_limit=100),
+               lambda m: m.AbsDeltaEnergyController(0., iteration_limit=23)):
+        solver = nb.ConjugateGradient(mk(nb))
+        e, status = solver(nb.QuadraticEnergy(xt, M, jt))
+        ctrl = mk(ocg)
+        eo, so, nito = ocg.conjugate_gradient_np(ocg.QuadraticEnergy(x0, Mo, j), ctrl)
+        assert (solver.nit, status) == (nito, so)
+        assert rel(host(e.position), eo.position) <= 1e-9
+        assert abs(e.value - eo.value) <= 1e-10 * abs(eo.value)
+
+
+def check_cg_failure_modes():
+    """Non-positive-definite operator: same error behaviour as the reference
+    (re/conjugate_gradient.py:151-167,276-279; conjugate_gradient.py:86-96)."""
+    import pytest
+    j = dev(np.ones(8))
+    neg = lambda t, out=None: -t  # noqa: E731
+    with pytest.raises(ValueError):
+        cgm._cg(neg, j)
+    assert cgm._static_cg(neg, j).info == -1
+    r = cgm._cg(neg, j, _raise_nonposdef=False)
+    assert r.info == 0 and r.nit == 1
+    e, status = nb.ConjugateGradient(nb.GradientNormController(iteration_limit=5))(
+        nb.QuadraticEnergy(j.clone(), neg, j))
+    assert status == cgm.ERROR

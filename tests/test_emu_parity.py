@@ -1,0 +1,73 @@
+"""CPU-only: the kernels' index arithmetic (sequential thread emulator of the SAME kernel
+sources, tests/emu/README.md) and the Python host logic, checked against the oracle and the
+golden vectors of the reference.  The GPU twins of these tests are in test_gpu_parity.py."""
+
+import numpy as np
+import pytest
+
+import parity_cases as pc
+
+pytestmark = pytest.mark.usefixtures("emu")
+
+
+def test_ducc_dispatch_golden(golden):
+    pc.check_hartley_golden(golden)
+
+
+def test_hartley_pow2_shapes():
+    pc.check_hartley_shapes([((4,), None), ((8,), None), ((64,), None), ((2048,), None), ((8192,), None),
+                             ((2, 4), None), ((16, 32), None), ((128, 128), None), ((64, 16), None),
+                             ((4, 8, 16), None), ((16, 16, 16), None), ((2, 2, 4), None), ((32, 4, 64), None),
+                             ((3, 8, 16), (1, 2)), ((5, 64), (1,)), ((2, 3, 8, 8, 8), (2, 3, 4))])
+
+
+def test_hartley_long_axes():
+    # three-step radix plans (n > 1024) on strided and contiguous axes
+    pc.check_hartley_shapes([((2048, 4), None), ((4096, 8), None), ((8192, 4), None), ((4, 4096), None)],
+                            dtypes=(np.float64,))
+    pc.check_hartley_shapes([((16384,), None), ((4096, 4), None)], dtypes=(np.float32,))
+
+
+def test_hartley_generic_shapes():
+    pc.check_hartley_shapes([((10,), None), ((12, 9), None), ((15, 27), None), ((7, 1, 5), None), ((1,), None),
+                             ((6, 16, 8), (1,)), ((8, 4, 16), (0, 2)), ((16, 2), None), ((8, 6), None)])
+
+
+@pytest.mark.parametrize("shape", [(64,), (32, 16), (8, 16, 32)])
+def test_inplace_roundtrip(shape):
+    pc.check_inplace_and_roundtrip(shape)
+    pc.check_inplace_and_roundtrip(shape, np.float32)
+
+
+def test_operator_golden(golden):
+    pc.check_operator_golden(golden)
+
+
+def test_vdot():
+    pc.check_vdot()
+
+
+def test_cf_golden(golden):
+    pc.check_cf_golden(golden, ["cf1d", "cf2d", "cf2d_odd", "cf3d", "cfprod"])
+
+
+@pytest.mark.parametrize("shape,dist,mode", [((64,), 0.3, 1), ((32, 32), 1 / 32, 1), ((16, 16, 16), 1 / 16, 1),
+                                             ((8, 4, 16), 1 / 16, 2), ((5, 6), (0.3, 0.5), 2)])
+def test_cf_vs_oracle(shape, dist, mode):
+    pc.check_cf_vs_oracle(shape, dist, np.float64, mode)
+    pc.check_cf_vs_oracle(shape, dist, np.float32, mode)
+
+
+@pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((8, 8, 16), (1 / 8, 1 / 8, 1 / 16))])
+def test_metric(shape, dist):
+    pc.check_metric(shape, dist)
+    pc.check_metric(shape, dist, np.float32)
+
+
+@pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((16, 16, 16), 1 / 16)])
+def test_cg_parity(shape, dist):
+    pc.check_cg_parity(shape, dist)
+
+
+def test_cg_failure_modes():
+    pc.check_cg_failure_modes()

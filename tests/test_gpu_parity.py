@@ -1,0 +1,116 @@
+"""GPU parity tests proper: the CUDA kernels, called through the C ABI of
+``include/niftyb200.h`` (ctypes), against the CPU oracle and the reference's golden vectors,
+plus size-independent properties at the BASELINE sizes (sub-sampled direct Hartley sums,
+Parseval, involution, adjointness)."""
+
+import numpy as np
+import pytest
+import torch
+
+import parity_cases as pc
+
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("cuda")]
+
+
+def test_native_library_loaded(cuda):
+    import ctypes
+    assert cuda.path.endswith("libniftyb200.so") and cuda.nb2_version() >= 100
+    assert cuda.nb2_sm_count() > 0
+    assert isinstance(cuda.cdll, ctypes.CDLL)
+
+
+def test_ducc_dispatch_golden(golden):
+    pc.check_hartley_golden(golden)
+
+
+def test_hartley_pow2_shapes():
+    pc.check_hartley_shapes([((4,), None), ((8,), None), ((64,), None), ((2048,), None), ((8192,), None),
+                             ((2, 4), None), ((16, 32), None), ((128, 128), None), ((64, 16), None),
+                             ((4, 8, 16), None), ((16, 16, 16), None), ((2, 2, 4), None), ((32, 4, 64), None),
+                             ((3, 8, 16), (1, 2)), ((5, 64), (1,)), ((2, 3, 8, 8, 8), (2, 3, 4)),
+                             ((1024, 1024), None), ((64, 64, 64), None), ((128, 256, 64), None),
+                             ((512, 8, 1024), None), ((8, 1024, 64), None)])
+
+
+def test_hartley_long_axes():
+    pc.check_hartley_shapes([((2048, 64), None), ((4096, 64), None), ((8192, 16), None), ((16, 4096), None),
+                             ((64, 8192), None), ((16384,), None), ((2048, 2048), None)])
+
+
+def test_hartley_generic_shapes():
+    pc.check_hartley_shapes([((10,), None), ((12, 9), None), ((15, 27), None), ((7, 1, 5), None), ((1,), None),
+                             ((6, 16, 8), (1,)), ((8, 4, 16), (0, 2)), ((16, 2), None), ((8, 6), None),
+                             ((100, 60), None)])
+
+
+@pytest.mark.parametrize("shape", [(64,), (32, 16), (8, 16, 32), (256, 256), (128, 128, 128)])
+def test_inplace_roundtrip(shape):
+    pc.check_inplace_and_roundtrip(shape)
+    pc.check_inplace_and_roundtrip(shape, np.float32)
+
+
+def test_operator_golden(golden):
+    pc.check_operator_golden(golden)
+
+
+def test_vdot():
+    pc.check_vdot()
+
+
+def test_cf_golden(golden):
+    pc.check_cf_golden(golden, ["cf1d", "cf2d", "cf2d_odd", "cf3d", "cfprod"])
+
+
+@pytest.mark.parametrize("shape,dist,mode", [((64,), 0.3, 1), ((32, 32), 1 / 32, 1), ((16, 16, 16), 1 / 16, 1),
+                                             ((8, 4, 16), 1 / 16, 2), ((5, 6), (0.3, 0.5), 2),
+                                             ((128, 128), 1 / 128, 1), ((512, 512), 1 / 512, 1),
+                                             ((64, 64, 64), 1 / 64, 1), ((128, 128, 128), 1 / 128, 1)])
+def test_cf_vs_oracle(shape, dist, mode):
+    pc.check_cf_vs_oracle(shape, dist, np.float64, mode)
+    pc.check_cf_vs_oracle(shape, dist, np.float32, mode)
+
+
+@pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((8, 8, 16), (1 / 8, 1 / 8, 1 / 16)),
+                                        ((128, 128), 1 / 128), ((64, 64, 64), 1 / 64)])
+def test_metric(shape, dist):
+    pc.check_metric(shape, dist)
+    pc.check_metric(shape, dist, np.float32)
+
+
+@pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((16, 16, 16), 1 / 16), ((128, 128), 1 / 128),
+                                        ((64, 64, 64), 1 / 64)])
+def test_cg_parity(shape, dist):
+    pc.check_cg_parity(shape, dist)
+
+
+def test_cg_failure_modes():
+    pc.check_cg_failure_modes()
+
+
+# ---------------------------------------------------------------- BASELINE sizes: properties
+@pytest.mark.parametrize("shape,dt", [((4096, 4096), torch.float32), ((4096, 4096), torch.float64),
+                                      ((512, 512, 512), torch.float32), ((512, 512, 512), torch.float64),
+                                      ((1024, 1024, 1024), torch.float32)])
+def test_full_size_properties(shape, dt):
+    """Sub-sampled direct sums, Parseval ||Hx||^2 = N ||x||^2 and H(H x) = N x at full size."""
+    from niftyb200.transforms import PointOp, get_plan
+    from oracle import transforms as otr
+    n = int(np.prod(shape))
+    gen = torch.Generator(device="cuda").manual_seed(42)
+    x = torch.randn(shape, dtype=dt, device="cuda", generator=gen)
+    plan = get_plan(shape, None, dt)
+    y = plan.hartley(x)
+    tol = 1e-5 if dt == torch.float32 else 1e-12
+    nx, ny = float(torch.linalg.vector_norm(x.double())), float(torch.linalg.vector_norm(y.double()))
+    assert abs(ny ** 2 / (n * nx ** 2) - 1.0) <= 10 * tol
+    # spot checks against an O(N) direct evaluation of single output elements
+    if n <= 2 ** 27:
+        xh = x.cpu().numpy().astype(np.float64)
+        idx = [tuple(0 for _ in shape), tuple(s // 2 for s in shape), tuple(s - 1 for s in shape),
+               tuple((7 * (i + 1) * s) // 23 for i, s in enumerate(shape))]
+        ref = otr.direct_hartley_samples(xh, idx)
+        got = np.array([float(y[i]) for i in idx])
+        assert np.max(np.abs(got - ref)) <= 100 * tol * ny / np.sqrt(n) * np.sqrt(np.log2(n))
+    z = plan.hartley(y, out=y, epi=PointOp(scale=1.0 / n))
+    err = float(torch.linalg.vector_norm((z - x).double())) / nx
+    assert err <= 4 * tol, err
