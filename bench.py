@@ -1,0 +1,326 @@
+#!/usr/bin/env python3
+"""bench.py -- metric-CG iterations/s (each = 1 CF forward + 1 CF adjoint apply + fused CG
+vector updates) on a synthetic correlated field, BASELINE.json's metric and config.
+
+  python bench.py --gpus N --steps K --warmup W [--dtype f32|f64] [--shape 1024,1024,1024]
+  python bench.py --impl reference ...     # the reference's CPU algorithm on the host cores
+
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for the definitions.
+"""
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "joss-nifty_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "metric_cg_iters_per_s"
+UNIT = "CG iterations/s"
+# demos/1_tomography.py:21-34 hyper-parameters
+CF_KW = dict(fluctuations=(1.0, 0.5), loglogavgslope=(-5.0, 0.2), flexibility=(1.0, 0.2), asperity=(0.5, 5e-2))
+OFFSET = (2.0, (1e-1, 3e-2))
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--shape", default="1024,1024,1024")
+    ap.add_argument("--cpu-shape", default="512,512,512", help="bounded sample for the CPU baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------- clocks during the timed region
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------- CPU arm: the reference's algorithm on host cores
+def cpu_cg_iters_per_s(shape, dtype, iters=2):
+    """Oracle (NumPy/SciPy restatement of the reference, oracle/) CG iterations on the host
+    cores: reference fallback path scipy pocketfft with workers = all cores."""
+    from oracle import correlated_field as ocf, metric as om, cg as ocg, transforms as otr
+    cores = os.cpu_count() or 1
+    otr.set_nthreads(cores)
+    dt = np.float32 if dtype == "f32" else np.float64
+    mk = ocf.CorrelatedFieldMaker("")
+    mk.set_amplitude_total_offset(*OFFSET)
+    mk.add_fluctuations(shape, 1.0 / shape[0], **CF_KW, non_parametric_kind="power")
+    cf = mk.finalize()
+    rng = np.random.default_rng(43)
+    p = {k: rng.standard_normal(s) for k, s in cf.domain.items() if k != "xi"}
+    amps, azm = cf.normalized_amplitudes(p), cf.azm(p)
+    rng = np.random.default_rng(42)
+    x0 = rng.standard_normal(shape, dtype=dt)
+    w = np.exp(0.3 * rng.standard_normal(shape, dtype=dt))
+    mat = om.cf_metric_xi(cf, [a.astype(dt) for a in amps], dt(azm), w)
+    j = mat(x0) * dt(0.5) + x0
+    t0 = time.perf_counter()
+    res = ocg.cg_re(mat, j, x0, absdelta=0.0, miniter=iters, maxiter=iters, _raise_nonposdef=False)
+    t = time.perf_counter() - t0
+    # one iteration = one metric apply + vector updates; the solve did res.nfev applies
+    return res.nfev / t, cores, t
+
+
+def scale_to(shape_from, shape_to):
+    """N log N work ratio used to express a bounded CPU sample in the headline workload's unit."""
+    nf, nt = float(np.prod(shape_from)), float(np.prod(shape_to))
+    return (nf * np.log2(nf)) / (nt * np.log2(nt))
+
+
+# ---------------------------------------------------------------- GPU arm
+def setup_problem(nb, torch, shape, tdt, seed=42):
+    """Synthetic C3/C4 problem: xi ~ N(0,1), tomography hyper-parameters,
+    Gaussian likelihood with a dense per-voxel inverse variance."""
+    mk = nb.CorrelatedFieldMaker("", dtype=tdt)
+    mk.set_amplitude_total_offset(*OFFSET)
+    mk.add_fluctuations(shape, 1.0 / shape[0], **CF_KW, non_parametric_kind="power")
+    cf = mk.finalize()
+    rng = np.random.default_rng(43)
+    p = {k: rng.standard_normal(s) for k, s in cf.domain.items() if not k.endswith("xi")}
+    tab = cf.tables(p)
+    gen = torch.Generator(device="cuda").manual_seed(seed)
+    w = torch.exp(0.3 * torch.randn(shape, dtype=tdt, device="cuda", generator=gen))
+    M = nb.CFMetric(cf, tab, w)
+    x0 = torch.randn(shape, dtype=tdt, device="cuda", generator=gen)
+    j = M(x0)
+    j.mul_(0.5).add_(x0)
+    return cf, tab, M, j, x0
+
+
+def time_region(torch, dist, fn):
+    """barrier + sync, CUDA events on the launching stream, barrier + sync; max over ranks."""
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        dist.barrier()
+    return ms
+
+
+def run_b200(args):
+    import torch
+    import niftyb200 as nb
+    from niftyb200 import _lib
+    from niftyb200.transforms import PointOp
+    cgm = sys.modules["niftyb200.cg"]
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist = dist_mod
+    lib = _lib.get()
+    shape = tuple(int(s) for s in args.shape.split(","))
+    tdt = torch.float32 if args.dtype == "f32" else torch.float64
+    s = 4 if args.dtype == "f32" else 8
+    N, d = int(np.prod(shape)), len(shape)
+    peak, peak_src = peaks()
+
+    cf, tab, M, j, x0 = setup_problem(nb, torch, shape, tdt, seed=42 + rank)
+    loop = cgm.CGLoop(M, j, x0)
+    loop.run(args.warmup)
+    n0 = lib.nb2_launch_count()
+    with ClockSampler(local) as clk:
+        ms = time_region(torch, dist, lambda: loop.run(args.steps))
+    launches = int(lib.nb2_launch_count() - n0)
+    ms_step = ms / args.steps
+    value = world * 1000.0 / ms_step          # replicas: every rank runs its own grid
+
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+           "config": {"workload": f"3D correlated field {'x'.join(map(str, shape))} metric-CG "
+                                  "(configs[3] grid on one GPU; 1 step = 1 CG iteration = CF fwd + CF adj + fused updates)",
+                      "l2": "inputs larger than L2 (each vector %.2f GB)" % (N * s / 1e9),
+                      "multi_gpu": "independent replicas per rank" if world > 1 else "single GPU"},
+           "gpu_launches": launches, "clocks": clk.summary()}
+    B_cg = (4 * d + 13) * N * s                # SURVEY.md 8(d) nominal bytes per CG iteration
+    out["extra"] = {"cg_nominal_bytes": B_cg, "cg_hbm_frac_of_measured": B_cg / (ms_step * 1e-3) / 1e9 / peak}
+
+    if rank == 0:
+        # ---- per-kernel timing (CUDA events, same stream), applies/s, roofline of the dominant kernel
+        plan = cf.plans[0]
+        a, b = x0, torch.empty_like(x0)
+        reps = max(3, min(10, args.steps))
+
+        def tk(fn):
+            fn()
+            return time_region(torch, None, lambda: [fn() for _ in range(reps)]) / reps
+
+        t_fwd = tk(lambda: cf.apply_xi(a, tab, out=b))
+        t_adj = tk(lambda: cf.adjoint_xi(a, tab, out=b))
+        names = {0: "StridedPass(axis0)", 1: "StridedPass(axis1)", 2: "RowPass(contiguous+Hartley combine)"}
+        passes = {}
+        if plan.is_fast:
+            pro = PointOp(tab.amp_mode, tab.amp, tab.azm)
+            for which in range(3):
+                if len(shape) - 3 + which < 0:
+                    continue
+                passes[names[which]] = tk(lambda w=which: plan.run_pass(w, a, b))
+            passes["StridedPass(axis0)+amplitude gather"] = tk(lambda: plan.run_pass(3 - len(shape), a, b, pro=pro)) \
+                if len(shape) > 1 else None
+        t_upd = tk(lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r))
+        t_axp = tk(lambda: loop.vec.axpby(1.0, loop.r, 1.0, b))
+        dom = max((k for k in passes if passes[k]), key=lambda k: passes[k]) if passes else None
+        if dom:
+            ach = 2 * N * s / (passes[dom] * 1e-3) / 1e9
+            out["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+                               "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                               "algorithmic_bytes_per_launch": 2 * N * s}
+        out["extra"].update({
+            "fwd_applies_per_s": 1000.0 / t_fwd, "adj_applies_per_s": 1000.0 / t_adj,
+            "fwd_adj_pairs_per_s": 1000.0 / (t_fwd + t_adj),
+            "fwd_hbm_frac": 2 * d * N * s / (t_fwd * 1e-3) / 1e9 / peak,
+            "adj_hbm_frac": 2 * d * N * s / (t_adj * 1e-3) / 1e9 / peak,
+            "kernel_ms": {**{k: v for k, v in passes.items() if v}, "CgUpdate(+3 dots)": t_upd, "Axpby": t_axp},
+            "kernel_hbm_frac": {**{k: 2 * N * s / (v * 1e-3) / 1e9 / peak for k, v in passes.items() if v},
+                                "CgUpdate(+3 dots)": 7 * N * s / (t_upd * 1e-3) / 1e9 / peak,
+                                "Axpby": 3 * N * s / (t_axp * 1e-3) / 1e9 / peak}})
+        del b
+
+        # ---- end to end through the public API with HOST buffers
+        if not args.no_e2e:
+            jh = torch.empty(shape, dtype=tdt, pin_memory=True).copy_(j)
+            xh = torch.empty(shape, dtype=tdt, pin_memory=True).copy_(x0)
+            oh = torch.empty(shape, dtype=tdt, pin_memory=True)
+            K = args.steps
+
+            def solve():
+                jd, xd = jh.to("cuda", non_blocking=True), xh.to("cuda", non_blocking=True)
+                xs, info = nb.cg(M, jd, xd, absdelta=0.0, miniter=K, maxiter=K, _raise_nonposdef=False)
+                oh.copy_(xs, non_blocking=True)
+                torch.cuda.synchronize()
+                return info
+
+            solve()
+            t0 = time.perf_counter()
+            solve()
+            te = time.perf_counter() - t0
+            out["e2e"] = {"value": K / te, "unit": UNIT, "h2d_bytes_per_step": 2 * N * s / K,
+                          "d2h_bytes_per_step": N * s / K + 24,
+                          "what": f"nb.cg(...) solve of {K} iterations, j and x0 from pinned host memory, "
+                                  "solution back to host, per-iteration scalars read by the host"}
+            del jh, xh, oh
+
+        # ---- CPU baseline on a bounded sample
+        if not args.no_cpu_baseline and world == 1:
+            cshape = tuple(int(v) for v in args.cpu_shape.split(","))
+            cshape = cshape if np.prod(cshape) <= N else shape
+            v, cores, t = cpu_cg_iters_per_s(cshape, args.dtype)
+            out["cpu_baseline"] = {"value": v * scale_to(cshape, shape), "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": f"oracle CG (scipy pocketfft, workers={cores}) at {'x'.join(map(str, cshape))}: "
+                                             f"{v:.4f} it/s measured over {t:.1f}s, scaled by N log N to the headline grid",
+                                   "measured_value_at_sample": v}
+        print(json.dumps(out), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    shape = tuple(int(s) for s in args.shape.split(","))
+    cshape = tuple(int(v) for v in args.cpu_shape.split(","))
+    cshape = cshape if np.prod(cshape) <= np.prod(shape) else shape
+    iters = max(1, min(args.steps, 3))
+    v, cores, t = cpu_cg_iters_per_s(cshape, args.dtype, iters=iters)
+    val = v * scale_to(cshape, shape)
+    out = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", 1)),
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / val, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+           "config": {"workload": f"3D correlated field {'x'.join(map(str, shape))} metric-CG, CPU arm on a bounded "
+                                  f"sample {'x'.join(map(str, cshape))} scaled by N log N"},
+           "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+                            "sample": f"oracle restatement of the reference CG + CF metric (ducc0 absent -> the reference's "
+                                      f"own scipy pocketfft branch), {iters} iterations at {'x'.join(map(str, cshape))} in {t:.1f}s"},
+           "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

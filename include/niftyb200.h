@@ -83,6 +83,15 @@ int64_t nb2_plan_ksq_size(const nb2_plan* plan);
 int nb2_hartley(nb2_plan* plan, const void* in, void* out, int convention, const nb2_pointop* pro,
                 const nb2_pointop* epi, void* stream);
 
+/* Profiling / tuning hook: run ONE pass of the fast path (which = 0: strided pass over axis 0,
+ * 1: strided pass over axis 1, 2: contiguous row pass with the Hartley combine).  `pro` is
+ * honoured by passes 0/1/2, `epi` by pass 2 only.  Fast-path plans only. */
+int nb2_hartley_pass(nb2_plan* plan, int which, const void* in, void* out, int convention,
+                     const nb2_pointop* pro, const nb2_pointop* epi, void* stream);
+
+/* Total number of kernels this library has launched in the calling process. */
+int64_t nb2_launch_count(void);
+
 /* Complex-to-complex FFT, out = scale * FFT(in); forward != 0 -> exp(-i..), else exp(+i..).
  * Replaces ducc_dispatch.fftn / ifftn (src/ducc_dispatch.py:66-72; ifftn = backward, scale 1/N).
  * `in`/`out`: interleaved complex of the plan's precision. */

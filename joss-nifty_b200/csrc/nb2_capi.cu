@@ -352,6 +352,26 @@ int nb2_hartley(nb2_plan* pl, const void* in, void* out, int conv, const nb2_poi
                                 : hartley_generic<double>(pl, in, out, conv, pro, epi, st);
 }
 
+int nb2_hartley_pass(nb2_plan* pl, int which, const void* in, void* out, int conv, const nb2_pointop* pro,
+                     const nb2_pointop* epi, void* stream) {
+    if (!pl || !in || !out || which < 0 || which > 2 || (conv != 0 && conv != 1)) {
+        last_error() = "nb2_hartley_pass: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (!pl->fast || (which == 0 && !pl->g.logN0) || (which == 1 && !pl->g.logN1)) {
+        last_error() = "nb2_hartley_pass: pass not part of this plan";
+        return NB2_ERR_UNSUPPORTED;
+    }
+    rt_stream st = (rt_stream)stream;
+    if (which < 2)
+        return pl->dtype == NB2_F32 ? run_strided<float>(pl, which, in, out, pro, st)
+                                    : run_strided<double>(pl, which, in, out, pro, st);
+    return pl->dtype == NB2_F32 ? run_rows<float>(pl, in, out, conv, pro, epi, st)
+                                : run_rows<double>(pl, in, out, conv, pro, epi, st);
+}
+
+int64_t nb2_launch_count(void) { return launch_counter(); }
+
 int nb2_c2c(nb2_plan* pl, const void* in, void* out, int forward, double scale, void* stream) {
     if (!pl || !in || !out) {
         last_error() = "nb2_c2c: invalid argument";

@@ -24,6 +24,11 @@ inline std::string& last_error() {
     static thread_local std::string e;
     return e;
 }
+// number of kernels launched by this library so far (bench.py reports it as gpu_launches)
+inline long long& launch_counter() {
+    static long long n = 0;
+    return n;
+}
 
 #if !defined(NB2_EMU)
 // ------------------------------------------------------------------ device runtime
@@ -77,6 +82,7 @@ inline int rt_launch(long long grid, int nthreads, size_t smem, rt_stream stream
     }
     nb2_kernel<K><<<(unsigned)grid, nthreads, smem, stream>>>(p);
     NB2_CUDA_OK(cudaGetLastError());
+    ++launch_counter();
     return 0;
 }
 
@@ -138,6 +144,7 @@ inline int rt_launch(long long grid, int nthreads, size_t smem, rt_stream, const
         std::memset(base, 0xAB, smem);  // poison: catches reads of unwritten shared memory
         EmuStep<K, 0>::run(p, bid, nthreads, base);
     }
+    ++launch_counter();
     return 0;
 }
 inline int rt_malloc(void** p, size_t bytes) {

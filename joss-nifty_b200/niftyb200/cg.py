@@ -413,3 +413,34 @@ def _static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, t
         vec.axpby(1.0, r, beta, d)                                     # :315
     nfev += i + i // N_RESET
     return CGResults(pos, i, nfev, info, info == 0)
+
+
+class CGLoop:
+    """The CG recurrence with the stopping tests taken out: ``run(n)`` executes exactly ``n``
+    iterations with the same primitives as :func:`_cg` (metric apply with fused curvature,
+    fused update + sums, direction update; exact residual every ``N_RESET`` iterations).
+    Used by ``bench.py`` / profiling, where a fixed amount of work has to be timed."""
+
+    def __init__(self, mat, j, x0=None):
+        self.mat, self.j = mat, j
+        (self.vec, self.pos, self.r, self.d, self.q, self.energy, self.nfev, self.gamma) = _cg_setup(mat, j, x0)
+        self.i = 0
+
+    def run(self, n):
+        mat, vec, j = self.mat, self.vec, self.j
+        for _ in range(n):
+            self.i += 1
+            self.q, curv = _apply_with_curv(mat, self.d, self.q)
+            self.nfev += 1
+            alpha = self.gamma / curv
+            if self.i % N_RESET == 0:
+                vec.axpby(-alpha, self.d, 1.0, self.pos)
+                self.q = _apply(mat, self.pos, self.q)
+                self.nfev += 1
+                gamma, xr, xb = vec.update(1, 0.0, self.d, self.q, j, self.pos, self.r)
+            else:
+                gamma, xr, xb = vec.update(0, alpha, self.d, self.q, j, self.pos, self.r)
+            self.energy = 0.5 * (xr - xb)
+            vec.axpby(1.0, self.r, max(0.0, gamma / self.gamma), self.d)
+            self.gamma = gamma
+        return self

@@ -134,6 +134,17 @@ class Plan:
         self.lib.check(rc, "nb2_hartley")
         return out
 
+    def run_pass(self, which, x, out, convention=None, pro=None, epi=None):
+        """Profiling hook: one pass of the fast path (``nb2_hartley_pass``)."""
+        cpro = pro.to_c(self.lib) if pro is not None else None
+        cepi = epi.to_c(self.lib) if epi is not None else None
+        rc = self.lib.nb2_hartley_pass(self._h, int(which), _ptr(self.lib, x, "x"), _ptr(self.lib, out, "out"),
+                                       config.convention_code(convention),
+                                       ctypes.byref(cpro) if cpro is not None else None,
+                                       ctypes.byref(cepi) if cepi is not None else None, _stream(x))
+        self.lib.check(rc, "nb2_hartley_pass")
+        return out
+
     def c2c(self, z, forward=True, scale=1.0, out=None):
         """Complex FFT of the complex tensor ``z`` (device) over the plan's axes."""
         if tuple(z.shape) != self.shape or z.dtype != _CPLX_OF[self.code]:
