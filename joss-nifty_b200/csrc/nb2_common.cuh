@@ -112,4 +112,52 @@ template <typename T> NB2_HD cplx<T> ldc_ro(const cplx<T>* p) {
 #endif
 }
 
+// ---------------------------------------------------------------- 4-wide vector access (16 B / 32 B)
+template <typename T> struct alignas(4 * sizeof(T) > 16 ? 16 : 4 * sizeof(T)) vec4 { T v[4]; };
+
+template <typename T> NB2_HD vec4<T> ld4_stream(const T* p) {
+    vec4<T> r;
+#if defined(__CUDA_ARCH__)
+    if (sizeof(T) == 4) {
+        const float4 t = __ldcs(reinterpret_cast<const float4*>(p));
+        r.v[0] = T(t.x); r.v[1] = T(t.y); r.v[2] = T(t.z); r.v[3] = T(t.w);
+    } else {
+        const double2 t0 = __ldcs(reinterpret_cast<const double2*>(p));
+        const double2 t1 = __ldcs(reinterpret_cast<const double2*>(p) + 1);
+        r.v[0] = T(t0.x); r.v[1] = T(t0.y); r.v[2] = T(t1.x); r.v[3] = T(t1.y);
+    }
+#else
+    for (int i = 0; i < 4; ++i) r.v[i] = p[i];
+#endif
+    return r;
+}
+template <typename T> NB2_HD vec4<T> ld4_ro(const T* p) {
+    vec4<T> r;
+#if defined(__CUDA_ARCH__)
+    if (sizeof(T) == 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+        r.v[0] = T(t.x); r.v[1] = T(t.y); r.v[2] = T(t.z); r.v[3] = T(t.w);
+    } else {
+        const double2 t0 = __ldg(reinterpret_cast<const double2*>(p));
+        const double2 t1 = __ldg(reinterpret_cast<const double2*>(p) + 1);
+        r.v[0] = T(t0.x); r.v[1] = T(t0.y); r.v[2] = T(t1.x); r.v[3] = T(t1.y);
+    }
+#else
+    for (int i = 0; i < 4; ++i) r.v[i] = p[i];
+#endif
+    return r;
+}
+template <typename T> NB2_HD void st4_stream(T* p, const vec4<T>& r) {
+#if defined(__CUDA_ARCH__)
+    if (sizeof(T) == 4) {
+        __stcs(reinterpret_cast<float4*>(p), make_float4(float(r.v[0]), float(r.v[1]), float(r.v[2]), float(r.v[3])));
+    } else {
+        __stcs(reinterpret_cast<double2*>(p), make_double2(double(r.v[0]), double(r.v[1])));
+        __stcs(reinterpret_cast<double2*>(p) + 1, make_double2(double(r.v[2]), double(r.v[3])));
+    }
+#else
+    for (int i = 0; i < 4; ++i) p[i] = r.v[i];
+#endif
+}
+
 }  // namespace nb2

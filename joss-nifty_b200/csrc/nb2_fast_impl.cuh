@@ -33,8 +33,11 @@ int choose_logw(int logn, long long inner) {
     const size_t col = size_t(pitch_of(logn)) * sizeof(cplx<T>);  // bytes per tile column
     int logw = 0;
     while ((1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= 72 * 1024) ++logw;
-    // prefer at least 64-byte row segments when they fit in shared memory
-    const int want = ilog2(64 / sizeof(cplx<T>));
+    // row segments of at least 64 bytes; 128 bytes when consecutive rows are >= 1 MiB apart
+    // (measured on B200, 1024^3 fp32: axis-0 pass 2.26 ms with 128 B vs 2.89 ms with 64 B segments,
+    //  axis-1 pass 1.82 ms with 64 B / two CTAs per SM vs 2.14 ms with 128 B / one CTA per SM)
+    const size_t seg = inner * sizeof(cplx<T>) >= (size_t(1) << 20) ? 128 : 64;
+    const int want = ilog2(seg / sizeof(cplx<T>));
     while (logw < want && (1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= kSmemLimit) ++logw;
     return logw;
 }
@@ -47,7 +50,13 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
     }
     const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
     const long long outer = axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
-    const int logw = choose_logw<T>(logn, inner);
+    int logw = choose_logw<T>(logn, inner);
+    // developer tuning knobs (not part of the API): tile width / alternative radix plan
+    if (const char* e = std::getenv("NB2_STRIDED_LOGW")) {
+        const int v = std::atoi(e);
+        if (v >= 0 && (1ll << v) <= inner) logw = v;
+    }
+    const char* alt = std::getenv("NB2_PLAN10");
     int rc = 0;
 #define NB2_RUN_STRIDED(A, B, C)                                                              \
     {                                                                                         \
@@ -73,7 +82,13 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
             rc = rt_launch<K>(outer * p.tiles_per_outer, nthreads, smem, st, p);              \
         }                                                                                     \
     }
-    NB2_PLAN_SWITCH(logn, NB2_RUN_STRIDED)
+    if (logn == 10 && alt && alt[0] == 'a') {
+        NB2_RUN_STRIDED(16, 4, 16)
+    } else if (logn == 10 && alt && alt[0] == 'b') {
+        NB2_RUN_STRIDED(8, 16, 8)
+    } else {
+        NB2_PLAN_SWITCH(logn, NB2_RUN_STRIDED)
+    }
 #undef NB2_RUN_STRIDED
     return rc;
 }
@@ -82,7 +97,7 @@ template <typename T>
 int choose_G(int logm, long long Q) {
     const size_t row = size_t(pitch_of(logm)) * sizeof(cplx<T>);
     int G = 1;
-    while (G < 16 && 2 * G <= Q && size_t(4 * G) * row <= 72 * 1024) G *= 2;
+    while (G < 16 && 2 * G <= Q && size_t(4 * G) * row <= 36 * 1024) G *= 2;
     return G;
 }
 
@@ -91,7 +106,11 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
              rt_stream st) {
     const int logm = pl->g.logM;
     const RowPairs rp = row_pairs(pl->g);
-    const int G = choose_G<T>(logm, rp.Q);
+    int G = choose_G<T>(logm, rp.Q);
+    if (const char* e = std::getenv("NB2_ROWS_G")) {
+        const int v = std::atoi(e);
+        if (v >= 1 && v <= 16 && 2 * v <= rp.Q + 1) G = v;
+    }
     const long long ctas_per_item = (rp.Q + G - 1) / G;
     const long long grid = ctas_per_item * pl->g.batch;
     const bool want_dot = epi && epi->dot;
@@ -133,7 +152,16 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
         else                                                                                  \
             rc = rt_launch<K>(grid, nthreads, smem, st, p);                                   \
     }
-    NB2_PLAN_SWITCH(logm, NB2_RUN_ROWS)
+    const char* alt = std::getenv("NB2_PLAN9");
+    if (logm == 9 && alt && alt[0] == 'a') {
+        NB2_RUN_ROWS(16, 2, 16)
+    } else if (logm == 9 && alt && alt[0] == 'b') {
+        NB2_RUN_ROWS(8, 8, 8)
+    } else if (logm == 9 && alt && alt[0] == 'c') {
+        NB2_RUN_ROWS(16, 1, 32)
+    } else {
+        NB2_PLAN_SWITCH(logm, NB2_RUN_ROWS)
+    }
 #undef NB2_RUN_ROWS
     if (rc) return rc;
     if (want_dot) {

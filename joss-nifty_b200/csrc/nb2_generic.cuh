@@ -16,6 +16,7 @@ template <typename T>
 struct NaiveDft {
     static constexpr int NPHASES = 1;
     static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
     struct Params {
         const cplx<T>* in;
         cplx<T>* out;
@@ -53,6 +54,7 @@ template <typename T>
 struct RealToCplx {
     static constexpr int NPHASES = 1;
     static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
     struct Params {
         const T* in;
         cplx<T>* out;
@@ -72,6 +74,7 @@ template <typename T>
 struct CplxToHartley {
     static constexpr int NPHASES = 1;
     static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
     struct Params {
         const cplx<T>* in;
         T* out;
@@ -96,6 +99,7 @@ template <typename T>
 struct CplxScale {
     static constexpr int NPHASES = 1;
     static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
     struct Params {
         const cplx<T>* in;
         cplx<T>* out;

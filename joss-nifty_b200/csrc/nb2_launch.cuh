@@ -61,7 +61,7 @@ struct PhaseStep<K, PH, false> {
 };
 
 template <class K>
-__global__ void __launch_bounds__(K::MAX_THREADS) nb2_kernel(const typename K::Params p) {
+__global__ void __launch_bounds__(K::MAX_THREADS, K::MIN_BLOCKS) nb2_kernel(const typename K::Params p) {
     extern __shared__ __align__(16) char nb2_smem[];
     PhaseStep<K, 0>::run(p, nb2_smem, true);
 }

@@ -23,6 +23,23 @@
 #include "nb2_pointwise.cuh"
 #include "nb2_radix.cuh"
 
+// occupancy targets (CTAs per SM) handed to ptxas through __launch_bounds__
+#ifndef NB2_MINB256_F32
+#define NB2_MINB256_F32 1   // radix-32 kernels: compiled for up to 512 threads -> <= 128 registers
+#endif
+#ifndef NB2_MINB512_F32
+#define NB2_MINB512_F32 2   // radix <= 16 kernels, 512 threads: <= 64 registers
+#endif
+#ifndef NB2_MINB256_F64
+#define NB2_MINB256_F64 1
+#endif
+#ifndef NB2_MINB512_F64
+#define NB2_MINB512_F64 1
+#endif
+#ifndef NB2_TWPOW
+#define NB2_TWPOW 1         // 1: inter-step twiddles by binary powering of W^r instead of table loads
+#endif
+
 namespace nb2 {
 
 // shared-memory slot of logical row L (padded so that every step is bank-conflict free)
@@ -33,6 +50,19 @@ template <int R1, int R2, int R3> constexpr int slot_pitch() {
     return R1 * R2 * R3 + R1 * R2 + (R2 > 1 ? R1 : 0);
 }
 
+// w[k] = w1^k for k = 1..R-1 by binary powering (multiplication depth <= log2 R)
+template <int R, typename T> NB2_HD void tw_powers(cplx<T> w1, cplx<T> (&w)[R]) {
+    w[0] = mk<T>(T(1), T(0));
+    if (R > 1) w[1] = w1;
+    NB2_UNROLL
+    for (int k = 2; k < R; ++k) {
+        // largest power of two <= k
+        int hb = 1;
+        while (2 * hb <= k) hb *= 2;
+        w[k] = (k == hb) ? w[hb / 2] * w[hb / 2] : w[hb] * w[k - hb];
+    }
+}
+
 // ============================================================================ StridedPass
 template <typename T, int R1, int R2, int R3>
 struct StridedPass {
@@ -40,7 +70,10 @@ struct StridedPass {
     static constexpr int MM = R2 * R3;
     static constexpr bool SINGLE = (MM == 1);
     static constexpr int NPHASES = 3;
-    static constexpr int MAX_THREADS = (R1 >= 32 || R3 >= 32) ? 256 : 512;
+    static constexpr bool BIG = (R1 >= 32 || R3 >= 32);
+    static constexpr int MAX_THREADS = (BIG && sizeof(T) == 8) ? 256 : 512;
+    static constexpr int MIN_BLOCKS = sizeof(T) == 4 ? (BIG ? NB2_MINB256_F32 : NB2_MINB512_F32)
+                                                     : (MAX_THREADS == 256 ? NB2_MINB256_F64 : NB2_MINB512_F64);
 
     struct Params {
         const cplx<T>* in;
@@ -108,10 +141,18 @@ struct StridedPass {
                     }
                 }
                 fft_reg<R1, true>(x);
+#if NB2_TWPOW
+                cplx<T> wp[R1];
+                if (!SINGLE) tw_powers<R1>(ldc_ro(p.tw + r), wp);
+#endif
                 NB2_UNROLL
                 for (int k1 = 0; k1 < R1; ++k1) {
                     cplx<T> v = x[brev<R1>(k1)];
+#if NB2_TWPOW
+                    if (!SINGLE && k1 != 0) v = v * wp[k1];
+#else
                     if (!SINGLE && k1 != 0) v = v * ldc_ro(p.tw + r * k1);
+#endif
                     if (SINGLE) {
                         stc_stream(p.out + base + c + (long long)k1 * p.inner, v);
                     } else {
@@ -184,7 +225,10 @@ struct RowPass {
     static constexpr int MM = R2 * R3;
     static constexpr int PITCH = slot_pitch<R1, R2, R3>();
     static constexpr int NPHASES = 6;
-    static constexpr int MAX_THREADS = (R1 >= 32 || R3 >= 32) ? 256 : 512;
+    static constexpr bool BIG = (R1 >= 32 || R3 >= 32);
+    static constexpr int MAX_THREADS = (BIG && sizeof(T) == 8) ? 256 : 512;
+    static constexpr int MIN_BLOCKS = sizeof(T) == 4 ? (BIG ? NB2_MINB256_F32 : NB2_MINB512_F32)
+                                                     : (MAX_THREADS == 256 ? NB2_MINB256_F64 : NB2_MINB512_F64);
 
     struct Params {
         const cplx<T>* in;
@@ -254,6 +298,46 @@ struct RowPass {
         return v;
     }
 
+    // epilogue for four consecutive outputs.  `kq`: |k2| of the first element counted from the
+    // nearer end of the last axis -- first half: k2 = kq + i  (mirror length kq + i),
+    // second half: k2 = M + k + i (mirror length M - k - i = kq - i), selected by `down`.
+    template <typename OP>
+    NB2_HD static void epi_quad(const OP& e, vec4<T>& h, int f01, int kq, long long item, long long idx,
+                                double& acc) {
+        const bool down = (idx & (2 * M - 1)) >= M;   // second half of the row: mode length decreases
+        if (e.amp_mode == 1) {
+            NB2_UNROLL
+            for (int i = 0; i < 4; ++i) {
+                const int km = down ? kq - i : kq + i;
+                h.v[i] *= ld_ro(e.amp + f01 + km * km) * e.scale;
+            }
+        } else if (e.amp_mode == 2) {
+            const vec4<T> f = ld4_stream(e.amp + item);
+            NB2_UNROLL
+            for (int i = 0; i < 4; ++i) h.v[i] *= f.v[i] * e.scale;
+        } else {
+            NB2_UNROLL
+            for (int i = 0; i < 4; ++i) h.v[i] *= e.scale;
+        }
+        if (e.mul) {
+            const vec4<T> m = ld4_stream(e.mul + idx);
+            NB2_UNROLL
+            for (int i = 0; i < 4; ++i) h.v[i] *= m.v[i];
+        }
+        NB2_UNROLL
+        for (int i = 0; i < 4; ++i) h.v[i] += e.add_scalar;
+        if (e.add) {
+            const vec4<T> m = ld4_stream(e.add + idx);
+            NB2_UNROLL
+            for (int i = 0; i < 4; ++i) h.v[i] += m.v[i];
+        }
+        if (e.dot) {
+            const vec4<T> m = ld4_stream(e.dot + idx);
+            NB2_UNROLL
+            for (int i = 0; i < 4; ++i) acc += double(m.v[i]) * double(h.v[i]);
+        }
+    }
+
     template <int PH>
     NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
         cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
@@ -299,11 +383,19 @@ struct RowPass {
                 }
                 fft_reg<R1, true>(x);
                 cplx<T>* dst = smem + s * PITCH;
+#if NB2_TWPOW
+                cplx<T> wp[R1];
+                if (MM > 1) tw_powers<R1>(ldc_ro(p.tw + 2 * r), wp);
+#endif
                 NB2_UNROLL
                 for (int k1 = 0; k1 < R1; ++k1) {
                     cplx<T> v = x[brev<R1>(k1)];
                     // W_M^(r k1) = W_2M^(2 r k1)
+#if NB2_TWPOW
+                    if (MM > 1 && k1 != 0) v = v * wp[k1];
+#else
                     if (MM > 1 && k1 != 0) v = v * ldc_ro(p.tw + 2 * r * k1);
+#endif
                     dst[slot_of<R2, R3>(k1 * MM + r)] = v;
                 }
             }
@@ -343,31 +435,68 @@ struct RowPass {
         } else if (PH == 3) {
             // untangle + Hartley combine + epilogue
             double acc = 0.0;
-            const int nb = nslots * M;
             const long long itemrows = 1ll << (p.g.logN0 + p.g.logN1);
             const T sgn = p.conv == NB2_CANONICAL ? T(-1) : T(1);
             int prev_s = -1;
             RowSlot rs{};
-            for (int b = tid; b < nb; b += nthreads) {
-                const int k = b % M, s = b / M;
-                if (s != prev_s) {
-                    rs = slot_info(p, bid, s);
-                    prev_s = s;
+            if (M >= 4) {
+                // four consecutive k per thread: 16/32-byte global accesses
+                constexpr int Q4 = M >= 4 ? M / 4 : 1;
+                const int nb = nslots * Q4;
+                long long rowbase = 0, itembase = 0;
+                int f01 = 0;
+                for (int b = tid; b < nb; b += nthreads) {
+                    const int k = (b % Q4) * 4, s = b / Q4;
+                    if (s != prev_s) {
+                        rs = slot_info(p, bid, s);
+                        prev_s = s;
+                        rowbase = rs.row * (2 * M);
+                        itembase = (rs.row & (itemrows - 1)) * (2 * M);
+                        f01 = int(sq_mirror(rs.k0, p.g.logN0) + sq_mirror(rs.k1, p.g.logN1));
+                    }
+                    if (!rs.valid || rs.dup) continue;
+                    const cplx<T>* za = smem + s * PITCH;
+                    const cplx<T>* zb = smem + (s ^ 1) * PITCH;
+                    vec4<T> h1, h2;
+                    NB2_UNROLL
+                    for (int i = 0; i < 4; ++i) {
+                        const cplx<T> a = za[slot_of_k(k + i)];
+                        const cplx<T> bb = conj(zb[slot_of_k((M - k - i) & (M - 1))]);
+                        const cplx<T> E = a + bb;
+                        const cplx<T> O = mul_mi(a - bb);
+                        const cplx<T> WO = ldc_ro(p.tw + k + i) * O;
+                        const cplx<T> F1 = E + WO, F2 = E - WO;
+                        h1.v[i] = T(0.5) * (F1.re + sgn * F1.im);
+                        h2.v[i] = T(0.5) * (F2.re + sgn * F2.im);
+                    }
+                    epi_quad(p.epi, h1, f01, k, itembase + k, rowbase + k, acc);
+                    epi_quad(p.epi, h2, f01, M - k, itembase + M + k, rowbase + M + k, acc);
+                    st4_stream(p.out + rowbase + k, h1);
+                    st4_stream(p.out + rowbase + M + k, h2);
                 }
-                if (!rs.valid || rs.dup) continue;
-                const cplx<T> a = smem[s * PITCH + slot_of_k(k)];
-                const cplx<T> bb = conj(smem[(s ^ 1) * PITCH + slot_of_k((M - k) & (M - 1))]);
-                const cplx<T> E = a + bb;              // 2 * even-sample spectrum
-                const cplx<T> O = mul_mi(a - bb);      // 2 * odd-sample spectrum
-                const cplx<T> WO = ldc_ro(p.tw + k) * O;
-                const cplx<T> F1 = E + WO, F2 = E - WO;  // 2 F[k], 2 F[k + M]
-                const T h1 = T(0.5) * (F1.re + sgn * F1.im), h2 = T(0.5) * (F2.re + sgn * F2.im);
-                const long long idx = rs.row * (2 * M) + k;
-                const long long item = (rs.row & (itemrows - 1)) * (2 * M) + k;
-                const T o1 = apply_epi(p.epi, p.g, h1, rs.k0, rs.k1, k, item, idx, acc);
-                const T o2 = apply_epi(p.epi, p.g, h2, rs.k0, rs.k1, k + M, item + M, idx + M, acc);
-                st_stream(p.out + idx, o1);
-                st_stream(p.out + idx + M, o2);
+            } else {
+                const int nb = nslots * M;
+                for (int b = tid; b < nb; b += nthreads) {
+                    const int k = b % M, s = b / M;
+                    if (s != prev_s) {
+                        rs = slot_info(p, bid, s);
+                        prev_s = s;
+                    }
+                    if (!rs.valid || rs.dup) continue;
+                    const cplx<T> a = smem[s * PITCH + slot_of_k(k)];
+                    const cplx<T> bb = conj(smem[(s ^ 1) * PITCH + slot_of_k((M - k) & (M - 1))]);
+                    const cplx<T> E = a + bb;              // 2 * even-sample spectrum
+                    const cplx<T> O = mul_mi(a - bb);      // 2 * odd-sample spectrum
+                    const cplx<T> WO = ldc_ro(p.tw + k) * O;
+                    const cplx<T> F1 = E + WO, F2 = E - WO;  // 2 F[k], 2 F[k + M]
+                    const T h1 = T(0.5) * (F1.re + sgn * F1.im), h2 = T(0.5) * (F2.re + sgn * F2.im);
+                    const long long idx = rs.row * (2 * M) + k;
+                    const long long item = (rs.row & (itemrows - 1)) * (2 * M) + k;
+                    const T o1 = apply_epi(p.epi, p.g, h1, rs.k0, rs.k1, k, item, idx, acc);
+                    const T o2 = apply_epi(p.epi, p.g, h2, rs.k0, rs.k1, k + M, item + M, idx + M, acc);
+                    st_stream(p.out + idx, o1);
+                    st_stream(p.out + idx + M, o2);
+                }
             }
             if (p.epi.dot) red[tid] = acc;
         } else if (PH == 4) {

@@ -20,6 +20,14 @@
 
 namespace nb2 {
 
+NB2_HD bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+template <typename... P> NB2_HD bool all_aligned16(P... ps) {
+    bool ok = true;
+    const void* a[] = {static_cast<const void*>(ps)...};
+    for (const void* q : a) ok = ok && (q == nullptr || aligned16(q));
+    return ok;
+}
+
 // Block reduction of NV fp64 values per thread.  `red` holds NV * nthreads doubles.
 // phase A (end of the accumulating phase): red[v * nthreads + tid] = acc[v]
 // phase B: warp 0 folds, phase C: (emulator only) final tree.
@@ -62,6 +70,7 @@ template <typename T>
 struct CgUpdate {
     static constexpr int NPHASES = 3;
     static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
     struct Params {
         T* x;
         T* r;
@@ -83,7 +92,38 @@ struct CgUpdate {
         if (PH == 0) {
             double s0 = 0, s1 = 0, s2 = 0;
             const long long stride = p.nctas * nthreads;
-            for (long long i = bid * nthreads + tid; i < p.n; i += stride) {
+            const long long n4 = all_aligned16(p.x, p.r, p.d, p.q, p.b) ? p.n / 4 : 0;
+            for (long long v = bid * nthreads + tid; v < n4; v += stride) {
+                const long long i = 4 * v;
+                vec4<T> xv, rv;
+                if (p.mode == 0) {
+                    xv = ld4_stream(p.x + i);
+                    rv = ld4_stream(p.r + i);
+                    const vec4<T> dv = ld4_stream(p.d + i), qv = ld4_stream(p.q + i);
+                    NB2_UNROLL
+                    for (int e = 0; e < 4; ++e) {
+                        xv.v[e] -= p.alpha * dv.v[e];
+                        rv.v[e] -= p.alpha * qv.v[e];
+                    }
+                    st4_stream(p.x + i, xv);
+                } else {
+                    xv = ld4_stream(p.x + i);
+                    rv = ld4_stream(p.q + i);
+                }
+                const vec4<T> bv = ld4_stream(p.b + i);
+                if (p.mode != 0) {
+                    NB2_UNROLL
+                    for (int e = 0; e < 4; ++e) rv.v[e] -= bv.v[e];
+                }
+                st4_stream(p.r + i, rv);
+                NB2_UNROLL
+                for (int e = 0; e < 4; ++e) {
+                    s0 += double(rv.v[e]) * double(rv.v[e]);
+                    s1 += double(xv.v[e]) * double(rv.v[e]);
+                    s2 += double(xv.v[e]) * double(bv.v[e]);
+                }
+            }
+            for (long long i = 4 * n4 + bid * nthreads + tid; i < p.n; i += stride) {
                 T xv, rv;
                 if (p.mode == 0) {
                     xv = ld_stream(p.x + i) - p.alpha * ld_stream(p.d + i);
@@ -116,6 +156,7 @@ template <typename T>
 struct Axpby {
     static constexpr int NPHASES = 1;
     static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
     struct Params {
         const T* x;
         T* y;
@@ -128,7 +169,20 @@ struct Axpby {
     template <int PH>
     NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
         const long long stride = p.nctas * nthreads;
-        for (long long i = bid * nthreads + tid; i < p.n; i += stride) {
+        const long long n4 = all_aligned16(p.x, p.y) ? p.n / 4 : 0;
+        for (long long v = bid * nthreads + tid; v < n4; v += stride) {
+            vec4<T> xv = ld4_stream(p.x + 4 * v);
+            if (p.b != T(0)) {
+                const vec4<T> yv = ld4_stream(p.y + 4 * v);
+                NB2_UNROLL
+                for (int e = 0; e < 4; ++e) xv.v[e] = p.a * xv.v[e] + p.b * yv.v[e];
+            } else {
+                NB2_UNROLL
+                for (int e = 0; e < 4; ++e) xv.v[e] = p.a * xv.v[e];
+            }
+            st4_stream(p.y + 4 * v, xv);
+        }
+        for (long long i = 4 * n4 + bid * nthreads + tid; i < p.n; i += stride) {
             const T xv = ld_stream(p.x + i);
             const T yv = p.b == T(0) ? T(0) : p.b * ld_stream(p.y + i);
             st_stream(p.y + i, p.a * xv + yv);
@@ -141,6 +195,7 @@ template <typename T>
 struct Dot {
     static constexpr int NPHASES = 3;
     static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
     struct Params {
         const T* a;
         const T* b;
@@ -156,7 +211,13 @@ struct Dot {
         if (PH == 0) {
             double s = 0;
             const long long stride = p.nctas * nthreads;
-            for (long long i = bid * nthreads + tid; i < p.n; i += stride)
+            const long long n4 = all_aligned16(p.a, p.b) ? p.n / 4 : 0;
+            for (long long v = bid * nthreads + tid; v < n4; v += stride) {
+                const vec4<T> av = ld4_stream(p.a + 4 * v), bv = ld4_stream(p.b + 4 * v);
+                NB2_UNROLL
+                for (int e = 0; e < 4; ++e) s += double(av.v[e]) * double(bv.v[e]);
+            }
+            for (long long i = 4 * n4 + bid * nthreads + tid; i < p.n; i += stride)
                 s += double(ld_stream(p.a + i)) * double(ld_stream(p.b + i));
             red[tid] = s;
         } else if (PH == 1) {
@@ -172,6 +233,7 @@ struct Dot {
 struct FinalReduce {
     static constexpr int NPHASES = 3;
     static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
     struct Params {
         const double* partials;
         long long nparts;
@@ -215,6 +277,7 @@ template <typename T>
 struct Eltwise {
     static constexpr int NPHASES = 3;
     static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
     struct Params {
         const T* in;
         T* out;

@@ -92,7 +92,8 @@ def get():
         import torch
         if not torch.cuda.is_available():
             raise NativeError("niftyb200: no CUDA device available (there is no CPU fallback)")
-        _lib = Library(DEFAULT_PATH, "cuda")
+        # NIFTYB200_LIB: developer knob to load another CUDA build of the same library (tuning)
+        _lib = Library(os.environ.get("NIFTYB200_LIB", DEFAULT_PATH), "cuda")
     return _lib
 
 

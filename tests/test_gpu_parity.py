@@ -80,7 +80,7 @@ def test_metric(shape, dist):
 @pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((16, 16, 16), 1 / 16), ((128, 128), 1 / 128),
                                         ((64, 64, 64), 1 / 64)])
 def test_cg_parity(shape, dist):
-    pc.check_cg_parity(shape, dist)
+    pc.check_cg_parity(shape, dist, strict=int(np.prod(shape)) <= 4096)
 
 
 def test_cg_failure_modes():

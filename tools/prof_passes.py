@@ -1,0 +1,51 @@
+"""Profiling driver: each kernel of the hot path twice on one grid (for ncu / timing).
+Usage: python tools/prof_passes.py [f32|f64] [n] [reps]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "joss-nifty_b200"))
+import torch  # noqa: E402
+import bench  # noqa: E402
+import niftyb200 as nb  # noqa: E402
+from niftyb200.transforms import PointOp  # noqa: E402
+
+dt = sys.argv[1] if len(sys.argv) > 1 else "f32"
+n = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
+reps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
+shape = (n, n, n)
+tdt = torch.float32 if dt == "f32" else torch.float64
+cf, tab, M, j, x0 = bench.setup_problem(nb, torch, shape, tdt)
+plan = cf.plans[0]
+a, b = x0, torch.empty_like(x0)
+cgm = sys.modules["niftyb200.cg"]
+loop = cgm.CGLoop(M, j, x0)
+pro = PointOp(tab.amp_mode, tab.amp, tab.azm)
+epi_f = PointOp(scale=cf.dvol, add_scalar=0.0, mul=M.w)
+curv = torch.zeros((), dtype=torch.float64, device="cuda")
+epi_a = PointOp(tab.amp_mode, tab.amp, tab.azm * cf.dvol, add=x0, dot=x0, dot_out=curv)
+only = os.environ.get("PROF_ONLY")
+cases = [("strided0", lambda: plan.run_pass(0, a, b)), ("strided1", lambda: plan.run_pass(1, a, b)),
+         ("rows", lambda: plan.run_pass(2, a, b)), ("strided0+amp", lambda: plan.run_pass(0, a, b, pro=pro)),
+         ("rows+mul", lambda: plan.run_pass(2, a, b, epi=epi_f)), ("rows+amp+add+dot", lambda: plan.run_pass(2, a, b, epi=epi_a)),
+         ("cg_update", lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r)),
+         ("axpby", lambda: loop.vec.axpby(1.0, loop.r, 1.0, b))]
+for name, fn in cases:
+    if only and not any(name == o for o in only.split(',')):
+        continue
+    fn()
+    if reps == 0:
+        torch.cuda.synchronize()
+        continue
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    N = n ** 3
+    print(f"{name:20s} {ms:8.3f} ms   {2 * N * x0.element_size() / ms / 1e6:8.1f} GB/s (2Ns)", flush=True)
