@@ -83,6 +83,11 @@ int64_t nb2_plan_ksq_size(const nb2_plan* plan);
 int nb2_hartley(nb2_plan* plan, const void* in, void* out, int convention, const nb2_pointop* pro,
                 const nb2_pointop* epi, void* stream);
 
+/* Expand an amp_mode-1 table into the full-size factor field of one batch item,
+ * out[k] = table[ksq(k)] * scale: PowerDistributor.times (src/operators/distributors.py:114-119)
+ * evaluated once per expansion point, for use as an amp_mode-2 field.  Fast-path plans only. */
+int nb2_expand_table(nb2_plan* plan, const void* table, double scale, void* out, void* stream);
+
 /* Profiling / tuning hook: run ONE pass of the fast path (which = 0: strided pass over axis 0,
  * 1: strided pass over axis 1, 2: contiguous row pass with the Hartley combine).  `pro` is
  * honoured by passes 0/1/2, `epi` by pass 2 only.  Fast-path plans only. */

@@ -352,6 +352,26 @@ int nb2_hartley(nb2_plan* pl, const void* in, void* out, int conv, const nb2_poi
                                 : hartley_generic<double>(pl, in, out, conv, pro, epi, st);
 }
 
+int nb2_expand_table(nb2_plan* pl, const void* table, double scale, void* out, void* stream) {
+    if (!pl || !table || !out) {
+        last_error() = "nb2_expand_table: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (!pl->fast) {
+        last_error() = "nb2_expand_table: fast-path plans only";
+        return NB2_ERR_UNSUPPORTED;
+    }
+    const long long n = 1ll << (pl->g.logN0 + pl->g.logN1 + pl->g.logM + 1);
+    const long long grid = vec_grid(n);
+    rt_stream st = (rt_stream)stream;
+    if (pl->dtype == NB2_F32) {
+        ExpandTable<float>::Params p{(const float*)table, (float*)out, (float)scale, pl->g, n, grid};
+        return rt_launch<ExpandTable<float>>(grid, kVecThreads, 0, st, p);
+    }
+    ExpandTable<double>::Params p{(const double*)table, (double*)out, scale, pl->g, n, grid};
+    return rt_launch<ExpandTable<double>>(grid, kVecThreads, 0, st, p);
+}
+
 int nb2_hartley_pass(nb2_plan* pl, int which, const void* in, void* out, int conv, const nb2_pointop* pro,
                      const nb2_pointop* epi, void* stream) {
     if (!pl || !in || !out || which < 0 || which > 2 || (conv != 0 && conv != 1)) {

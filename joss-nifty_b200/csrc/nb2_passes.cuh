@@ -112,32 +112,65 @@ struct StridedPass {
                 NB2_UNROLL
                 for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + (long long)n1 * MM * p.inner);
                 if (p.has_pro) {
-                    long long k0, k1, m;
-                    decode(p.g, base + c, k0, k1, m);
-                    const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
-                    // fixed part of ksq: the non-transformed coordinates
-                    const long long fx = p.axis == 0 ? sq_mirror(k1, p.g.logN1) : sq_mirror(k0, p.g.logN0);
-                    const long long fe = fx + sq_mirror(2 * m, p.g.logM + 1);
-                    const long long fo = fx + sq_mirror(2 * m + 1, p.g.logM + 1);
-                    const int logNrow = p.axis == 0 ? p.g.logN0 : p.g.logN1;
-                    NB2_UNROLL
-                    for (int n1 = 0; n1 < R1; ++n1) {
-                        const long long row = r + (long long)n1 * MM;
-                        T ae, ao;
-                        if (p.pro.amp_mode == 1) {
-                            const long long fr = sq_mirror(row, logNrow);
-                            ae = ld_ro(p.pro.amp + fe + fr) * p.pro.scale;
-                            ao = ld_ro(p.pro.amp + fo + fr) * p.pro.scale;
-                        } else if (p.pro.amp_mode == 2) {
-                            const long long lin = (base + c + row * p.inner) & itemmask;
-                            const cplx<T> f = ldc_stream(reinterpret_cast<const cplx<T>*>(p.pro.amp) + lin);
-                            ae = f.re * p.pro.scale;
-                            ao = f.im * p.pro.scale;
-                        } else {
-                            ae = ao = p.pro.scale;
+                    // amplitude factors are fetched in batches of PB rows, two batches in flight,
+                    // so that their latency overlaps instead of serialising per row
+                    constexpr int PB = R1 >= 8 ? 8 : R1;
+                    constexpr int NBATCH = R1 / PB;
+                    if (p.pro.amp_mode == 2) {
+                        const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
+                        const cplx<T>* fsrc = reinterpret_cast<const cplx<T>*>(p.pro.amp) +
+                                              ((base + c + (long long)r * p.inner) & itemmask);
+                        const long long fstride = (long long)MM * p.inner;
+                        cplx<T> f[2][PB];
+                        NB2_UNROLL
+                        for (int i = 0; i < PB; ++i) f[0][i] = ldc_stream(fsrc + i * fstride);
+                        NB2_UNROLL
+                        for (int g = 0; g < NBATCH; ++g) {
+                            if (g + 1 < NBATCH) {
+                                NB2_UNROLL
+                                for (int i = 0; i < PB; ++i)
+                                    f[(g + 1) & 1][i] = ldc_stream(fsrc + ((g + 1) * PB + i) * fstride);
+                            }
+                            NB2_UNROLL
+                            for (int i = 0; i < PB; ++i) {
+                                x[g * PB + i].re *= f[g & 1][i].re * p.pro.scale;
+                                x[g * PB + i].im *= f[g & 1][i].im * p.pro.scale;
+                            }
                         }
-                        x[n1].re *= ae;
-                        x[n1].im *= ao;
+                    } else if (p.pro.amp_mode == 1) {
+                        long long k0, k1, m;
+                        decode(p.g, base + c, k0, k1, m);
+                        // fixed part of ksq: the non-transformed coordinates
+                        const int fx = int(p.axis == 0 ? sq_mirror(k1, p.g.logN1) : sq_mirror(k0, p.g.logN0));
+                        const T* te = p.pro.amp + fx + int(sq_mirror(2 * m, p.g.logM + 1));
+                        const T* to = p.pro.amp + fx + int(sq_mirror(2 * m + 1, p.g.logM + 1));
+                        const int nrow = 1 << (p.axis == 0 ? p.g.logN0 : p.g.logN1);
+                        T fe[2][PB], fo[2][PB];
+                        NB2_UNROLL
+                        for (int i = 0; i < PB; ++i) {
+                            const int row = r + i * MM, km = row < nrow - row ? row : nrow - row;
+                            fe[0][i] = ld_ro(te + km * km);
+                            fo[0][i] = ld_ro(to + km * km);
+                        }
+                        NB2_UNROLL
+                        for (int g = 0; g < NBATCH; ++g) {
+                            if (g + 1 < NBATCH) {
+                                NB2_UNROLL
+                                for (int i = 0; i < PB; ++i) {
+                                    const int row = r + ((g + 1) * PB + i) * MM, km = row < nrow - row ? row : nrow - row;
+                                    fe[(g + 1) & 1][i] = ld_ro(te + km * km);
+                                    fo[(g + 1) & 1][i] = ld_ro(to + km * km);
+                                }
+                            }
+                            NB2_UNROLL
+                            for (int i = 0; i < PB; ++i) {
+                                x[g * PB + i].re *= fe[g & 1][i] * p.pro.scale;
+                                x[g * PB + i].im *= fo[g & 1][i] * p.pro.scale;
+                            }
+                        }
+                    } else {
+                        NB2_UNROLL
+                        for (int n1 = 0; n1 < R1; ++n1) x[n1] = x[n1] * p.pro.scale;
                     }
                 }
                 fft_reg<R1, true>(x);
@@ -301,40 +334,40 @@ struct RowPass {
     // epilogue for four consecutive outputs.  `kq`: |k2| of the first element counted from the
     // nearer end of the last axis -- first half: k2 = kq + i  (mirror length kq + i),
     // second half: k2 = M + k + i (mirror length M - k - i = kq - i), selected by `down`.
+    // Epilogue for four consecutive outputs, split in two so that every global load is issued
+    // before the shared-memory work of the untangle step and only consumed after it.
+    struct EpiLoads {
+        vec4<T> f, m, a, d;
+    };
+    // `kq`/`down`: mode length along the last axis of element i is kq + i (first half of the
+    // row) or kq - i (second half).
     template <typename OP>
-    NB2_HD static void epi_quad(const OP& e, vec4<T>& h, int f01, int kq, long long item, long long idx,
-                                double& acc) {
-        const bool down = (idx & (2 * M - 1)) >= M;   // second half of the row: mode length decreases
+    NB2_HD static void epi_fetch(const OP& e, EpiLoads& L, int f01, int kq, bool down, long long item,
+                                 long long idx) {
         if (e.amp_mode == 1) {
             NB2_UNROLL
             for (int i = 0; i < 4; ++i) {
                 const int km = down ? kq - i : kq + i;
-                h.v[i] *= ld_ro(e.amp + f01 + km * km) * e.scale;
+                L.f.v[i] = ld_ro(e.amp + f01 + km * km);
             }
         } else if (e.amp_mode == 2) {
-            const vec4<T> f = ld4_stream(e.amp + item);
-            NB2_UNROLL
-            for (int i = 0; i < 4; ++i) h.v[i] *= f.v[i] * e.scale;
-        } else {
-            NB2_UNROLL
-            for (int i = 0; i < 4; ++i) h.v[i] *= e.scale;
+            L.f = ld4_stream(e.amp + item);
         }
-        if (e.mul) {
-            const vec4<T> m = ld4_stream(e.mul + idx);
-            NB2_UNROLL
-            for (int i = 0; i < 4; ++i) h.v[i] *= m.v[i];
-        }
+        if (e.mul) L.m = ld4_stream(e.mul + idx);
+        if (e.add) L.a = ld4_stream(e.add + idx);
+        if (e.dot && e.dot != e.add) L.d = ld4_stream(e.dot + idx);   // the CG curvature reads d once
+    }
+    template <typename OP>
+    NB2_HD static void epi_apply(const OP& e, const EpiLoads& L, vec4<T>& h, double& acc) {
         NB2_UNROLL
-        for (int i = 0; i < 4; ++i) h.v[i] += e.add_scalar;
-        if (e.add) {
-            const vec4<T> m = ld4_stream(e.add + idx);
-            NB2_UNROLL
-            for (int i = 0; i < 4; ++i) h.v[i] += m.v[i];
-        }
-        if (e.dot) {
-            const vec4<T> m = ld4_stream(e.dot + idx);
-            NB2_UNROLL
-            for (int i = 0; i < 4; ++i) acc += double(m.v[i]) * double(h.v[i]);
+        for (int i = 0; i < 4; ++i) {
+            T v = h.v[i] * e.scale;
+            if (e.amp_mode != 0) v *= L.f.v[i];
+            if (e.mul) v *= L.m.v[i];
+            v += e.add_scalar;
+            if (e.add) v += L.a.v[i];
+            if (e.dot) acc += double(e.dot != e.add ? L.d.v[i] : L.a.v[i]) * double(v);
+            h.v[i] = v;
         }
     }
 
@@ -457,6 +490,9 @@ struct RowPass {
                     if (!rs.valid || rs.dup) continue;
                     const cplx<T>* za = smem + s * PITCH;
                     const cplx<T>* zb = smem + (s ^ 1) * PITCH;
+                    EpiLoads L1, L2;
+                    epi_fetch(p.epi, L1, f01, k, false, itembase + k, rowbase + k);
+                    epi_fetch(p.epi, L2, f01, M - k, true, itembase + M + k, rowbase + M + k);
                     vec4<T> h1, h2;
                     NB2_UNROLL
                     for (int i = 0; i < 4; ++i) {
@@ -469,8 +505,8 @@ struct RowPass {
                         h1.v[i] = T(0.5) * (F1.re + sgn * F1.im);
                         h2.v[i] = T(0.5) * (F2.re + sgn * F2.im);
                     }
-                    epi_quad(p.epi, h1, f01, k, itembase + k, rowbase + k, acc);
-                    epi_quad(p.epi, h2, f01, M - k, itembase + M + k, rowbase + M + k, acc);
+                    epi_apply(p.epi, L1, h1, acc);
+                    epi_apply(p.epi, L2, h2, acc);
                     st4_stream(p.out + rowbase + k, h1);
                     st4_stream(p.out + rowbase + M + k, h2);
                 }

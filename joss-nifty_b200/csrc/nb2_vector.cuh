@@ -311,4 +311,37 @@ struct Eltwise {
     }
 };
 
+// ---------------------------------------------------------------- amplitude table -> full-size factor field
+// out[k0,k1,k2] = table[ksq(k0,k1,k2)] * scale  -- the PowerDistributor gather
+// (src/operators/distributors.py:114-119) evaluated once per expansion point, so that the
+// transform passes can stream the factor (amp_mode 2) instead of gathering it per element.
+template <typename T>
+struct ExpandTable {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
+    struct Params {
+        const T* table;
+        T* out;
+        T scale;
+        Geom g;
+        long long n;  // elements of one item (N0*N1*N2)
+        long long nctas;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+        const long long stride = p.nctas * nthreads;
+        const int logN2 = p.g.logM + 1;
+        for (long long i = bid * nthreads + tid; i < p.n; i += stride) {
+            const long long k2 = i & ((1ll << logN2) - 1);
+            const long long k1 = (i >> logN2) & ((1ll << p.g.logN1) - 1);
+            const long long k0 = (i >> (logN2 + p.g.logN1)) & ((1ll << p.g.logN0) - 1);
+            const long long ksq = sq_mirror(k0, p.g.logN0) + sq_mirror(k1, p.g.logN1) + sq_mirror(k2, logN2);
+            p.out[i] = ld_ro(p.table + ksq) * p.scale;
+        }
+    }
+};
+
 }  // namespace nb2

@@ -50,6 +50,7 @@ class Library:
         "nb2_plan_is_fast": (c_int, [c_void_p]),
         "nb2_plan_ksq_size": (c_int64, [c_void_p]),
         "nb2_hartley": (c_int, [c_void_p, c_void_p, c_void_p, c_int, POINTER(PointOp), POINTER(PointOp), c_void_p]),
+        "nb2_expand_table": (c_int, [c_void_p, c_void_p, c_double, c_void_p, c_void_p]),
         "nb2_hartley_pass": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, POINTER(PointOp), POINTER(PointOp),
                                      c_void_p]),
         "nb2_launch_count": (c_int64, []),

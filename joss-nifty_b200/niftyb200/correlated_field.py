@@ -252,6 +252,15 @@ class CorrelatedField:
             full = e if full is None else torch.tensordot(full, e, dims=0)    # outer_amplitude :681-688
         return Tables(2, full.to(self.dtype).contiguous(), azm, amps)
 
+    def streaming_tables(self, tab):
+        """Tables with the gather resolved once: ``field = azm * amp[pindex]`` as a full-size
+        array (one extra N*s of HBM, streamed by the passes instead of a per-element L2 gather).
+        Pays off whenever the same expansion point is applied many times (every CG solve)."""
+        if tab.amp_mode != 1:
+            return tab
+        field = self.plans[0].expand_table(tab.amp, scale=tab.azm)
+        return Tables(2, field, 1.0, tab.amps)
+
     # ---- hot tail ---------------------------------------------------------------------
     def apply_xi(self, xi, tab, out=None, convention=None, offset=None, mul=None):
         """``offset + prod_g (1/V_g) hartley_g(azm * amp[pindex] * xi)`` on device tensors."""

@@ -34,8 +34,10 @@ def poisson_exp_weight(signal):
 class CFMetric:
     """``mat(t) = A H w H A t + t`` on device tensors."""
 
-    def __init__(self, cf, tables, weight, convention=None):
-        self.cf, self.tab, self.convention = cf, tables, convention
+    def __init__(self, cf, tables, weight, convention=None, stream_amplitude=True):
+        self.cf, self.convention = cf, convention
+        # the expansion point is fixed for the whole solve: resolve the amplitude gather once
+        self.tab = cf.streaming_tables(tables) if stream_amplitude else tables
         if tuple(weight.shape) != cf.shape:
             raise ValueError("weight must have the field's shape")
         self.w = weight.to(device=cf.device, dtype=cf.dtype).contiguous()

@@ -134,6 +134,16 @@ class Plan:
         self.lib.check(rc, "nb2_hartley")
         return out
 
+    def expand_table(self, table, scale=1.0, out=None):
+        """Full-size factor field ``table[ksq(k)] * scale`` of one batch item (``nb2_expand_table``)."""
+        nt = len(self.axes)
+        if out is None:
+            out = torch.empty(self.shape[len(self.shape) - nt:], dtype=self.dtype, device=table.device)
+        rc = self.lib.nb2_expand_table(self._h, _ptr(self.lib, table, "table"), float(scale),
+                                       _ptr(self.lib, out, "out"), _stream(table))
+        self.lib.check(rc, "nb2_expand_table")
+        return out
+
     def run_pass(self, which, x, out, convention=None, pro=None, epi=None):
         """Profiling hook: one pass of the fast path (``nb2_hartley_pass``)."""
         cpro = pro.to_c(self.lib) if pro is not None else None

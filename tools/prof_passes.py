@@ -29,6 +29,9 @@ only = os.environ.get("PROF_ONLY")
 cases = [("strided0", lambda: plan.run_pass(0, a, b)), ("strided1", lambda: plan.run_pass(1, a, b)),
          ("rows", lambda: plan.run_pass(2, a, b)), ("strided0+amp", lambda: plan.run_pass(0, a, b, pro=pro)),
          ("rows+mul", lambda: plan.run_pass(2, a, b, epi=epi_f)), ("rows+amp+add+dot", lambda: plan.run_pass(2, a, b, epi=epi_a)),
+         ("strided0+field", lambda: plan.run_pass(0, a, b, pro=PointOp(M.tab.amp_mode, M.tab.amp, M.tab.azm))),
+         ("rows+field+add+dot", lambda: plan.run_pass(2, a, b, epi=PointOp(M.tab.amp_mode, M.tab.amp, M.tab.azm * cf.dvol,
+                                                                             add=x0, dot=x0, dot_out=curv))),
          ("cg_update", lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r)),
          ("axpby", lambda: loop.vec.axpby(1.0, loop.r, 1.0, b))]
 for name, fn in cases:
