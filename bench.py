@@ -154,6 +154,24 @@ def setup_problem(nb, torch, shape, tdt, seed=42):
     return cf, tab, M, j, x0
 
 
+def setup_slab_problem(nb, torch, shape, tdt, seed=42):
+    """Same synthetic problem, slab-decomposed: local parts of w (layout Y) and x0 (layout X)."""
+    mk = nb.CorrelatedFieldMaker("", dtype=tdt)
+    mk.set_amplitude_total_offset(*OFFSET)
+    mk.add_fluctuations(shape, 1.0 / shape[0], **CF_KW, non_parametric_kind="power")
+    cf = nb.SlabCorrelatedField(mk.finalize())
+    rng = np.random.default_rng(43)
+    p = {k: rng.standard_normal(s) for k, s in cf.cf.domain.items() if not k.endswith("xi")}
+    tab = cf.tables(p)
+    gen = torch.Generator(device="cuda").manual_seed(seed)
+    w = torch.exp(0.3 * torch.randn(cf.position_shape, dtype=tdt, device="cuda", generator=gen))
+    M = nb.CFMetric(cf, tab, w)
+    x0 = torch.randn(cf.latent_shape, dtype=tdt, device="cuda", generator=gen)
+    j = M(x0)
+    j.mul_(0.5).add_(x0)
+    return cf, tab, M, j, x0
+
+
 def time_region(torch, dist, fn):
     """barrier + sync, CUDA events on the launching stream, barrier + sync; max over ranks."""
     if dist is not None:
@@ -194,7 +212,10 @@ def run_b200(args):
     N, d = int(np.prod(shape)), len(shape)
     peak, peak_src = peaks()
 
-    cf, tab, M, j, x0 = setup_problem(nb, torch, shape, tdt, seed=42 + rank)
+    if world > 1:
+        cf, tab, M, j, x0 = setup_slab_problem(nb, torch, shape, tdt, seed=42 + rank)
+    else:
+        cf, tab, M, j, x0 = setup_problem(nb, torch, shape, tdt, seed=42)
     loop = cgm.CGLoop(M, j, x0)
     loop.run(args.warmup)
     n0 = lib.nb2_launch_count()
@@ -202,20 +223,30 @@ def run_b200(args):
         ms = time_region(torch, dist, lambda: loop.run(args.steps))
     launches = int(lib.nb2_launch_count() - n0)
     ms_step = ms / args.steps
-    value = world * 1000.0 / ms_step          # replicas: every rank runs its own grid
+    value = 1000.0 / ms_step                  # ONE global grid, slab-decomposed over the ranks when world > 1
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-           "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+           "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
            "config": {"workload": f"3D correlated field {'x'.join(map(str, shape))} metric-CG "
-                                  "(configs[3] grid on one GPU; 1 step = 1 CG iteration = CF fwd + CF adj + fused updates)",
-                      "l2": "inputs larger than L2 (each vector %.2f GB)" % (N * s / 1e9),
-                      "multi_gpu": "independent replicas per rank" if world > 1 else "single GPU"},
+                                  "(configs[3] grid; 1 step = 1 CG iteration = CF fwd + CF adj + fused updates)",
+                      "l2": "inputs larger than L2 (each vector %.2f GB per GPU)" % (N * s / 1e9 / world),
+                      "multi_gpu": (f"slab-decomposed over {world} GPUs: one NCCL all-to-all per transform, "
+                                    "all-reduce of <=3 fp64 scalars per dot") if world > 1 else "single GPU"},
            "gpu_launches": launches, "clocks": clk.summary()}
     B_cg = (4 * d + 13) * N * s                # SURVEY.md 8(d) nominal bytes per CG iteration
-    out["extra"] = {"cg_nominal_bytes": B_cg, "cg_hbm_frac_of_measured": B_cg / (ms_step * 1e-3) / 1e9 / peak}
+    out["extra"] = {"cg_nominal_bytes": B_cg, "cg_hbm_frac_of_measured": B_cg / world / (ms_step * 1e-3) / 1e9 / peak}
+    if world > 1:
+        # combined roofline: max(HBM time of the local share, NVLink time of two all-to-alls)
+        nvl = 770.0   # GB/s per direction per GPU, measured peer copy (B200_PROFILING.md)
+        t_hbm = B_cg / world / (peak * 1e9)
+        t_nvl = 2 * (world - 1) / world * N * s / world / (nvl * 1e9)
+        out["extra"].update({"combined_roofline_ms": max(t_hbm, t_nvl) * 1e3, "t_hbm_ms": t_hbm * 1e3, "t_nvlink_ms": t_nvl * 1e3,
+                             "frac_of_combined_roofline": max(t_hbm, t_nvl) * 1e3 / ms_step, "nvlink_gbs_assumed": nvl})
 
-    if rank == 0:
+    if rank == 0 and world > 1:
+        print(json.dumps(out), flush=True)
+    if rank == 0 and world == 1:
         # ---- per-kernel timing (CUDA events, same stream), applies/s, roofline of the dominant kernel
         plan = cf.plans[0]
         a, b = x0, torch.empty_like(x0)

@@ -72,6 +72,11 @@ int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* ax
 int nb2_plan_destroy(nb2_plan* plan);
 /* 1 if the plan runs on the power-of-two fast path (3 fused passes), 0 for the generic path */
 int nb2_plan_is_fast(const nb2_plan* plan);
+/* Mirror rule of the contiguous (row) pass for slab-decomposed grids: the Hartley partner of
+ * row (k0,k1) is ((N0-k0-shift0) mod N0, (N1-k1-shift1) mod N1).  0 = index negation (a full
+ * axis, default); 1 = pure reflection (the mirror-symmetric local part of a distributed axis,
+ * whose two halves are each other's mirror images).  Fast-path plans only. */
+int nb2_plan_set_mirror(nb2_plan* plan, int shift0, int shift1);
 /* number of entries an amp_mode-1 table must have: 1 + sum_j (N_j/2)^2 ; 0 if not fast */
 int64_t nb2_plan_ksq_size(const nb2_plan* plan);
 

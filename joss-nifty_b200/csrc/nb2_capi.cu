@@ -285,6 +285,7 @@ int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* ax
         pl->g.logN1 = ilog2(n[1]);
         pl->g.logM = ilog2(n[2]) - 1;
         pl->g.batch = 1;
+        pl->g.shift0 = pl->g.shift1 = 0;
         for (int i = 0; i < ndim - pl->naxes; ++i) pl->g.batch *= pl->shape[i];
         const size_t es = dtype == NB2_F32 ? sizeof(cplx<float>) : sizeof(cplx<double>);
         if (pl->g.logN0 > 13 || pl->g.logN1 > 13 || pl->g.logM > 13 || pl->g.logM < 1) fast = false;
@@ -327,6 +328,16 @@ int nb2_plan_destroy(nb2_plan* pl) {
     rt_free(pl->work1);
     for (int t = 0; t < kMaxDim; ++t) rt_free(pl->roots[t]);
     delete pl;
+    return NB2_OK;
+}
+
+int nb2_plan_set_mirror(nb2_plan* pl, int shift0, int shift1) {
+    if (!pl || !pl->fast || (shift0 & ~1) || (shift1 & ~1) || (shift0 && !pl->g.logN0) || (shift1 && !pl->g.logN1)) {
+        last_error() = "nb2_plan_set_mirror: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    pl->g.shift0 = shift0;
+    pl->g.shift1 = shift1;
     return NB2_OK;
 }
 

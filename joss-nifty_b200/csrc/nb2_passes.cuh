@@ -241,7 +241,13 @@ struct RowPairs {
 NB2_HD RowPairs row_pairs(const Geom& g) {
     const long long N0 = 1ll << g.logN0, N1 = 1ll << g.logN1;
     RowPairs rp;
-    rp.h = N1 / 2 + 1;
+    if (g.shift0) {   // no self-mirrored k0: canonical k0 in [0, N0/2), every k1
+        rp.h = 0;
+        rp.nmid = (N0 / 2) * N1;
+        rp.Q = rp.nmid;
+        return rp;
+    }
+    rp.h = g.shift1 ? N1 / 2 : N1 / 2 + 1;
     rp.nmid = N0 >= 2 ? (N0 / 2 - 1) * N1 : 0;
     rp.Q = rp.nmid + (N0 >= 2 ? 2 : 1) * rp.h;
     return rp;
@@ -295,14 +301,14 @@ struct RowPass {
         if (!rs.valid) return rs;
         long long k0, k1;
         if (q < rp.nmid) {
-            k0 = 1 + (q >> p.g.logN1);
+            k0 = (p.g.shift0 ? 0 : 1) + (q >> p.g.logN1);
             k1 = q & (N1 - 1);
         } else {
             const long long qq = q - rp.nmid;
             k0 = (qq / rp.h) ? N0 / 2 : 0;
             k1 = qq % rp.h;
         }
-        const long long k0m = (N0 - k0) & (N0 - 1), k1m = (N1 - k1) & (N1 - 1);
+        const long long k0m = (N0 - k0 - p.g.shift0) & (N0 - 1), k1m = (N1 - k1 - p.g.shift1) & (N1 - 1);
         if (s & 1) {
             rs.dup = (k0m == k0 && k1m == k1);
             k0 = k0m;

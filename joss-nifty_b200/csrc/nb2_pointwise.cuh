@@ -33,6 +33,11 @@ struct PointOp {
 struct Geom {
     int logN0, logN1, logM;   // log2 of N0, N1 and M = N2/2
     long long batch;
+    // Mirror rule of the row pass: the partner of row (k0, k1) is ((N0 - k0 - shift0) mod N0,
+    // (N1 - k1 - shift1) mod N1).  shift = 0: ordinary index negation (a full axis);
+    // shift = 1: pure reflection without fixed points -- a mirror-symmetric LOCAL part of a
+    // slab-decomposed axis (niftyb200/distributed.py), whose two halves are each other's mirrors.
+    int shift0, shift1;
 };
 
 NB2_HD long long sq_mirror(long long k, int logN) {

@@ -29,8 +29,17 @@ N_RESET = 20                           # re/conjugate_gradient.py:18
 
 
 # ---------------------------------------------------------------- fused vector kernels
+def _dot(a, b, comm=None):
+    """sum(a*b) as a Python float; all-reduced over the ranks of a slab-decomposed vector."""
+    t = vdot_device(a, b)
+    if comm is not None:
+        comm.allreduce_(t)
+    return float(t.cpu())
+
+
 class _Vec:
-    def __init__(self, like):
+    def __init__(self, like, comm=None):
+        self.comm = comm
         self.lib = _lib.get()
         if like.dtype not in _TORCH_REAL:
             raise TypeError("CG vectors must be float32 or float64 tensors")
@@ -43,6 +52,8 @@ class _Vec:
         rc = lib.nb2_cg_update(self.code, self.n, mode, float(alpha), _ptr(lib, d), _ptr(lib, q), _ptr(lib, b),
                                _ptr(lib, x), _ptr(lib, r), _ptr(lib, self.sums), _stream(x))
         lib.check(rc, "nb2_cg_update")
+        if self.comm is not None:
+            self.comm.allreduce_(self.sums)      # one all-reduce of three fp64 scalars
         s = self.sums.cpu()
         return float(s[0]), float(s[1]), float(s[2])
 
@@ -61,7 +72,7 @@ def _apply_with_curv(A, d, q):
     res = A(d)
     if res.data_ptr() != q.data_ptr():
         q.copy_(res)
-    return q, float(vdot_device(d, q).cpu())
+    return q, _dot(d, q, getattr(A, "comm", None))
 
 
 def _apply(A, x, out):
@@ -250,14 +261,18 @@ class ConjugateGradient:
 CGResults = namedtuple("CGResults", "x nit nfev info success")
 
 
-def _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord, tol, atol):
+def _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord, tol, atol, comm=None):
     """re/conjugate_gradient.py:93-107."""
     norm_ord = 2 if norm_ord is None else norm_ord
-    maxiter_fallback = 20 * j.numel()
+    maxiter_fallback = 20 * j.numel() * (comm.size if comm is not None else 1)
     miniter = min(6, maxiter if maxiter is not None else maxiter_fallback) if miniter is None else miniter
     maxiter = max(min(200, maxiter_fallback), miniter) if maxiter is None else maxiter
     if absdelta is None and resnorm is None:
-        resnorm = max(tol * float(torch.linalg.vector_norm(j.reshape(-1).double(), ord=norm_ord).cpu()), atol)
+        if comm is not None and norm_ord == 2:
+            jn = float(np.sqrt(_dot(j, j, comm)))
+        else:
+            jn = float(torch.linalg.vector_norm(j.reshape(-1).double(), ord=norm_ord).cpu())
+        resnorm = max(tol * jn, atol)
     fi = np.finfo(np.float32 if j.dtype == torch.float32 else np.float64)
     return norm_ord, miniter, maxiter, resnorm, 6.0 * fi.eps, 6.0 * fi.tiny
 
@@ -269,13 +284,14 @@ def _norm(r, rr, norm_ord):
 
 
 def _cg_setup(mat, j, x0):
-    vec = _Vec(j)
+    comm = getattr(mat, "comm", None)
+    vec = _Vec(j, comm)
     q = torch.empty_like(j)
     if x0 is None:
         pos = torch.zeros_like(j)
         r = -j
         energy, nfev = 0.0, 0
-        gamma = float(vdot_device(r, r).cpu())
+        gamma = _dot(r, r, comm)
     else:
         pos = x0.clone()
         q = _apply(mat, pos, q)
@@ -301,7 +317,7 @@ def cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5,
 def _cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5, atol=0.0, miniter=None,
         maxiter=None, name=None, time_threshold=None, _raise_nonposdef=True, history=None):
     norm_ord, miniter, maxiter, resnorm, eps, tiny = _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord,
-                                                               tol, atol)
+                                                               tol, atol, getattr(mat, "comm", None))
     vec, pos, r, d, q, energy, nfev, previous_gamma = _cg_setup(mat, j, x0)
     info, i = -1, 0
     if previous_gamma == 0:
@@ -374,7 +390,7 @@ def _static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, t
     (``:266-338``) with the same ``info`` bookkeeping (-2 running, -1 error, 0 converged,
     i > 0 iteration limit); the while-loop runs on the host, the state stays on the device."""
     norm_ord, miniter, maxiter, resnorm, eps, tiny = _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord,
-                                                               tol, atol)
+                                                               tol, atol, getattr(mat, "comm", None))
     vec, pos, r, d, q, energy, nfev, gamma = _cg_setup(mat, j, x0)
     info, i = (0 if gamma == 0.0 else -2), 0
     while info < -1:

@@ -38,12 +38,16 @@ class CFMetric:
         self.cf, self.convention = cf, convention
         # the expansion point is fixed for the whole solve: resolve the amplitude gather once
         self.tab = cf.streaming_tables(tables) if stream_amplitude else tables
-        if tuple(weight.shape) != cf.shape:
-            raise ValueError("weight must have the field's shape")
+        # slab-decomposed fields: latent vectors and position-space fields have different local shapes
+        self.latent_shape = tuple(getattr(cf, "latent_shape", cf.shape))
+        self.position_shape = tuple(getattr(cf, "position_shape", cf.shape))
+        self.comm = getattr(cf, "comm", None)
+        if tuple(weight.shape) != self.position_shape:
+            raise ValueError("weight must have the (local) position-space shape")
         self.w = weight.to(device=cf.device, dtype=cf.dtype).contiguous()
-        self._u = torch.empty(cf.shape, dtype=cf.dtype, device=cf.device)
+        self._u = torch.empty(self.position_shape, dtype=cf.dtype, device=cf.device)
         self._curv = torch.zeros((), dtype=torch.float64, device=cf.device)
-        self.shape, self.dtype, self.device = cf.shape, cf.dtype, cf.device
+        self.shape, self.dtype, self.device = self.latent_shape, cf.dtype, cf.device
         self.napply = 0
 
     def forward_weighted(self, t, out):

@@ -134,6 +134,10 @@ class Plan:
         self.lib.check(rc, "nb2_hartley")
         return out
 
+    def set_mirror(self, shift0, shift1):
+        """Mirror rule of the row pass for slab-decomposed grids (``nb2_plan_set_mirror``)."""
+        self.lib.check(self.lib.nb2_plan_set_mirror(self._h, int(shift0), int(shift1)), "nb2_plan_set_mirror")
+
     def expand_table(self, table, scale=1.0, out=None):
         """Full-size factor field ``table[ksq(k)] * scale`` of one batch item (``nb2_expand_table``)."""
         nt = len(self.axes)

@@ -1,0 +1,37 @@
+"""world_size-2 test of the slab-decomposed path on CPU: gloo for the collectives, the kernel
+emulator for the passes (tests/emu/README.md).  The N>1 GPU twin is test_gpu_distributed.py."""
+
+import conftest
+import dist_worker
+
+
+def check(res, strict=True):
+    assert res["err_f"] <= 1e-12 and res["err_a"] <= 1e-12 and res["err_m"] <= 1e-12, res
+    assert res["err_c"] <= 1e-12, res
+    assert res["nit"][0] == res["nit"][1] and res["info"][0] == res["info"][1] and res["nfev"][0] == res["nfev"][1], res
+    assert res["err_x"] <= (1e-8 if strict else 1e-3), res
+
+
+def test_slab_two_ranks_gloo():
+    res = dist_worker.launch(2, "gloo", conftest.build_emulator(), (16, 16, 16))
+    check(res)
+
+
+def test_slab_four_ranks_gloo():
+    res = dist_worker.launch(4, "gloo", conftest.build_emulator(), (16, 16, 8), port=29541)
+    check(res)
+
+
+def test_symmetric_split_is_a_partition():
+    import numpy as np
+    from niftyb200.distributed import SymmetricSplit
+    for N, P in ((16, 1), (16, 2), (64, 4), (1024, 8)):
+        s = SymmetricSplit(N, P)
+        allk = np.concatenate([s.owned(r) for r in range(P)])
+        assert sorted(allk.tolist()) == list(range(N))
+        for r in range(P):
+            own = s.owned(r)
+            n = own.size
+            for l in range(n):
+                lm = (n - l - s.shift(r)) % n
+                assert (N - own[l]) % N == own[lm]        # local mirror rule == global index negation
