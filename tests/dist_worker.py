@@ -27,7 +27,7 @@ def run(rank, world, port, backend, emu_path, shape, result):
         import parity_cases as pc
         from oracle import cg as ocg
         cgm = sys.modules["niftyb200.cg"]
-        dist_ = 1.0 / shape[0]
+        dist_ = tuple(1.0 / s for s in shape)      # isotropic harmonic pixels
         cf, co = pc.make_pair(shape, dist_, torch.float64, kw=pc.GENTLE_KW)
         scf = nb.SlabCorrelatedField(cf)
         ht = scf.ht
