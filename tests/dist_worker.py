@@ -56,8 +56,9 @@ def run(rank, world, port, backend, emu_path, shape, result):
         r = cgm._cg(M, ht.scatter_x(j), ht.scatter_x(x0), **kw)
         ro = ocg.cg_re(Mo, j, x0, **kw)
         err_x = pc.rel(ht.gather_x(r.x), ro.x)
+        window = [ro.nit] + [ocg.cg_re(Mo, pc.perturb(j, sd), x0, **kw).nit for sd in (1, 2, 3, 4)]
         if rank == 0:
-            result.update(err_f=err_f, err_a=err_a, err_m=err_m, err_c=err_c, nit=(r.nit, ro.nit), info=(r.info, ro.info),
+            result.update(window=window, err_f=err_f, err_a=err_a, err_m=err_m, err_c=err_c, nit=(r.nit, ro.nit), info=(r.info, ro.info),
                           nfev=(r.nfev, ro.nfev), err_x=err_x)
     finally:
         dist.destroy_process_group()
