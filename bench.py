@@ -54,13 +54,49 @@ def peaks():
 
 # ---------------------------------------------------------------- clocks during the timed region
 class ClockSampler:
+    """Samples SM clock and throttle reasons of one GPU during the timed region.
+
+    NVML in a thread (10 ms period; the same counters nvidia-smi prints, without its start-up
+    latency, which is longer than a short multi-GPU timed region); `nvidia-smi -lms` as fallback."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index=0):
-        self.rows, self.proc, self.index = [], None, index
+        self.rows, self.proc, self.index, self.stop, self.th = [], None, index, False, None
+
+    def _nvml_handle(self):
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        try:
+            uuid = "GPU-" + str(torch.cuda.get_device_properties(self.index).uuid)
+            return pynvml, pynvml.nvmlDeviceGetHandleByUUID(uuid)
+        except Exception:
+            return pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.index)
+
+    def _poll(self, nv, h):
+        bits = (("hw_slowdown", nv.nvmlClocksThrottleReasonHwSlowdown),
+                ("hw_thermal_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown),
+                ("sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwThermalSlowdown),
+                ("sw_power_cap", nv.nvmlClocksThrottleReasonSwPowerCap))
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        while not self.stop:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.rows.append([str(sm), str(mx)] + ["Active" if mask & b else "Not Active" for _, b in bits])
+            except Exception:
+                pass
+            time.sleep(0.01)
 
     def __enter__(self):
+        try:
+            nv, h = self._nvml_handle()
+            self.th = threading.Thread(target=self._poll, args=(nv, h), daemon=True)
+            self.th.start()
+            return self
+        except Exception:
+            self.th = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -76,12 +112,15 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def __exit__(self, *a):
+        self.stop = True
         if self.proc is not None:
             self.proc.terminate()
             try:
                 self.proc.wait(timeout=2)
             except Exception:
                 self.proc.kill()
+        elif self.th is not None:
+            self.th.join(timeout=1)
 
     def summary(self):
         sm, mx, reasons = [], [], set()
@@ -245,7 +284,11 @@ def run_b200(args):
                              "frac_of_combined_roofline": max(t_hbm, t_nvl) * 1e3 / ms_step, "nvlink_gbs_assumed": nvl})
 
     if rank == 0 and world > 1:
-        print(json.dumps(out), flush=True)
+        ach = B_cg / world / (ms_step * 1e-3) / 1e9
+        out["roofline"] = {"bound": "hbm", "kernel": "whole CG iteration, local share (9 kernels + 2 all-to-alls)",
+                           "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                           "peak_source": peak_src, "algorithmic_bytes_per_launch": B_cg / world}
+        emit(out)
     if rank == 0 and world == 1:
         # ---- per-kernel timing (CUDA events, same stream), applies/s, roofline of the dominant kernel
         plan = cf.plans[0]
@@ -280,13 +323,16 @@ def run_b200(args):
         t_upd = tk(lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r))
         t_axp = tk(lambda: loop.vec.axpby(1.0, loop.r, 1.0, b))
         # the kernels that run inside one CG iteration (the gather variant is reported, not used there)
+        # ALGORITHMIC bytes per launch: every full-size operand once
+        # (the curvature dot re-reads the array that is added, so add+dot count once)
+        kbytes = {k: (2 + ("field" in k) + ("weight" in k) + ("add" in k)) * N * s for k in passes}
         in_step = {k: v for k, v in passes.items() if v and "gather" not in k}
         dom = max(in_step, key=lambda k: in_step[k]) if in_step else None
         if dom:
-            ach = 2 * N * s / (passes[dom] * 1e-3) / 1e9
+            ach = kbytes[dom] / (passes[dom] * 1e-3) / 1e9
             out["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
                                "frac": ach / peak, "traffic": None, "peak_source": peak_src,
-                               "algorithmic_bytes_per_launch": 2 * N * s}
+                               "algorithmic_bytes_per_launch": kbytes[dom]}
         out["extra"].update({
             "fwd_applies_per_s": 1000.0 / t_fwd, "adj_applies_per_s": 1000.0 / t_adj,
             "fwd_adj_pairs_per_s": 1000.0 / (t_fwd + t_adj),
@@ -294,7 +340,7 @@ def run_b200(args):
             "fwd_hbm_frac": 2 * d * N * s / (t_fwd * 1e-3) / 1e9 / peak,
             "adj_hbm_frac": 2 * d * N * s / (t_adj * 1e-3) / 1e9 / peak,
             "kernel_ms": {**{k: v for k, v in passes.items() if v}, "CgUpdate(+3 dots)": t_upd, "Axpby": t_axp},
-            "kernel_hbm_frac": {**{k: 2 * N * s / (v * 1e-3) / 1e9 / peak for k, v in passes.items() if v},
+            "kernel_hbm_frac": {**{k: kbytes[k] / (v * 1e-3) / 1e9 / peak for k, v in passes.items() if v},
                                 "CgUpdate(+3 dots)": 7 * N * s / (t_upd * 1e-3) / 1e9 / peak,
                                 "Axpby": 3 * N * s / (t_axp * 1e-3) / 1e9 / peak}})
         del b
@@ -332,7 +378,7 @@ def run_b200(args):
                                    "sample": f"oracle CG (scipy pocketfft, workers={cores}) at {'x'.join(map(str, cshape))}: "
                                              f"{v:.4f} it/s measured over {t:.1f}s, scaled by N log N to the headline grid",
                                    "measured_value_at_sample": v}
-        print(json.dumps(out), flush=True)
+        emit(out)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -358,11 +404,34 @@ def run_reference(args):
                                       f"own scipy pocketfft branch), {iters} iterations at {'x'.join(map(str, cshape))} in {t:.1f}s"},
            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
-    print(json.dumps(out), flush=True)
+    emit(out)
+
+
+_REAL_STDOUT = None
+
+
+def guard_stdout():
+    """Route fd 1 to stderr for the life of the process so that native libraries (NCCL prints its
+    version banner on stdout) cannot add lines next to the ONE JSON line; emit() writes that line
+    to the real stdout."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(out):
+    line = (json.dumps(out) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        os.write(1, line)
+    else:
+        os.write(_REAL_STDOUT, line)
 
 
 if __name__ == "__main__":
     a = parse_args()
+    guard_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:

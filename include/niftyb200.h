@@ -99,6 +99,16 @@ int nb2_expand_table(nb2_plan* plan, const void* table, double scale, void* out,
 int nb2_hartley_pass(nb2_plan* plan, int which, const void* in, void* out, int convention,
                      const nb2_pointop* pro, const nb2_pointop* epi, void* stream);
 
+/* Slab decomposition (no counterpart in the reference, which shards samples only:
+ * src/utilities.py:295-390): strided pass `which` (0 or 1) whose input and/or output rows are
+ * remapped so that the pack / unpack around the all-to-all costs no extra sweep.  With a table,
+ * row j (0 <= j < N_which) of outer item o starts at complex offset  o * outer_stride + rowoff[j]
+ * (tables are device int64 arrays, offsets in complex elements = pairs of real scalars);
+ * NULL table = natural layout on that side.  Cannot run in place. */
+int nb2_strided_pass_remap(nb2_plan* plan, int which, const void* in, void* out, const nb2_pointop* pro,
+                           const int64_t* in_rowoff, int64_t in_outer_stride, const int64_t* out_rowoff,
+                           int64_t out_outer_stride, void* stream);
+
 /* Total number of kernels this library has launched in the calling process. */
 int64_t nb2_launch_count(void);
 

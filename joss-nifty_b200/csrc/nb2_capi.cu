@@ -401,6 +401,31 @@ int nb2_hartley_pass(nb2_plan* pl, int which, const void* in, void* out, int con
                                 : run_rows<double>(pl, in, out, conv, pro, epi, st);
 }
 
+int nb2_strided_pass_remap(nb2_plan* pl, int which, const void* in, void* out, const nb2_pointop* pro,
+                           const int64_t* in_rowoff, int64_t in_outer_stride, const int64_t* out_rowoff,
+                           int64_t out_outer_stride, void* stream) {
+    if (!pl || !in || !out || which < 0 || which > 1) {
+        last_error() = "nb2_strided_pass_remap: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (!pl->fast || (which == 0 && !pl->g.logN0) || (which == 1 && !pl->g.logN1)) {
+        last_error() = "nb2_strided_pass_remap: pass not part of this plan";
+        return NB2_ERR_UNSUPPORTED;
+    }
+    if ((in_rowoff || out_rowoff) && in == out) {
+        last_error() = "nb2_strided_pass_remap: a remapped pass cannot run in place";
+        return NB2_ERR_ARG;
+    }
+    RowRemap rm;
+    rm.in_rowoff = (const long long*)in_rowoff;
+    rm.in_ostride = in_outer_stride;
+    rm.out_rowoff = (const long long*)out_rowoff;
+    rm.out_ostride = out_outer_stride;
+    rt_stream st = (rt_stream)stream;
+    return pl->dtype == NB2_F32 ? run_strided<float>(pl, which, in, out, pro, st, &rm)
+                                : run_strided<double>(pl, which, in, out, pro, st, &rm);
+}
+
 int64_t nb2_launch_count(void) { return launch_counter(); }
 
 int nb2_c2c(nb2_plan* pl, const void* in, void* out, int forward, double scale, void* stream) {

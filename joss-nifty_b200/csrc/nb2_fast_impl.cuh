@@ -43,7 +43,8 @@ int choose_logw(int logn, long long inner) {
 }
 
 template <typename T>
-int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st) {
+int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st,
+                const RowRemap* rm) {
     const int logn = axis == 0 ? pl->g.logN0 : pl->g.logN1;
     if (logn == 0) {  // nothing to transform; still apply prologue / copy
         return NB2_ERR_ARG;
@@ -72,6 +73,10 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         p.has_pro = pro ? 1 : 0;                                                              \
         p.pro = to_pointop<T>(pro, nullptr);                                                  \
         p.g = pl->g;                                                                          \
+        p.in_rowoff = rm ? rm->in_rowoff : nullptr;                                           \
+        p.out_rowoff = rm ? rm->out_rowoff : nullptr;                                         \
+        p.in_ostride = rm ? rm->in_ostride : 0;                                               \
+        p.out_ostride = rm ? rm->out_ostride : 0;                                             \
         const size_t smem = K::smem_bytes(logw);                                              \
         if (smem > kSmemLimit) {                                                              \
             rc = NB2_ERR_UNSUPPORTED;                                                         \

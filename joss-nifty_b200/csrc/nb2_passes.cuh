@@ -86,6 +86,12 @@ struct StridedPass {
         int has_pro;
         PointOp<T> pro;
         Geom g;
+        // Optional row remapping (slab decomposition: the pack / unpack of the all-to-all is folded
+        // into the pass on either side of the exchange).  With a table, row j of outer item o
+        // starts at  o * ostride + rowoff[j]  instead of  (o * N + j) * inner.
+        const long long* in_rowoff;
+        const long long* out_rowoff;
+        long long in_ostride, out_ostride;
     };
 
     static size_t smem_bytes(int logw) {
@@ -103,14 +109,23 @@ struct StridedPass {
         cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
         const int w = 1 << p.logw;
         const long long base = tile_base(p, bid);
+        const long long tcol = (bid % p.tiles_per_outer) << p.logw;
+        const long long obase = p.out_rowoff ? (bid / p.tiles_per_outer) * p.out_ostride + tcol : base;
         if (PH == 0) {
             const int nb = MM << p.logw;
             for (int b = tid; b < nb; b += nthreads) {
                 const int c = b & (w - 1), r = b >> p.logw;
-                const cplx<T>* src = p.in + base + c + (long long)r * p.inner;
                 cplx<T> x[R1];
-                NB2_UNROLL
-                for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + (long long)n1 * MM * p.inner);
+                if (p.in_rowoff) {
+                    const cplx<T>* src = p.in + (bid / p.tiles_per_outer) * p.in_ostride + tcol + c;
+                    const long long* ro = p.in_rowoff + r;
+                    NB2_UNROLL
+                    for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + ld_ro(ro + n1 * MM));
+                } else {
+                    const cplx<T>* src = p.in + base + c + (long long)r * p.inner;
+                    NB2_UNROLL
+                    for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + (long long)n1 * MM * p.inner);
+                }
                 if (p.has_pro) {
                     // amplitude factors are fetched in batches of PB rows, two batches in flight,
                     // so that their latency overlaps instead of serialising per row
@@ -187,7 +202,7 @@ struct StridedPass {
                     if (!SINGLE && k1 != 0) v = v * ldc_ro(p.tw + r * k1);
 #endif
                     if (SINGLE) {
-                        stc_stream(p.out + base + c + (long long)k1 * p.inner, v);
+                        stc_stream(p.out + obase + c + (p.out_rowoff ? ld_ro(p.out_rowoff + k1) : (long long)k1 * p.inner), v);
                     } else {
                         smem[(slot_of<R2, R3>(k1 * MM + r) << p.logw) + c] = v;
                     }
@@ -223,10 +238,17 @@ struct StridedPass {
                     for (int n3 = 0; n3 < R3; ++n3)
                         x[n3] = smem[(slot_of<R2, R3>(k1 * MM + k2 * R3 + n3) << p.logw) + c];
                     fft_reg<R3, true>(x);
-                    cplx<T>* dst = p.out + base + c + (long long)(k1 + R1 * k2) * p.inner;
-                    NB2_UNROLL
-                    for (int k3 = 0; k3 < R3; ++k3)
-                        stc_stream(dst + (long long)k3 * (R1 * R2) * p.inner, x[brev<R3>(k3)]);
+                    if (p.out_rowoff) {
+                        cplx<T>* dst = p.out + obase + c;
+                        const long long* ro = p.out_rowoff + (k1 + R1 * k2);
+                        NB2_UNROLL
+                        for (int k3 = 0; k3 < R3; ++k3) stc_stream(dst + ld_ro(ro + k3 * (R1 * R2)), x[brev<R3>(k3)]);
+                    } else {
+                        cplx<T>* dst = p.out + base + c + (long long)(k1 + R1 * k2) * p.inner;
+                        NB2_UNROLL
+                        for (int k3 = 0; k3 < R3; ++k3)
+                            stc_stream(dst + (long long)k3 * (R1 * R2) * p.inner, x[brev<R3>(k3)]);
+                    }
                 }
             }
         }

@@ -37,6 +37,14 @@ struct nb2_plan {
 
 namespace nb2 {
 
+// Row remapping of a strided pass (see StridedPass::Params); offsets in complex elements.
+struct RowRemap {
+    const long long* in_rowoff = nullptr;
+    long long in_ostride = 0;
+    const long long* out_rowoff = nullptr;
+    long long out_ostride = 0;
+};
+
 struct PlanDims { int r1, r2, r3; };
 PlanDims plan_dims(int logn);
 int pitch_of(int logn);
@@ -58,7 +66,8 @@ PointOp<T> to_pointop(const nb2_pointop* o, double* partials) {
 
 // fast-path passes (explicitly instantiated for float and double in nb2_fast_*.cu)
 template <typename T>
-int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st);
+int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st,
+                const RowRemap* rm = nullptr);
 template <typename T>
 int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
              rt_stream st);

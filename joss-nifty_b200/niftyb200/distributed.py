@@ -15,8 +15,8 @@ self-mirrored planes ``0`` and ``N/2``).  Two layouts are used:
 * layout X (harmonic side, e.g. ``xi``): axis 0 split, axes 1, 2 complete -- local ``(N0/P, N1, N2)``
 * layout Y (position side, e.g. the signal and the likelihood weight): axis 1 split -- local ``(N0, N1/P, N2)``
 
-A transform X -> Y is: strided pass over axis 1 (local) -> all-to-all -> strided pass over axis 0
-(local) -> row pass (mirror in k0 by index negation, in k1 by reflection inside the local
+A transform X -> Y is: strided pass over axis 1 (local, storing straight into the send blocks) ->
+all-to-all -> strided pass over axis 0 (local, loading straight from the receive blocks) -> row pass (mirror in k0 by index negation, in k1 by reflection inside the local
 symmetric part); Y -> X is the same with the roles of the axes exchanged.  Hartley is symmetric,
 so X -> Y serves the forward apply and Y -> X its adjoint.
 """
@@ -87,31 +87,32 @@ class SlabHartley:
         blk = (P, self.n0, self.n1, N2)
         self.send = torch.empty(blk, dtype=dtype, device=dev)
         self.recv = torch.empty(blk, dtype=dtype, device=dev)
-        self.work_x = torch.empty(self.shape_x, dtype=dtype, device=dev)
-        self.work_y = torch.empty(self.shape_y, dtype=dtype, device=dev)
-        self.perm0 = torch.cat(self.own0)
+        # Row-offset tables (complex elements) that fold the pack / unpack of the exchange into
+        # the strided passes on either side of it (nb2_strided_pass_remap).  The exchange buffers
+        # hold blocks [peer][l0][l1][m]; global plane k0 = own0[q][l0], k1 = own1[q][l1].
+        M = N2 // 2
+        t0 = np.empty(N0, dtype=np.int64)
+        t1 = np.empty(N1, dtype=np.int64)
+        for q in range(P):
+            t0[self.s0.owned(q)] = (q * self.n0 + np.arange(self.n0)) * self.n1 * M
+            t1[self.s1.owned(q)] = (q * self.n0 * self.n1 + np.arange(self.n1)) * M
+        self.rowoff0, self.rowoff1 = torch.from_numpy(t0).to(dev), torch.from_numpy(t1).to(dev)
+        self.ostride1 = self.n1 * M
 
     def x_to_y(self, x, out, convention=None, pro=None, epi=None):
         """Hartley transform of ``x`` (layout X) into ``out`` (layout Y)."""
-        P = self.comm.size
-        z = self.plan_x.run_pass(1, x, self.work_x, convention, pro=pro)           # axis 1, local
-        for q in range(P):                                                          # pack by destination
-            torch.index_select(z, 1, self.own1[q], out=self.send[q])
+        # axis 1 (local), stored straight into the send blocks
+        self.plan_x.run_strided_remap(1, x, self.send, pro, out_rowoff=self.rowoff1, out_ostride=self.ostride1)
         self.comm.all_to_all(self.recv, self.send)                                  # the one exchange
-        out.index_copy_(0, self.perm0, self.recv.view(P * self.n0, self.n1, self.shape[2]))
-        self.plan_y.run_pass(0, out, out, convention)                               # axis 0, local
+        # axis 0 (local), loaded straight from the receive blocks
+        self.plan_y.run_strided_remap(0, self.recv, out, in_rowoff=self.rowoff0)
         return self.plan_y.run_pass(2, out, out, convention, epi=epi)               # rows + Hartley combine
 
     def y_to_x(self, y, out, convention=None, pro=None, epi=None):
         """Hartley transform of ``y`` (layout Y) into ``out`` (layout X)."""
-        P = self.comm.size
-        z = self.plan_y.run_pass(0, y, self.work_y, convention, pro=pro)           # axis 0, local
-        for q in range(P):
-            torch.index_select(z, 0, self.own0[q], out=self.send[q])
+        self.plan_y.run_strided_remap(0, y, self.send, pro, out_rowoff=self.rowoff0)
         self.comm.all_to_all(self.recv, self.send)
-        for s in range(P):
-            out.index_copy_(1, self.own1[s], self.recv[s])
-        self.plan_x.run_pass(1, out, out, convention)                               # axis 1, local
+        self.plan_x.run_strided_remap(1, self.recv, out, in_rowoff=self.rowoff1, in_ostride=self.ostride1)
         return self.plan_x.run_pass(2, out, out, convention, epi=epi)
 
     # ---- host-side helpers: natural global array <-> local parts ----------------------------

@@ -159,6 +159,20 @@ class Plan:
         self.lib.check(rc, "nb2_hartley_pass")
         return out
 
+    def run_strided_remap(self, which, x, out, pro=None, in_rowoff=None, in_ostride=0, out_rowoff=None,
+                          out_ostride=0):
+        """Strided pass ``which`` with remapped rows (``nb2_strided_pass_remap``): the pack / unpack
+        of the slab all-to-all folded into the pass.  Offsets count complex elements."""
+        cpro = pro.to_c(self.lib) if pro is not None else None
+        rc = self.lib.nb2_strided_pass_remap(
+            self._h, int(which), _ptr(self.lib, x, "x"), _ptr(self.lib, out, "out"),
+            ctypes.byref(cpro) if cpro is not None else None,
+            _ptr(self.lib, in_rowoff, "in_rowoff") if in_rowoff is not None else None, int(in_ostride),
+            _ptr(self.lib, out_rowoff, "out_rowoff") if out_rowoff is not None else None, int(out_ostride),
+            _stream(x))
+        self.lib.check(rc, "nb2_strided_pass_remap")
+        return out
+
     def c2c(self, z, forward=True, scale=1.0, out=None):
         """Complex FFT of the complex tensor ``z`` (device) over the plan's axes."""
         if tuple(z.shape) != self.shape or z.dtype != _CPLX_OF[self.code]:
