@@ -104,10 +104,15 @@ int nb2_hartley_pass(nb2_plan* plan, int which, const void* in, void* out, int c
  * remapped so that the pack / unpack around the all-to-all costs no extra sweep.  With a table,
  * row j (0 <= j < N_which) of outer item o starts at complex offset  o * outer_stride + rowoff[j]
  * (tables are device int64 arrays, offsets in complex elements = pairs of real scalars);
- * NULL table = natural layout on that side.  Cannot run in place. */
+ * NULL table = natural layout on that side.  `ncols` > 0 restricts the pass to a subset of the
+ * complex columns of the natural side, so that the exchange can be pipelined in chunks of the
+ * last axis: dense column j (0 <= j < ncols) is natural column
+ * col0 + (j / run) * run_stride + j % run  (run = 0: one run of ncols columns; powers of two);
+ * a remapped side is dense in j.  Cannot run in place when a table is given. */
 int nb2_strided_pass_remap(nb2_plan* plan, int which, const void* in, void* out, const nb2_pointop* pro,
                            const int64_t* in_rowoff, int64_t in_outer_stride, const int64_t* out_rowoff,
-                           int64_t out_outer_stride, void* stream);
+                           int64_t out_outer_stride, int64_t col0, int64_t ncols, int64_t run, int64_t run_stride,
+                           void* stream);
 
 /* Total number of kernels this library has launched in the calling process. */
 int64_t nb2_launch_count(void);

@@ -403,7 +403,8 @@ int nb2_hartley_pass(nb2_plan* pl, int which, const void* in, void* out, int con
 
 int nb2_strided_pass_remap(nb2_plan* pl, int which, const void* in, void* out, const nb2_pointop* pro,
                            const int64_t* in_rowoff, int64_t in_outer_stride, const int64_t* out_rowoff,
-                           int64_t out_outer_stride, void* stream) {
+                           int64_t out_outer_stride, int64_t col0, int64_t ncols, int64_t run, int64_t run_stride,
+                           void* stream) {
     if (!pl || !in || !out || which < 0 || which > 1) {
         last_error() = "nb2_strided_pass_remap: invalid argument";
         return NB2_ERR_ARG;
@@ -411,6 +412,10 @@ int nb2_strided_pass_remap(nb2_plan* pl, int which, const void* in, void* out, c
     if (!pl->fast || (which == 0 && !pl->g.logN0) || (which == 1 && !pl->g.logN1)) {
         last_error() = "nb2_strided_pass_remap: pass not part of this plan";
         return NB2_ERR_UNSUPPORTED;
+    }
+    if (col0 < 0 || ncols < 0 || run < 0 || run_stride < 0) {
+        last_error() = "nb2_strided_pass_remap: negative column range";
+        return NB2_ERR_ARG;
     }
     if ((in_rowoff || out_rowoff) && in == out) {
         last_error() = "nb2_strided_pass_remap: a remapped pass cannot run in place";
@@ -421,6 +426,10 @@ int nb2_strided_pass_remap(nb2_plan* pl, int which, const void* in, void* out, c
     rm.in_ostride = in_outer_stride;
     rm.out_rowoff = (const long long*)out_rowoff;
     rm.out_ostride = out_outer_stride;
+    rm.col0 = col0;
+    rm.ncols = ncols;
+    rm.run = run;
+    rm.run_stride = run_stride;
     rt_stream st = (rt_stream)stream;
     return pl->dtype == NB2_F32 ? run_strided<float>(pl, which, in, out, pro, st, &rm)
                                 : run_strided<double>(pl, which, in, out, pro, st, &rm);

@@ -51,11 +51,18 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
     }
     const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
     const long long outer = axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
+    const long long ncols = (rm && rm->ncols) ? rm->ncols : inner;
+    const long long run = (rm && rm->run) ? rm->run : ncols;
+    if (ncols > inner || (ncols & (ncols - 1)) || (run & (run - 1)) || run > ncols) {
+        last_error() = "strided pass: column subset must consist of power-of-two runs";
+        return NB2_ERR_ARG;
+    }
     int logw = choose_logw<T>(logn, inner);
+    while ((1ll << logw) > run) --logw;
     // developer tuning knobs (not part of the API): tile width / alternative radix plan
     if (const char* e = std::getenv("NB2_STRIDED_LOGW")) {
         const int v = std::atoi(e);
-        if (v >= 0 && (1ll << v) <= inner) logw = v;
+        if (v >= 0 && (1ll << v) <= run) logw = v;
     }
     const char* alt = std::getenv("NB2_PLAN10");
     int rc = 0;
@@ -68,7 +75,7 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         p.tw = (const cplx<T>*)(axis == 0 ? pl->tw0 : pl->tw1);                               \
         p.inner = inner;                                                                      \
         p.logw = logw;                                                                        \
-        p.tiles_per_outer = inner >> logw;                                                    \
+        p.tiles_per_outer = ncols >> logw;                                                    \
         p.axis = axis;                                                                        \
         p.has_pro = pro ? 1 : 0;                                                              \
         p.pro = to_pointop<T>(pro, nullptr);                                                  \
@@ -77,6 +84,9 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         p.out_rowoff = rm ? rm->out_rowoff : nullptr;                                         \
         p.in_ostride = rm ? rm->in_ostride : 0;                                               \
         p.out_ostride = rm ? rm->out_ostride : 0;                                             \
+        p.col0 = rm ? rm->col0 : 0;                                                           \
+        p.run_stride = rm ? rm->run_stride : 0;                                               \
+        p.logrun = ilog2(run);                                                                \
         const size_t smem = K::smem_bytes(logw);                                              \
         if (smem > kSmemLimit) {                                                              \
             rc = NB2_ERR_UNSUPPORTED;                                                         \

@@ -89,9 +89,13 @@ struct StridedPass {
         // Optional row remapping (slab decomposition: the pack / unpack of the all-to-all is folded
         // into the pass on either side of the exchange).  With a table, row j of outer item o
         // starts at  o * ostride + rowoff[j]  instead of  (o * N + j) * inner.
+        // Column subset of the natural side (tiles_per_outer then counts the tiles of the subset;
+        // remapped sides are dense in it): dense column j is natural column
+        //   col0 + (j >> logrun) * run_stride + (j & (run - 1)),  run = 1 << logrun.
         const long long* in_rowoff;
         const long long* out_rowoff;
-        long long in_ostride, out_ostride;
+        long long in_ostride, out_ostride, col0, run_stride;
+        int logrun;
     };
 
     static size_t smem_bytes(int logw) {
@@ -101,7 +105,8 @@ struct StridedPass {
 
     NB2_HD static long long tile_base(const Params& p, long long bid) {
         const long long o = bid / p.tiles_per_outer, tile = bid - o * p.tiles_per_outer;
-        return o * N * p.inner + (tile << p.logw);
+        const long long tc = tile << p.logw;
+        return o * N * p.inner + p.col0 + (tc >> p.logrun) * p.run_stride + (tc & ((1ll << p.logrun) - 1));
     }
 
     template <int PH>

@@ -43,6 +43,9 @@ struct RowRemap {
     long long in_ostride = 0;
     const long long* out_rowoff = nullptr;
     long long out_ostride = 0;
+    // column subset of the natural side: ncols dense columns (0 = every column) in runs of `run`
+    // contiguous columns (0 = one run) whose starts are `run_stride` apart, the first at col0
+    long long col0 = 0, ncols = 0, run = 0, run_stride = 0;
 };
 
 struct PlanDims { int r1, r2, r3; };

@@ -55,7 +55,7 @@ class Library:
         "nb2_hartley_pass": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, POINTER(PointOp), POINTER(PointOp),
                                      c_void_p]),
         "nb2_strided_pass_remap": (c_int, [c_void_p, c_int, c_void_p, c_void_p, POINTER(PointOp), c_void_p, c_int64,
-                                           c_void_p, c_int64, c_void_p]),
+                                           c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_void_p]),
         "nb2_launch_count": (c_int64, []),
         "nb2_c2c": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double, c_void_p]),
         "nb2_vdot": (c_int, [c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),

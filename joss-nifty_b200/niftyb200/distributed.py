@@ -21,6 +21,8 @@ symmetric part); Y -> X is the same with the roles of the axes exchanged.  Hartl
 so X -> Y serves the forward apply and Y -> X its adjoint.
 """
 
+import os
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -59,15 +61,15 @@ class Comm:
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return t
 
-    def all_to_all(self, recv, send):
-        dist.all_to_all_single(recv, send, group=self.group)
-        return recv
+    def all_to_all(self, recv, send, async_op=False):
+        """Returns the work handle when ``async_op`` (the caller ``wait()``s before reading)."""
+        return dist.all_to_all_single(recv, send, group=self.group, async_op=async_op)
 
 
 class SlabHartley:
     """Distributed genuine 3-D Hartley transform between layouts X and Y."""
 
-    def __init__(self, shape, dtype, comm):
+    def __init__(self, shape, dtype, comm, chunks=None):
         if len(shape) != 3:
             raise ValueError("slab decomposition is implemented for 3-D grids")
         self.shape, self.dtype, self.comm = tuple(int(s) for s in shape), dtype, comm
@@ -84,35 +86,61 @@ class SlabHartley:
             raise ValueError("slab decomposition needs power-of-two extents")
         self.plan_x.set_mirror(self.s0.shift(r), 0)
         self.plan_y.set_mirror(0, self.s1.shift(r))
-        blk = (P, self.n0, self.n1, N2)
+        # The exchange is pipelined in `C` chunks of complex columns (last axis): the strided pass
+        # before it stores chunk c straight into its send blocks, the all-to-all of chunk c runs on
+        # NCCL's stream while chunk c+1 is being transformed, and the strided pass after it loads
+        # straight from the receive blocks (nb2_strided_pass_remap) -- no pack / unpack sweeps.
+        M = N2 // 2
+        if chunks is None:
+            chunks = int(os.environ.get("NIFTYB200_SLAB_CHUNKS", "0"))
+        if not chunks:
+            local_bytes = self.n0 * N1 * N2 * torch.empty((), dtype=dtype).element_size()
+            chunks = 4 if (local_bytes >= (64 << 20) and M >= 256) else 1
+        if chunks < 1 or M % chunks or (M // chunks) & (M // chunks - 1):
+            raise ValueError(f"chunks={chunks} must split the {M} complex columns into powers of two")
+        self.chunks, self.mc, self.m = chunks, M // chunks, M
+        blk = (chunks, P, self.n0, self.n1, 2 * self.mc)
         self.send = torch.empty(blk, dtype=dtype, device=dev)
         self.recv = torch.empty(blk, dtype=dtype, device=dev)
-        # Row-offset tables (complex elements) that fold the pack / unpack of the exchange into
-        # the strided passes on either side of it (nb2_strided_pass_remap).  The exchange buffers
-        # hold blocks [peer][l0][l1][m]; global plane k0 = own0[q][l0], k1 = own1[q][l1].
-        M = N2 // 2
+        # row-offset tables (complex elements) into one chunk's blocks [peer][l0][l1][m];
+        # global plane k0 = own0[q][l0], k1 = own1[q][l1]
         t0 = np.empty(N0, dtype=np.int64)
         t1 = np.empty(N1, dtype=np.int64)
         for q in range(P):
-            t0[self.s0.owned(q)] = (q * self.n0 + np.arange(self.n0)) * self.n1 * M
-            t1[self.s1.owned(q)] = (q * self.n0 * self.n1 + np.arange(self.n1)) * M
+            t0[self.s0.owned(q)] = (q * self.n0 + np.arange(self.n0)) * self.n1 * self.mc
+            t1[self.s1.owned(q)] = (q * self.n0 * self.n1 + np.arange(self.n1)) * self.mc
         self.rowoff0, self.rowoff1 = torch.from_numpy(t0).to(dev), torch.from_numpy(t1).to(dev)
-        self.ostride1 = self.n1 * M
+        self.ostride1 = self.n1 * self.mc
+
+    def _exchange(self, before, after):
+        """before(c) fills send[c]; after(c) consumes recv[c]; the all-to-alls overlap both."""
+        works = []
+        for c in range(self.chunks):
+            before(c)
+            works.append(self.comm.all_to_all(self.recv[c], self.send[c], async_op=self.chunks > 1))
+        for c in range(self.chunks):
+            if works[c] is not None:
+                works[c].wait()
+            after(c)
 
     def x_to_y(self, x, out, convention=None, pro=None, epi=None):
         """Hartley transform of ``x`` (layout X) into ``out`` (layout Y)."""
-        # axis 1 (local), stored straight into the send blocks
-        self.plan_x.run_strided_remap(1, x, self.send, pro, out_rowoff=self.rowoff1, out_ostride=self.ostride1)
-        self.comm.all_to_all(self.recv, self.send)                                  # the one exchange
-        # axis 0 (local), loaded straight from the receive blocks
-        self.plan_y.run_strided_remap(0, self.recv, out, in_rowoff=self.rowoff0)
+        mc = self.mc
+        self._exchange(
+            lambda c: self.plan_x.run_strided_remap(1, x, self.send[c], pro, out_rowoff=self.rowoff1,
+                                                    out_ostride=self.ostride1, col0=c * mc, ncols=mc),
+            lambda c: self.plan_y.run_strided_remap(0, self.recv[c], out, in_rowoff=self.rowoff0, col0=c * mc,
+                                                    ncols=self.n1 * mc, run=mc, run_stride=self.m))
         return self.plan_y.run_pass(2, out, out, convention, epi=epi)               # rows + Hartley combine
 
     def y_to_x(self, y, out, convention=None, pro=None, epi=None):
         """Hartley transform of ``y`` (layout Y) into ``out`` (layout X)."""
-        self.plan_y.run_strided_remap(0, y, self.send, pro, out_rowoff=self.rowoff0)
-        self.comm.all_to_all(self.recv, self.send)
-        self.plan_x.run_strided_remap(1, self.recv, out, in_rowoff=self.rowoff1, in_ostride=self.ostride1)
+        mc = self.mc
+        self._exchange(
+            lambda c: self.plan_y.run_strided_remap(0, y, self.send[c], pro, out_rowoff=self.rowoff0, col0=c * mc,
+                                                    ncols=self.n1 * mc, run=mc, run_stride=self.m),
+            lambda c: self.plan_x.run_strided_remap(1, self.recv[c], out, in_rowoff=self.rowoff1,
+                                                    in_ostride=self.ostride1, col0=c * mc, ncols=mc))
         return self.plan_x.run_pass(2, out, out, convention, epi=epi)
 
     # ---- host-side helpers: natural global array <-> local parts ----------------------------

@@ -160,7 +160,7 @@ class Plan:
         return out
 
     def run_strided_remap(self, which, x, out, pro=None, in_rowoff=None, in_ostride=0, out_rowoff=None,
-                          out_ostride=0):
+                          out_ostride=0, col0=0, ncols=0, run=0, run_stride=0):
         """Strided pass ``which`` with remapped rows (``nb2_strided_pass_remap``): the pack / unpack
         of the slab all-to-all folded into the pass.  Offsets count complex elements."""
         cpro = pro.to_c(self.lib) if pro is not None else None
@@ -169,7 +169,7 @@ class Plan:
             ctypes.byref(cpro) if cpro is not None else None,
             _ptr(self.lib, in_rowoff, "in_rowoff") if in_rowoff is not None else None, int(in_ostride),
             _ptr(self.lib, out_rowoff, "out_rowoff") if out_rowoff is not None else None, int(out_ostride),
-            _stream(x))
+            int(col0), int(ncols), int(run), int(run_stride), _stream(x))
         self.lib.check(rc, "nb2_strided_pass_remap")
         return out
 

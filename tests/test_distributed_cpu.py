@@ -23,6 +23,13 @@ def test_slab_two_ranks_gloo():
     check(res)
 
 
+def test_slab_two_ranks_gloo_chunked_exchange(monkeypatch):
+    # the exchange pipelined in 4 column chunks (what large grids use on the GPUs)
+    monkeypatch.setenv("NIFTYB200_SLAB_CHUNKS", "4")
+    res = dist_worker.launch(2, "gloo", conftest.build_emulator(), (16, 8, 32), port=29543)
+    check(res)
+
+
 def test_slab_four_ranks_gloo():
     res = dist_worker.launch(4, "gloo", conftest.build_emulator(), (16, 16, 8), port=29541)
     check(res)
