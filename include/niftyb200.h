@@ -114,6 +114,18 @@ int nb2_strided_pass_remap(nb2_plan* plan, int which, const void* in, void* out,
                            int64_t out_outer_stride, int64_t col0, int64_t ncols, int64_t run, int64_t run_stride,
                            void* stream);
 
+/* Peer-visible device buffers for the slab exchange: with row-offset tables that point into the
+ * peers' mapped buffers (offsets relative to `out`, unified virtual addressing), the strided pass
+ * before the exchange stores its output straight into the other GPUs' memory over NVLink -- the
+ * all-to-all becomes part of the pass.  nb2_device_alloc: plain device allocation whose handle
+ * (64 bytes, CUDA IPC) nb2_ipc_export writes; nb2_ipc_open maps a peer process's buffer into this
+ * process (peer access is enabled on demand) and nb2_ipc_close unmaps it. */
+int nb2_device_alloc(int64_t bytes, void** ptr);
+int nb2_device_free(void* ptr);
+int nb2_ipc_export(void* ptr, void* handle64);
+int nb2_ipc_open(const void* handle64, void** ptr);
+int nb2_ipc_close(void* ptr);
+
 /* Total number of kernels this library has launched in the calling process. */
 int64_t nb2_launch_count(void);
 

@@ -233,6 +233,32 @@ int nb2_version(void) { return 100; }
 const char* nb2_last_error(void) { return last_error().c_str(); }
 int nb2_sm_count(void) { return rt_sm_count(); }
 
+int nb2_device_alloc(int64_t bytes, void** ptr) {
+    if (!ptr || bytes < 0) {
+        last_error() = "nb2_device_alloc: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (ensure_ctx()) return NB2_ERR_CUDA;
+    return rt_malloc(ptr, (size_t)bytes) ? NB2_ERR_CUDA : NB2_OK;
+}
+int nb2_device_free(void* ptr) { return rt_free(ptr) ? NB2_ERR_CUDA : NB2_OK; }
+int nb2_ipc_export(void* ptr, void* handle64) {
+    if (!ptr || !handle64) {
+        last_error() = "nb2_ipc_export: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    return rt_ipc_export(ptr, handle64);
+}
+int nb2_ipc_open(const void* handle64, void** ptr) {
+    if (!ptr || !handle64) {
+        last_error() = "nb2_ipc_open: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (ensure_ctx()) return NB2_ERR_CUDA;
+    return rt_ipc_open(handle64, ptr);
+}
+int nb2_ipc_close(void* ptr) { return ptr ? rt_ipc_close(ptr) : NB2_OK; }
+
 int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* axes, int dtype, nb2_plan** out) {
     if (!out || !shape || ndim < 1 || ndim > kMaxDim || naxes < 0 || naxes > ndim ||
         (dtype != NB2_F32 && dtype != NB2_F64)) {

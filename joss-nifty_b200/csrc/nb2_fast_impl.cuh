@@ -29,14 +29,16 @@ namespace nb2 {
 
 // choose tile width for a strided pass over rows of `inner` complex elements
 template <typename T>
-int choose_logw(int logn, long long inner) {
+int choose_logw(int logn, long long inner, bool remote_out = false) {
     const size_t col = size_t(pitch_of(logn)) * sizeof(cplx<T>);  // bytes per tile column
     int logw = 0;
     while ((1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= 72 * 1024) ++logw;
     // row segments of at least 64 bytes; 128 bytes when consecutive rows are >= 1 MiB apart
     // (measured on B200, 1024^3 fp32: axis-0 pass 2.26 ms with 128 B vs 2.89 ms with 64 B segments,
     //  axis-1 pass 1.82 ms with 64 B / two CTAs per SM vs 2.14 ms with 128 B / one CTA per SM)
-    const size_t seg = inner * sizeof(cplx<T>) >= (size_t(1) << 20) ? 128 : 64;
+    // stores that cross NVLink into a peer's memory (slab exchange): 128 B segments
+    // (2 GPUs, 1024^3 fp32, axis-1 pass with half of the rows remote: 1.52 ms vs 2.42 ms with 64 B)
+    const size_t seg = (remote_out || inner * sizeof(cplx<T>) >= (size_t(1) << 20)) ? 128 : 64;
     const int want = ilog2(seg / sizeof(cplx<T>));
     while (logw < want && (1ll << (logw + 1)) <= inner && (col << (logw + 1)) <= kSmemLimit) ++logw;
     return logw;
@@ -57,7 +59,7 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         last_error() = "strided pass: column subset must consist of power-of-two runs";
         return NB2_ERR_ARG;
     }
-    int logw = choose_logw<T>(logn, inner);
+    int logw = choose_logw<T>(logn, inner, rm && rm->out_rowoff);
     while ((1ll << logw) > run) --logw;
     // developer tuning knobs (not part of the API): tile width / alternative radix plan
     if (const char* e = std::getenv("NB2_STRIDED_LOGW")) {

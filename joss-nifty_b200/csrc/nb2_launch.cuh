@@ -112,6 +112,23 @@ inline int rt_sync(rt_stream s) {
     NB2_CUDA_OK(cudaStreamSynchronize(s));
     return 0;
 }
+// peer-visible allocations: CUDA IPC handles (64 bytes) let the other processes of the box map the
+// buffer, so that a pass can store its output straight into the peers' memory over NVLink
+inline int rt_ipc_export(void* p, void* handle64) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    NB2_CUDA_OK(cudaIpcGetMemHandle((cudaIpcMemHandle_t*)handle64, p));
+    return 0;
+}
+inline int rt_ipc_open(const void* handle64, void** p) {
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, sizeof(h));
+    NB2_CUDA_OK(cudaIpcOpenMemHandle(p, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+inline int rt_ipc_close(void* p) {
+    NB2_CUDA_OK(cudaIpcCloseMemHandle(p));
+    return 0;
+}
 inline int rt_sm_count() {
     int dev = 0, n = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
@@ -159,6 +176,9 @@ inline int rt_h2d(void* d, const void* s, size_t n, rt_stream) { std::memcpy(d, 
 inline int rt_d2h(void* d, const void* s, size_t n, rt_stream) { std::memcpy(d, s, n); return 0; }
 inline int rt_d2d(void* d, const void* s, size_t n, rt_stream) { std::memmove(d, s, n); return 0; }
 inline int rt_sync(rt_stream) { return 0; }
+inline int rt_ipc_export(void*, void*) { last_error() = "peer memory needs the CUDA build"; return -3; }
+inline int rt_ipc_open(const void*, void**) { last_error() = "peer memory needs the CUDA build"; return -3; }
+inline int rt_ipc_close(void*) { return -3; }
 inline int rt_sm_count() { return 4; }
 #endif
 

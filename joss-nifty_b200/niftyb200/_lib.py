@@ -56,6 +56,11 @@ class Library:
                                      c_void_p]),
         "nb2_strided_pass_remap": (c_int, [c_void_p, c_int, c_void_p, c_void_p, POINTER(PointOp), c_void_p, c_int64,
                                            c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_void_p]),
+        "nb2_device_alloc": (c_int, [c_int64, POINTER(c_void_p)]),
+        "nb2_device_free": (c_int, [c_void_p]),
+        "nb2_ipc_export": (c_int, [c_void_p, c_void_p]),
+        "nb2_ipc_open": (c_int, [c_void_p, POINTER(c_void_p)]),
+        "nb2_ipc_close": (c_int, [c_void_p]),
         "nb2_launch_count": (c_int64, []),
         "nb2_c2c": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double, c_void_p]),
         "nb2_vdot": (c_int, [c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),

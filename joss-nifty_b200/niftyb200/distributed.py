@@ -21,13 +21,15 @@ symmetric part); Y -> X is the same with the roles of the axes exchanged.  Hartl
 so X -> Y serves the forward apply and Y -> X its adjoint.
 """
 
+import ctypes
 import os
 
 import numpy as np
 import torch
 import torch.distributed as dist
 
-from .transforms import Plan, PointOp, device as _device
+from . import _lib
+from .transforms import Plan, PointOp, RawPointer, device as _device
 
 
 class SymmetricSplit:
@@ -66,6 +68,64 @@ class Comm:
         return dist.all_to_all_single(recv, send, group=self.group, async_op=async_op)
 
 
+class PeerExchange:
+    """Receive buffers of every rank mapped into every process of the box (CUDA IPC), so that the
+    strided pass before the exchange stores straight into the peers' HBM over NVLink: the
+    all-to-all is part of the pass (``nb2_strided_pass_remap`` with row offsets that point into
+    the peers' buffers).  Two buffers alternate between consecutive transforms; one all-reduce of
+    a single scalar per transform is the barrier that tells a rank its blocks have arrived."""
+
+    NBUF = 2
+
+    def __init__(self, comm, nbytes):
+        self.lib, self.comm, self.nbytes = _lib.get(), comm, int(nbytes)
+        self.own, self.peers, self.turn = [], [], 0
+        handles = []
+        for _ in range(self.NBUF):
+            p = ctypes.c_void_p()
+            self.lib.check(self.lib.nb2_device_alloc(self.nbytes, ctypes.byref(p)), "nb2_device_alloc")
+            h = ctypes.create_string_buffer(64)
+            self.lib.check(self.lib.nb2_ipc_export(p, h), "nb2_ipc_export")
+            self.own.append(p.value)
+            handles.append(h.raw)
+        everyone = [None] * comm.size
+        dist.all_gather_object(everyone, handles, group=comm.group)
+        for b in range(self.NBUF):
+            row = []
+            for q in range(comm.size):
+                if q == comm.rank:
+                    row.append(self.own[b])
+                    continue
+                p = ctypes.c_void_p()
+                self.lib.check(self.lib.nb2_ipc_open(ctypes.create_string_buffer(everyone[q][b], 64), ctypes.byref(p)),
+                               "nb2_ipc_open")
+                row.append(p.value)
+            self.peers.append(row)
+        self.flag = torch.zeros(1, dtype=torch.float32, device=_device())
+
+    def rel(self, b, q, elem):
+        """Offset of rank q's buffer b relative to this rank's buffer b, in elements of `elem` bytes."""
+        d = self.peers[b][q] - self.own[b]
+        assert d % elem == 0
+        return d // elem
+
+    def mine(self, b):
+        return RawPointer(self.own[b])
+
+    def arrive(self):
+        """Stream-ordered barrier: returns (on the stream) once every rank's pass has completed."""
+        self.comm.allreduce_(self.flag)
+
+    def close(self):
+        for b, row in enumerate(self.peers):
+            for q, p in enumerate(row):
+                if q != self.comm.rank:
+                    self.lib.nb2_ipc_close(p)
+        for p in self.own:
+            self.lib.nb2_device_free(p)
+        self.peers, self.own = [], []
+
+
 class SlabHartley:
     """Distributed genuine 3-D Hartley transform between layouts X and Y."""
 
@@ -91,6 +151,10 @@ class SlabHartley:
         # NCCL's stream while chunk c+1 is being transformed, and the strided pass after it loads
         # straight from the receive blocks (nb2_strided_pass_remap) -- no pack / unpack sweeps.
         M = N2 // 2
+        # peer-memory exchange (GPUs of one box): the pass before the exchange stores into the peers
+        use_p2p = os.environ.get("NIFTYB200_SLAB_P2P", "1") != "0" and P > 1 and dev.type == "cuda"
+        if use_p2p:
+            chunks = 1
         if chunks is None:
             chunks = int(os.environ.get("NIFTYB200_SLAB_CHUNKS", "0"))
         if not chunks:
@@ -100,8 +164,8 @@ class SlabHartley:
             raise ValueError(f"chunks={chunks} must split the {M} complex columns into powers of two")
         self.chunks, self.mc, self.m = chunks, M // chunks, M
         blk = (chunks, P, self.n0, self.n1, 2 * self.mc)
-        self.send = torch.empty(blk, dtype=dtype, device=dev)
-        self.recv = torch.empty(blk, dtype=dtype, device=dev)
+        self.send = None if use_p2p else torch.empty(blk, dtype=dtype, device=dev)
+        self.recv = None if use_p2p else torch.empty(blk, dtype=dtype, device=dev)
         # row-offset tables (complex elements) into one chunk's blocks [peer][l0][l1][m];
         # global plane k0 = own0[q][l0], k1 = own1[q][l1]
         t0 = np.empty(N0, dtype=np.int64)
@@ -111,6 +175,21 @@ class SlabHartley:
             t1[self.s1.owned(q)] = (q * self.n0 * self.n1 + np.arange(self.n1)) * self.mc
         self.rowoff0, self.rowoff1 = torch.from_numpy(t0).to(dev), torch.from_numpy(t1).to(dev)
         self.ostride1 = self.n1 * self.mc
+
+        self.peer = None
+        if use_p2p:
+            esz = torch.empty((), dtype=dtype).element_size()
+            self.peer = PeerExchange(comm, P * self.n0 * self.n1 * N2 * esz)
+            self.p2p_x, self.p2p_y = [], []       # per buffer: out-row tables of the pass before the exchange
+            for b in range(PeerExchange.NBUF):
+                tx = np.empty(N1, dtype=np.int64)   # X -> Y: row k1 of plane l0 -> rank q, block `r`
+                ty = np.empty(N0, dtype=np.int64)   # Y -> X: row k0 -> rank q, block `r`
+                for q in range(P):
+                    rel = self.peer.rel(b, q, 2 * esz)
+                    tx[self.s1.owned(q)] = rel + (r * self.n0 * self.n1 + np.arange(self.n1)) * M
+                    ty[self.s0.owned(q)] = rel + (r * self.n0 + np.arange(self.n0)) * self.n1 * M
+                self.p2p_x.append(torch.from_numpy(tx).to(dev))
+                self.p2p_y.append(torch.from_numpy(ty).to(dev))
 
     def _exchange(self, before, after):
         """before(c) fills send[c]; after(c) consumes recv[c]; the all-to-alls overlap both."""
@@ -126,6 +205,15 @@ class SlabHartley:
     def x_to_y(self, x, out, convention=None, pro=None, epi=None):
         """Hartley transform of ``x`` (layout X) into ``out`` (layout Y)."""
         mc = self.mc
+        if self.peer is not None:
+            b = self.peer.turn
+            self.peer.turn = (b + 1) % PeerExchange.NBUF
+            mine = self.peer.mine(b)
+            # axis 1 (local) with the stores going to the owners of the k1 planes, over NVLink
+            self.plan_x.run_strided_remap(1, x, mine, pro, out_rowoff=self.p2p_x[b], out_ostride=self.ostride1)
+            self.peer.arrive()
+            self.plan_y.run_strided_remap(0, mine, out, in_rowoff=self.rowoff0)
+            return self.plan_y.run_pass(2, out, out, convention, epi=epi)
         self._exchange(
             lambda c: self.plan_x.run_strided_remap(1, x, self.send[c], pro, out_rowoff=self.rowoff1,
                                                     out_ostride=self.ostride1, col0=c * mc, ncols=mc),
@@ -136,6 +224,14 @@ class SlabHartley:
     def y_to_x(self, y, out, convention=None, pro=None, epi=None):
         """Hartley transform of ``y`` (layout Y) into ``out`` (layout X)."""
         mc = self.mc
+        if self.peer is not None:
+            b = self.peer.turn
+            self.peer.turn = (b + 1) % PeerExchange.NBUF
+            mine = self.peer.mine(b)
+            self.plan_y.run_strided_remap(0, y, mine, pro, out_rowoff=self.p2p_y[b])
+            self.peer.arrive()
+            self.plan_x.run_strided_remap(1, mine, out, in_rowoff=self.rowoff1, in_ostride=self.ostride1)
+            return self.plan_x.run_pass(2, out, out, convention, epi=epi)
         self._exchange(
             lambda c: self.plan_y.run_strided_remap(0, y, self.send[c], pro, out_rowoff=self.rowoff0, col0=c * mc,
                                                     ncols=self.n1 * mc, run=mc, run_stride=self.m),

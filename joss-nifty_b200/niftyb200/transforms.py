@@ -20,7 +20,19 @@ _REAL_OF = {_lib.F32: torch.float32, _lib.F64: torch.float64}
 _CPLX_OF = {_lib.F32: torch.complex64, _lib.F64: torch.complex128}
 
 
+class RawPointer:
+    """A device address that is not a torch tensor (e.g. a peer GPU's mapped buffer)."""
+
+    def __init__(self, address):
+        self.address = int(address)
+
+    def offset(self, nbytes):
+        return RawPointer(self.address + int(nbytes))
+
+
 def _stream(t):
+    if isinstance(t, RawPointer):
+        return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     if t.device.type == "cuda":
         return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
     return None
@@ -29,6 +41,8 @@ def _stream(t):
 def _ptr(lib, t, what="tensor"):
     if t is None:
         return None
+    if isinstance(t, RawPointer):
+        return ctypes.c_void_p(t.address)
     if not isinstance(t, torch.Tensor):
         raise TypeError(f"{what}: expected a torch.Tensor, got {type(t).__name__}")
     if t.device.type != lib.device_type:
