@@ -81,6 +81,32 @@ template <typename V> NB2_HD V ld_ro(const V* p) {
 #endif
 }
 
+// ---------------------------------------------------------------- asynchronous global -> shared copies
+// cp.async (LDGSTS): the copy engine of the load/store unit moves BYTES (8 or 16) from global
+// to shared memory without passing through registers; commit/wait group the copies so that a
+// persistent CTA can fetch its next tile while it computes on the current one.
+template <int BYTES> NB2_HD void cp_async(void* smem_dst, const void* gmem_src) {
+#if defined(__CUDA_ARCH__)
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    if (BYTES == 16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+#else
+    for (int i = 0; i < BYTES; ++i) ((char*)smem_dst)[i] = ((const char*)gmem_src)[i];
+#endif
+}
+NB2_HD void cp_async_commit() {
+#if defined(__CUDA_ARCH__)
+    asm volatile("cp.async.commit_group;" ::: "memory");
+#endif
+}
+template <int PENDING> NB2_HD void cp_async_wait() {
+#if defined(__CUDA_ARCH__)
+    asm volatile("cp.async.wait_group %0;" ::"n"(PENDING) : "memory");
+#endif
+}
+
 #if defined(__CUDACC__)
 template <typename T> struct vec2_of;
 template <> struct vec2_of<float> { using type = float2; };

@@ -44,6 +44,28 @@ int choose_logw(int logn, long long inner, bool remote_out = false) {
     return logw;
 }
 
+// ---------------------------------------------------------------- pipelined (persistent) launches
+constexpr size_t kPipeSmem = 226 * 1024;
+// number of stage buffers of a persistent CTA (0: do not pipeline); NB2_PIPE=0 / NB2_STAGES=n: tuning knobs
+inline int pipe_stages(size_t stage_bytes) {
+    // measured on B200 (1024^3 fp32): the persistent cp.async variant is slower than many small
+    // CTAs for these passes (fewer compute warps per SM; 8-byte copies for padded fp32 rows), so it
+    // is opt-in (NB2_PIPE=1) and kept for launches that must leave SMs free
+    const char* pe = std::getenv("NB2_PIPE");
+    if (!pe || pe[0] != '1') return 0;
+    int want = 3;
+    if (const char* e = std::getenv("NB2_STAGES")) want = std::atoi(e);
+    while (want >= 2 && stage_bytes * want > kPipeSmem) --want;
+    return want >= 2 ? want : 0;
+}
+inline int pipe_threads(int nthreads, int maxt) {
+    if (const char* e = std::getenv("NB2_THREADS")) {
+        const int v = std::atoi(e);
+        if (v >= 32 && v <= maxt && v % 32 == 0) return v;
+    }
+    return nthreads;
+}
+
 template <typename T>
 int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st,
                 const RowRemap* rm) {
@@ -90,13 +112,25 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         p.run_stride = rm ? rm->run_stride : 0;                                               \
         p.logrun = ilog2(run);                                                                \
         const size_t smem = K::smem_bytes(logw);                                              \
+        p.staged = p.pro_staged = 0;                                                          \
         if (smem > kSmemLimit) {                                                              \
             rc = NB2_ERR_UNSUPPORTED;                                                         \
         } else {                                                                              \
             const long long nb1 = (long long)(B * C) << logw;                                 \
-            const int maxt = K::MAX_THREADS;                                \
-            const int nthreads = std::min(maxt, round32(nb1));                                \
-            rc = rt_launch<K>(outer * p.tiles_per_outer, nthreads, smem, st, p);              \
+            const int maxt = K::MAX_THREADS;                                                  \
+            const int nthreads = pipe_threads(std::min(maxt, round32(nb1)), maxt);            \
+            const long long ntiles = outer * p.tiles_per_outer;                               \
+            const bool field = pro && pro->amp_mode == 2;                                     \
+            const size_t stage = smem * (field ? 2 : 1);                                      \
+            const int stages = pipe_stages(stage);                                            \
+            if (!K::SINGLE && stages && ntiles >= 4ll * rt_sm_count() &&                      \
+                (sizeof(cplx<T>) << logw) >= 16 && aligned16(in) && (!field || aligned16(pro->amp))) { \
+                p.staged = 1;                                                                 \
+                p.pro_staged = field ? 1 : 0;                                                 \
+                rc = rt_launch_pipe<K>(ntiles, 0, nthreads, stage, stages, st, p);            \
+            } else {                                                                          \
+                rc = rt_launch<K>(ntiles, nthreads, smem, st, p);                             \
+            }                                                                                 \
         }                                                                                     \
     }
     if (logn == 10 && alt && alt[0] == 'a') {
@@ -161,13 +195,19 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
         p.pro = to_pointop<T>(pro, nullptr);                                                  \
         p.epi = to_pointop<T>(epi, pl->partials);                                             \
         const long long nb1 = (long long)2 * G * B * C;                                       \
-        const int maxt = K::MAX_THREADS;                                    \
-        const int nthreads = std::min(maxt, round32(nb1));                                    \
-        const size_t smem = K::smem_bytes(G, nthreads);                                       \
-        if (smem > kSmemLimit)                                                                \
+        const int maxt = K::MAX_THREADS;                                                      \
+        const int nthreads = pipe_threads(std::min(maxt, round32(nb1)), maxt);                \
+        const size_t smem = (K::smem_bytes(G, nthreads) + 15) & ~size_t(15);                  \
+        const int stages = pipe_stages(smem);                                                 \
+        p.staged = 0;                                                                         \
+        if (smem > kSmemLimit) {                                                              \
             rc = NB2_ERR_UNSUPPORTED;                                                         \
-        else                                                                                  \
+        } else if (stages && grid >= 4ll * rt_sm_count() && aligned16(in)) {                  \
+            p.staged = 1;                                                                     \
+            rc = rt_launch_pipe<K>(grid, 0, nthreads, smem, stages, st, p);                   \
+        } else {                                                                              \
             rc = rt_launch<K>(grid, nthreads, smem, st, p);                                   \
+        }                                                                                     \
     }
     const char* alt = std::getenv("NB2_PLAN9");
     if (logm == 9 && alt && alt[0] == 'a') {

@@ -69,6 +69,7 @@ struct StridedPass {
     static constexpr int N = R1 * R2 * R3;
     static constexpr int MM = R2 * R3;
     static constexpr bool SINGLE = (MM == 1);
+    static constexpr int TPITCH = slot_pitch<R1, R2, R3>();
     static constexpr int NPHASES = 3;
     static constexpr bool BIG = (R1 >= 32 || R3 >= 32);
     static constexpr int MAX_THREADS = (BIG && sizeof(T) == 8) ? 256 : 512;
@@ -96,6 +97,9 @@ struct StridedPass {
         const long long* out_rowoff;
         long long in_ostride, out_ostride, col0, run_stride;
         int logrun;
+        // pipelined launch (nb2_kernel_pipe): the tile -- and, with pro_staged, the amplitude
+        // field tile behind it -- has been copied into the stage buffer by prefetch()
+        int staged, pro_staged;
     };
 
     static size_t smem_bytes(int logw) {
@@ -107,6 +111,28 @@ struct StridedPass {
         const long long o = bid / p.tiles_per_outer, tile = bid - o * p.tiles_per_outer;
         const long long tc = tile << p.logw;
         return o * N * p.inner + p.col0 + (tc >> p.logrun) * p.run_stride + (tc & ((1ll << p.logrun) - 1));
+    }
+
+    // asynchronous copy of tile `bid` into a stage buffer, in the padded slot layout phase 0 works in
+    NB2_HD static void prefetch(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
+        constexpr int CH = 16 / sizeof(cplx<T>) > 0 ? 16 / sizeof(cplx<T>) : 1;   // elements per 16-byte copy
+        const int logcpr = p.logw - (CH == 2 ? 1 : 0);                              // log2(copies per row)
+        const long long base = tile_base(p, bid);
+        const long long tcol = (bid % p.tiles_per_outer) << p.logw;
+        const cplx<T>* src0 = p.in_rowoff ? p.in + (bid / p.tiles_per_outer) * p.in_ostride + tcol : p.in + base;
+        const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
+        const long long tile_elems = (long long)TPITCH << p.logw;
+        const int total = N << logcpr;
+        for (int i = tid; i < total; i += nthreads) {
+            const int row = i >> logcpr, cc = (i & ((1 << logcpr) - 1)) * CH;
+            const long long roff = p.in_rowoff ? ld_ro(p.in_rowoff + row) : (long long)row * p.inner;
+            cplx<T>* dst = smem + (slot_of<R2, R3>(row) << p.logw) + cc;
+            cp_async<16>(dst, src0 + roff + cc);
+            if (p.pro_staged)
+                cp_async<16>(dst + tile_elems, reinterpret_cast<const cplx<T>*>(p.pro.amp) +
+                                                   ((base + (long long)row * p.inner + cc) & itemmask));
+        }
     }
 
     template <int PH>
@@ -121,7 +147,10 @@ struct StridedPass {
             for (int b = tid; b < nb; b += nthreads) {
                 const int c = b & (w - 1), r = b >> p.logw;
                 cplx<T> x[R1];
-                if (p.in_rowoff) {
+                if (p.staged) {
+                    NB2_UNROLL
+                    for (int n1 = 0; n1 < R1; ++n1) x[n1] = smem[(slot_of<R2, R3>(r + n1 * MM) << p.logw) + c];
+                } else if (p.in_rowoff) {
                     const cplx<T>* src = p.in + (bid / p.tiles_per_outer) * p.in_ostride + tcol + c;
                     const long long* ro = p.in_rowoff + r;
                     NB2_UNROLL
@@ -136,7 +165,15 @@ struct StridedPass {
                     // so that their latency overlaps instead of serialising per row
                     constexpr int PB = R1 >= 8 ? 8 : R1;
                     constexpr int NBATCH = R1 / PB;
-                    if (p.pro.amp_mode == 2) {
+                    if (p.pro.amp_mode == 2 && p.pro_staged) {
+                        const cplx<T>* fs = smem + ((long long)TPITCH << p.logw);
+                        NB2_UNROLL
+                        for (int n1 = 0; n1 < R1; ++n1) {
+                            const cplx<T> f = fs[(slot_of<R2, R3>(r + n1 * MM) << p.logw) + c];
+                            x[n1].re *= f.re * p.pro.scale;
+                            x[n1].im *= f.im * p.pro.scale;
+                        }
+                    } else if (p.pro.amp_mode == 2) {
                         const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
                         const cplx<T>* fsrc = reinterpret_cast<const cplx<T>*>(p.pro.amp) +
                                               ((base + c + (long long)r * p.inner) & itemmask);
@@ -307,6 +344,7 @@ struct RowPass {
         int has_pro;
         PointOp<T> pro;
         PointOp<T> epi;
+        int staged;   // pipelined launch: prefetch() has copied the rows into the stage buffer
     };
 
     static size_t smem_bytes(int G, int nthreads) {
@@ -351,6 +389,23 @@ struct RowPass {
         const int k1 = k % R1, rest = k / R1;
         const int k2 = rest % R2, k3 = rest / R2;
         return slot_of<R2, R3>(k1 * MM + k2 * R3 + k3);
+    }
+
+    // asynchronous copy of the 2G rows of tile `bid` into a stage buffer (padded slot layout)
+    NB2_HD static void prefetch(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
+        const int total = 2 * p.G * M;
+        int prev_s = -1;
+        RowSlot rs{};
+        for (int i = tid; i < total; i += nthreads) {
+            const int s = i / M, L = i % M;
+            if (s != prev_s) {
+                rs = slot_info(p, bid, s);
+                prev_s = s;
+            }
+            if (!rs.valid) continue;
+            cp_async<(int)sizeof(cplx<T>)>(smem + s * PITCH + slot_of<R2, R3>(L), p.in + rs.row * M + L);
+        }
     }
 
     template <typename OP>
@@ -420,10 +475,16 @@ struct RowPass {
                     prev_s = s;
                 }
                 if (!rs.valid) continue;
-                const cplx<T>* src = p.in + rs.row * M + r;
                 cplx<T> x[R1];
-                NB2_UNROLL
-                for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + n1 * MM);
+                if (p.staged) {
+                    const cplx<T>* src = smem + s * PITCH;
+                    NB2_UNROLL
+                    for (int n1 = 0; n1 < R1; ++n1) x[n1] = src[slot_of<R2, R3>(r + n1 * MM)];
+                } else {
+                    const cplx<T>* src = p.in + rs.row * M + r;
+                    NB2_UNROLL
+                    for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + n1 * MM);
+                }
                 if (p.has_pro) {
                     const long long N0N1 = 1ll << (p.g.logN0 + p.g.logN1);
                     const long long rowitem = rs.row & (N0N1 - 1);

@@ -71,3 +71,16 @@ def test_cg_parity(shape, dist):
 
 def test_cg_failure_modes():
     pc.check_cg_failure_modes()
+
+
+@pytest.mark.parametrize("stages", ["2", "3"])
+def test_pipelined_passes(monkeypatch, stages):
+    # narrow tiles -> many tiles per pass -> the persistent, software-pipelined launch
+    # (prefetch into stage buffers + staged phase 0), incl. the prefetched amplitude field
+    monkeypatch.setenv("NB2_STRIDED_LOGW", "1")
+    monkeypatch.setenv("NB2_ROWS_G", "1")
+    monkeypatch.setenv("NB2_STAGES", stages)
+    monkeypatch.setenv("NB2_PIPE", "1")
+    pc.check_hartley_shapes([((64, 16), None), ((16, 64, 8), None), ((64, 2, 128), None)])
+    pc.check_metric((64, 64), 1 / 64)
+    pc.check_metric((16, 32, 16), (1 / 16, 1 / 32, 1 / 16), np.float32)

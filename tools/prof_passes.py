@@ -34,6 +34,9 @@ cases = [("strided0", lambda: plan.run_pass(0, a, b)), ("strided1", lambda: plan
                                                                              add=x0, dot=x0, dot_out=curv))),
          ("cg_update", lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r)),
          ("axpby", lambda: loop.vec.axpby(1.0, loop.r, 1.0, b))]
+if os.environ.get("PROF_NCU"):
+    torch.cuda.synchronize()
+    torch.cuda.profiler.start()
 for name, fn in cases:
     if only and not any(name == o for o in only.split(',')):
         continue
