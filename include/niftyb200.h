@@ -59,6 +59,14 @@ typedef struct nb2_pointop {
     double add_scalar;
     const void* dot;
     double* dot_out;
+    /* Spectrum cotangent of the correlated field (epilogue of a fast-path nb2_hartley only):
+     * bin_out[ksq(i)] += bin_x[i] * (transform[i] * scale), i.e. the value BEFORE the amplitude
+     * factor, binned by the integer squared mode length -- PowerDistributor.adjoint_times
+     * (src/operators/distributors.py:105-112 via special_add_at, src/utilities.py:223-240) in the
+     * ksq parametrisation of the bins (nb2_plan_ksq_size entries, fp64, accumulated with atomics:
+     * zero it first).  NULL = off. */
+    const void* bin_x;
+    double* bin_out;
 } nb2_pointop;
 
 int nb2_version(void);
@@ -72,6 +80,11 @@ int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* ax
 int nb2_plan_destroy(nb2_plan* plan);
 /* 1 if the plan runs on the power-of-two fast path (3 fused passes), 0 for the generic path */
 int nb2_plan_is_fast(const nb2_plan* plan);
+/* 0: generic path; 1: fast path over the trailing axes (3 fused passes); 2: fast path over 1-2
+ * leading axes with a contiguous inner batch (product spaces, e.g. the spatial sub-space of a
+ * space x frequency field: HarmonicTransformOperator(..., space=0),
+ * src/library/correlated_fields.py:790-793): strided passes + one mirror-combine pass. */
+int nb2_plan_kind(const nb2_plan* plan);
 /* Mirror rule of the contiguous (row) pass for slab-decomposed grids: the Hartley partner of
  * row (k0,k1) is ((N0-k0-shift0) mod N0, (N1-k1-shift1) mod N1).  0 = index negation (a full
  * axis, default); 1 = pure reflection (the mirror-symmetric local part of a distributed axis,

@@ -4,6 +4,7 @@
 // same file builds the sequential thread emulator used by the CPU-only index tests.
 #include "nb2_generic.cuh"
 #include "nb2_plan.h"
+#include "nb2_passes.cuh"
 #include "nb2_vector.cuh"
 
 using namespace nb2;
@@ -99,6 +100,62 @@ int hartley_fast(nb2_plan* pl, const void* in, void* out, int conv, const nb2_po
         p = nullptr;
     }
     return run_rows<T>(pl, cur, out, conv, p, epi, st);
+}
+
+// leading axes + inner batch (product spaces): strided passes, then the mirror combine
+template <typename T>
+int hartley_inner(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
+                  rt_stream st) {
+    if ((pro && pro->amp_mode == 1) || (epi && epi->amp_mode == 1)) {
+        last_error() = "amp_mode 1 (ksq table) needs a transform over the trailing axes";
+        return NB2_ERR_UNSUPPORTED;
+    }
+    const void* cur = in;
+    const nb2_pointop* p = pro;
+    int rc;
+    if (pl->g.logN0 > 0) {
+        if ((rc = run_strided<T>(pl, 0, cur, out, p, st))) return rc;
+        cur = out;
+        p = nullptr;
+    }
+    if (pl->g.logN1 > 0) {
+        if ((rc = run_strided<T>(pl, 1, cur, out, p, st))) return rc;
+        cur = out;
+        p = nullptr;
+    }
+    if (p) {
+        last_error() = "prologue without a transformed axis";
+        return NB2_ERR_UNSUPPORTED;
+    }
+    const RowPairs rp = row_pairs(pl->g);
+    const long long work = pl->g.batch * rp.Q << pl->g.logM;
+    const long long grid = vec_grid(work);
+    const bool want_dot = epi && epi->dot;
+    if (want_dot) {
+        if (!epi->dot_out) {
+            last_error() = "nb2_pointop.dot set without dot_out";
+            return NB2_ERR_ARG;
+        }
+        if (grid > pl->npartials) {
+            rt_sync(st);
+            rt_free(pl->partials);
+            pl->partials = nullptr;
+            pl->npartials = 0;
+            if (rt_malloc((void**)&pl->partials, grid * sizeof(double))) return NB2_ERR_CUDA;
+            pl->npartials = grid;
+        }
+    }
+    typename MirrorCombine<T>::Params mp;
+    mp.in = (const cplx<T>*)cur;
+    mp.out = (T*)out;
+    mp.g = pl->g;
+    mp.conv = conv;
+    mp.epi = to_pointop<T>(epi, pl->partials);
+    mp.nctas = grid;
+    rc = rt_launch<MirrorCombine<T>>(grid, kVecThreads, MirrorCombine<T>::smem_bytes(kVecThreads), st, mp);
+    if (rc) return rc;
+    if (want_dot) rc = launch_final_reduce(pl->partials, grid, 1, epi->dot_out, st);
+    return rc;
 }
 
 // ---------------------------------------------------------------- generic path
@@ -320,7 +377,42 @@ int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* ax
         if (fast && size_t(2 * pitch_of(pl->g.logM)) * es + 2048 > kSmemLimit) fast = false;
     }
     pl->fast = fast;
+    // ---- leading 1..2 contiguous axes with an even power-of-two-pairs inner batch
+    if (!fast && pl->naxes >= 1 && pl->naxes <= 2 && pl->axes[pl->naxes - 1] < ndim - 1 &&
+        (pl->naxes == 1 || pl->axes[1] == pl->axes[0] + 1)) {
+        long long innerB = 1, outerB = 1;
+        for (int i = pl->axes[pl->naxes - 1] + 1; i < ndim; ++i) innerB *= pl->shape[i];
+        for (int i = 0; i < pl->axes[0]; ++i) outerB *= pl->shape[i];
+        bool ok = innerB >= 2 && innerB % 2 == 0 && is_pow2(innerB / 2);
+        long long n[2] = {1, 1};
+        for (int i = 0; i < pl->naxes; ++i) {
+            n[2 - pl->naxes + i] = pl->shape[pl->axes[i]];
+            if (!is_pow2(pl->shape[pl->axes[i]])) ok = false;
+        }
+        if (ok) {
+            pl->g.logN0 = ilog2(n[0]);
+            pl->g.logN1 = ilog2(n[1]);
+            pl->g.logM = ilog2(innerB / 2);
+            pl->g.batch = outerB;
+            pl->g.shift0 = pl->g.shift1 = 0;
+            const size_t es = dtype == NB2_F32 ? sizeof(cplx<float>) : sizeof(cplx<double>);
+            if (pl->g.logN0 > 13 || pl->g.logN1 > 13 || pl->g.logM > 40) ok = false;
+            if (ok && pl->g.logN0 && size_t(pitch_of(pl->g.logN0)) * es > kSmemLimit) ok = false;
+            if (ok && pl->g.logN1 && size_t(pitch_of(pl->g.logN1)) * es > kSmemLimit) ok = false;
+            if (ok && !(pl->g.logN0 || pl->g.logN1)) ok = false;
+        }
+        pl->inner = ok;
+    }
     int rc = 0;
+    if (pl->inner) {
+        if (dtype == NB2_F32) {
+            if (pl->g.logN0) rc |= upload_table<float>(&pl->tw0, 1ll << pl->g.logN0, 1ll << pl->g.logN0);
+            if (pl->g.logN1) rc |= upload_table<float>(&pl->tw1, 1ll << pl->g.logN1, 1ll << pl->g.logN1);
+        } else {
+            if (pl->g.logN0) rc |= upload_table<double>(&pl->tw0, 1ll << pl->g.logN0, 1ll << pl->g.logN0);
+            if (pl->g.logN1) rc |= upload_table<double>(&pl->tw1, 1ll << pl->g.logN1, 1ll << pl->g.logN1);
+        }
+    }
     if (fast) {
         if (dtype == NB2_F32) {
             if (pl->g.logN0) rc |= upload_table<float>(&pl->tw0, 1ll << pl->g.logN0, 1ll << pl->g.logN0);
@@ -368,6 +460,7 @@ int nb2_plan_set_mirror(nb2_plan* pl, int shift0, int shift1) {
 }
 
 int nb2_plan_is_fast(const nb2_plan* pl) { return pl && pl->fast ? 1 : 0; }
+int nb2_plan_kind(const nb2_plan* pl) { return !pl ? -1 : (pl->fast ? 1 : (pl->inner ? 2 : 0)); }
 
 int64_t nb2_plan_ksq_size(const nb2_plan* pl) {
     if (!pl || !pl->fast) return 0;
@@ -382,9 +475,16 @@ int nb2_hartley(nb2_plan* pl, const void* in, void* out, int conv, const nb2_poi
         return NB2_ERR_ARG;
     }
     rt_stream st = (rt_stream)stream;
+    if ((pro && pro->bin_x) || (epi && epi->bin_x && (!pl->fast || !epi->bin_out))) {
+        last_error() = "nb2_hartley: the binned reduction (bin_x/bin_out) is an epilogue of fast-path plans";
+        return NB2_ERR_UNSUPPORTED;
+    }
     if (pl->fast)
         return pl->dtype == NB2_F32 ? hartley_fast<float>(pl, in, out, conv, pro, epi, st)
                                     : hartley_fast<double>(pl, in, out, conv, pro, epi, st);
+    if (pl->inner)
+        return pl->dtype == NB2_F32 ? hartley_inner<float>(pl, in, out, conv, pro, epi, st)
+                                    : hartley_inner<double>(pl, in, out, conv, pro, epi, st);
     return pl->dtype == NB2_F32 ? hartley_generic<float>(pl, in, out, conv, pro, epi, st)
                                 : hartley_generic<double>(pl, in, out, conv, pro, epi, st);
 }

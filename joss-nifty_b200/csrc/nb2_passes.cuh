@@ -411,6 +411,10 @@ struct RowPass {
     template <typename OP>
     NB2_HD static T apply_epi(const OP& e, const Geom& g, T h, long long k0, long long k1, long long k2,
                               long long item, long long idx, double& acc) {
+        if (e.bin_x) {
+            const long long ksq = sq_mirror(k0, g.logN0) + sq_mirror(k1, g.logN1) + sq_mirror(k2, g.logM + 1);
+            atomic_add_f64(e.bin_out + ksq, double(ld_stream(e.bin_x + idx)) * double(h * e.scale));
+        }
         T v = h * amp_factor(e, g, k0, k1, k2, item);
         if (e.mul) v *= ld_stream(e.mul + idx);
         v += e.add_scalar;
@@ -425,7 +429,7 @@ struct RowPass {
     // Epilogue for four consecutive outputs, split in two so that every global load is issued
     // before the shared-memory work of the untangle step and only consumed after it.
     struct EpiLoads {
-        vec4<T> f, m, a, d;
+        vec4<T> f, m, a, d, bx;
     };
     // `kq`/`down`: mode length along the last axis of element i is kq + i (first half of the
     // row) or kq - i (second half).
@@ -444,12 +448,17 @@ struct RowPass {
         if (e.mul) L.m = ld4_stream(e.mul + idx);
         if (e.add) L.a = ld4_stream(e.add + idx);
         if (e.dot && e.dot != e.add) L.d = ld4_stream(e.dot + idx);   // the CG curvature reads d once
+        if (e.bin_x) L.bx = ld4_stream(e.bin_x + idx);
     }
     template <typename OP>
-    NB2_HD static void epi_apply(const OP& e, const EpiLoads& L, vec4<T>& h, double& acc) {
+    NB2_HD static void epi_apply(const OP& e, const EpiLoads& L, vec4<T>& h, double& acc, int f01, int kq, bool down) {
         NB2_UNROLL
         for (int i = 0; i < 4; ++i) {
             T v = h.v[i] * e.scale;
+            if (e.bin_x) {
+                const int km = down ? kq - i : kq + i;
+                atomic_add_f64(e.bin_out + f01 + km * km, double(L.bx.v[i]) * double(v));
+            }
             if (e.amp_mode != 0) v *= L.f.v[i];
             if (e.mul) v *= L.m.v[i];
             v += e.add_scalar;
@@ -599,8 +608,8 @@ struct RowPass {
                         h1.v[i] = T(0.5) * (F1.re + sgn * F1.im);
                         h2.v[i] = T(0.5) * (F2.re + sgn * F2.im);
                     }
-                    epi_apply(p.epi, L1, h1, acc);
-                    epi_apply(p.epi, L2, h2, acc);
+                    epi_apply(p.epi, L1, h1, acc, f01, k, false);
+                    epi_apply(p.epi, L2, h2, acc, f01, M - k, true);
                     st4_stream(p.out + rowbase + k, h1);
                     st4_stream(p.out + rowbase + M + k, h2);
                 }
@@ -645,6 +654,109 @@ struct RowPass {
 #if !defined(__CUDA_ARCH__)
             if (p.epi.dot && tid == 0) {
                 // same pairing tree as the shuffle reduction above
+                double v[32];
+                for (int j = 0; j < 32; ++j) v[j] = j < nthreads ? red[j] : 0.0;
+                for (int off = 16; off > 0; off >>= 1)
+                    for (int j = 0; j < off; ++j) v[j] += v[j + off];
+                p.epi.dot_partials[bid] = v[0];
+            }
+#endif
+        }
+    }
+};
+
+// ============================================================================ MirrorCombine
+// Transforms over LEADING axes with a contiguous inner batch (product spaces: the spatial
+// sub-space of a space x frequency field, src/library/correlated_fields.py:790-793).  Two
+// adjacent batch entries a, b are packed as one complex number z = x_a + i x_b (a free
+// reinterpretation of the real array); after the complex FFT over the transformed axes
+//   F_a[k] = (Z[k] + conj Z[-k]) / 2,   F_b[k] = -i (Z[k] - conj Z[-k]) / 2,
+// and H = Re F +- Im F.  This kernel does that combine for a row k and its mirror row -k at
+// once (each element read once, written once; in place is fine) and applies the epilogue.
+template <typename T>
+struct MirrorCombine {
+    static constexpr int NPHASES = 3;
+    static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
+    struct Params {
+        const cplx<T>* in;
+        T* out;
+        Geom g;
+        int conv;
+        PointOp<T> epi;
+        long long nctas;
+    };
+    static size_t smem_bytes(int nthreads) { return size_t(nthreads) * sizeof(double); }
+    NB2_HDC static bool enabled(int) { return true; }
+
+    NB2_HD static T epi1(const PointOp<T>& e, T h, long long item, long long idx, double& acc) {
+        T v = h * e.scale;
+        if (e.amp_mode == 2) v *= ld_stream(e.amp + item);
+        if (e.mul) v *= ld_stream(e.mul + idx);
+        v += e.add_scalar;
+        if (e.add) v += ld_stream(e.add + idx);
+        if (e.dot) acc += double(ld_stream(e.dot + idx)) * double(v);
+        return v;
+    }
+
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        double* red = reinterpret_cast<double*>(smem_raw);
+        if (PH == 0) {
+            double acc = 0.0;
+            const RowPairs rp = row_pairs(p.g);
+            const long long N0 = 1ll << p.g.logN0, N1 = 1ll << p.g.logN1, M = 1ll << p.g.logM;
+            const long long total = p.g.batch * rp.Q * M, stride = p.nctas * nthreads;
+            const T sgn = p.conv == NB2_CANONICAL ? T(-1) : T(1);
+            for (long long i = bid * nthreads + tid; i < total; i += stride) {
+                const long long m = i & (M - 1), pr = i >> p.g.logM;
+                const long long item = pr / rp.Q, q = pr - item * rp.Q;
+                long long k0, k1;
+                if (q < rp.nmid) {
+                    k0 = (p.g.shift0 ? 0 : 1) + (q >> p.g.logN1);
+                    k1 = q & (N1 - 1);
+                } else {
+                    const long long qq = q - rp.nmid;
+                    k0 = (qq / rp.h) ? N0 / 2 : 0;
+                    k1 = qq % rp.h;
+                }
+                const long long k0m = (N0 - k0 - p.g.shift0) & (N0 - 1), k1m = (N1 - k1 - p.g.shift1) & (N1 - 1);
+                const long long ra = (k0 << p.g.logN1) + k1, rb = (k0m << p.g.logN1) + k1m;   // rows inside the item
+                const long long rows_item = N0 * N1;
+                const long long ea = (item * rows_item + ra) * M + m, eb = (item * rows_item + rb) * M + m;
+                const cplx<T> za = ldc_stream(p.in + ea), zb = ldc_stream(p.in + eb);
+                // row k:   F_a = (za + conj zb)/2, F_b = -i (za - conj zb)/2
+                const T ha = T(0.5) * ((za.re + zb.re) + sgn * (za.im - zb.im));
+                const T hb = T(0.5) * ((za.im + zb.im) - sgn * (za.re - zb.re));
+                cplx<T> oa;
+                oa.re = epi1(p.epi, ha, (ra * M + m) * 2, ea * 2, acc);
+                oa.im = epi1(p.epi, hb, (ra * M + m) * 2 + 1, ea * 2 + 1, acc);
+                cplx<T> ob;
+                if (ra != rb) {  // row -k: the roles of za and zb exchanged
+                    const T ga = T(0.5) * ((zb.re + za.re) + sgn * (zb.im - za.im));
+                    const T gb = T(0.5) * ((zb.im + za.im) - sgn * (zb.re - za.re));
+                    ob.re = epi1(p.epi, ga, (rb * M + m) * 2, eb * 2, acc);
+                    ob.im = epi1(p.epi, gb, (rb * M + m) * 2 + 1, eb * 2 + 1, acc);
+                }
+                stc_stream(reinterpret_cast<cplx<T>*>(p.out) + ea, oa);
+                if (ra != rb) stc_stream(reinterpret_cast<cplx<T>*>(p.out) + eb, ob);
+            }
+            red[tid] = acc;
+        } else if (PH == 1) {
+            if (p.epi.dot && tid < 32) {
+                double s = 0.0;
+                for (int j = tid; j < nthreads; j += 32) s += red[j];
+#if defined(__CUDA_ARCH__)
+                NB2_UNROLL
+                for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+                if (tid == 0) p.epi.dot_partials[bid] = s;
+#else
+                red[tid] = s;
+#endif
+            }
+        } else {
+#if !defined(__CUDA_ARCH__)
+            if (p.epi.dot && tid == 0) {
                 double v[32];
                 for (int j = 0; j < 32; ++j) v[j] = j < nthreads ? red[j] : 0.0;
                 for (int off = 16; off > 0; off >>= 1)

@@ -21,6 +21,7 @@ struct nb2_plan {
     int axes[nb2::kMaxDim] = {0};
     long long total = 1;
     bool fast = false;
+    bool inner = false;  // leading transformed axes + contiguous inner batch: strided passes + MirrorCombine
     // fast path geometry: (batch, N0, N1, N2)
     nb2::Geom g{};
     void* tw0 = nullptr;  // strided axis-0 table (N0 entries)
@@ -64,6 +65,8 @@ PointOp<T> to_pointop(const nb2_pointop* o, double* partials) {
     r.add_scalar = o ? (T)o->add_scalar : T(0);
     r.dot = o ? (const T*)o->dot : nullptr;
     r.dot_partials = partials;
+    r.bin_x = o ? (const T*)o->bin_x : nullptr;
+    r.bin_out = o ? o->bin_out : nullptr;
     return r;
 }
 

@@ -27,7 +27,21 @@ struct PointOp {
     T add_scalar;        // epilogue only (offset_mean)
     const T* dot;        // optional: accumulate sum(dot[i] * out[i]) in fp64, epilogue only
     double* dot_partials;  // one slot per CTA (deterministic two-level reduction)
+    // optional spectrum cotangent (epilogue of the row pass only): bin_out[ksq(i)] += bin_x[i] * value
+    // with value = transform * scale BEFORE the amplitude factor -- the binned reduction of
+    // PowerDistributor.adjoint_times (src/operators/distributors.py:105-112, utilities.py:223-240)
+    // in the ksq parametrisation of the bins; fp64 atomics
+    const T* bin_x;
+    double* bin_out;
 };
+
+NB2_HD void atomic_add_f64(double* p, double v) {
+#if defined(__CUDA_ARCH__)
+    atomicAdd(p, v);
+#else
+    *p += v;
+#endif
+}
 
 // Geometry of the (batch, N0, N1, N2) real array; N2 = 2*M, all powers of two.
 struct Geom {

@@ -31,6 +31,8 @@ class PointOp(ctypes.Structure):
         ("add_scalar", c_double),
         ("dot", c_void_p),
         ("dot_out", c_void_p),
+        ("bin_x", c_void_p),
+        ("bin_out", c_void_p),
     ]
 
 
@@ -48,6 +50,7 @@ class Library:
         "nb2_plan_create": (c_int, [c_int, POINTER(c_int64), c_int, POINTER(c_int32), c_int, POINTER(c_void_p)]),
         "nb2_plan_destroy": (c_int, [c_void_p]),
         "nb2_plan_is_fast": (c_int, [c_void_p]),
+        "nb2_plan_kind": (c_int, [c_void_p]),
         "nb2_plan_set_mirror": (c_int, [c_void_p, c_int, c_int]),
         "nb2_plan_ksq_size": (c_int64, [c_void_p]),
         "nb2_hartley": (c_int, [c_void_p, c_void_p, c_void_p, c_int, POINTER(PointOp), POINTER(PointOp), c_void_p]),

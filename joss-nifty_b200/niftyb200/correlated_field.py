@@ -259,7 +259,9 @@ class CorrelatedField:
         if tab.amp_mode != 1:
             return tab
         field = self.plans[0].expand_table(tab.amp, scale=tab.azm)
-        return Tables(2, field, 1.0, tab.amps)
+        st = Tables(2, field, 1.0, tab.amps)
+        st.azm_value = tab.azm        # the factor folded into the field
+        return st
 
     # ---- hot tail ---------------------------------------------------------------------
     def apply_xi(self, xi, tab, out=None, convention=None, offset=None, mul=None):
@@ -285,6 +287,60 @@ class CorrelatedField:
         for pl in reversed(self.plans[1:-1]):
             cur = pl.hartley(cur, out=cur, convention=convention)
         return self.plans[0].hartley(cur, out=cur, convention=convention, epi=epi)
+
+    def vjp(self, ybar, tab, xi, convention=None):
+        """Full cotangent of the hot tail for ``ybar`` (position space) at excitations ``xi``:
+        ``(xibar, [ampbar_g], azmbar, offsetbar)`` -- the xi block as in :meth:`adjoint_xi` plus the
+        table cotangents, i.e. the binned reductions of ``PowerDistributor.adjoint_times``
+        (``distributors.py:105-112``) that feed the VJP of the O(n_bins) amplitude chain.
+
+        Single isotropic sub-space on the fast path: ONE transform whose epilogue also accumulates
+        ``xi * h`` into the ksq bins (one extra read of ``xi``).  Anything else: the same algebra with
+        torch reductions over the explicit ``pindex`` (cold path)."""
+        amps = tab.amps
+        if self.single and self.grids[0].isotropic and self.plans[0].is_fast:
+            g = self.grids[0]
+            bins = torch.zeros(self.plans[0].ksq_size, dtype=torch.float64, device=self.device)
+            epi = PointOp(tab.amp_mode, tab.amp, tab.azm * self.dvol, bin_x=xi, bin_out=bins)
+            xibar = self.plans[0].hartley(ybar, convention=convention, epi=epi)
+            # bins[ksq] = sum_i xi_i * (azm' * h_i) over the points of that ksq, azm' = tab.azm
+            per_bin = bins[g.unique_ksq.to(self.device)]
+            true_azm = float(tab.azm) if tab.amp_mode == 1 else float(getattr(tab, "azm_value", tab.azm))
+            if tab.amp_mode == 2 and not hasattr(tab, "azm_value"):
+                raise ValueError("vjp needs the ksq tables or streaming tables made from them")
+            ampbar = per_bin * (true_azm / float(tab.azm))
+            azmbar = float((amps[0] * per_bin).sum() / float(tab.azm))
+            return xibar, [ampbar], azmbar, float(ybar.sum(dtype=torch.float64))
+        # general grids / product spaces
+        h = ybar
+        for pl, g in zip(reversed(self.plans), reversed(self.grids)):
+            h = pl.hartley(h, convention=convention, epi=PointOp(scale=1.0 / g.total_volume))
+        full = tab.amp if tab.amp_mode == 2 else None
+        if full is None:
+            raise ValueError("vjp: general grids use amp_mode-2 tables")
+        true_azm = float(getattr(tab, "azm_value", tab.azm))
+        xibar = h * full * float(tab.azm)
+        u = (xi.to(torch.float64) * h.to(torch.float64))
+        ea = None
+        exps = [g.expand(a, torch.float64) for a, g in zip(amps, self.grids)]
+        azmbar = None
+        ampbars = []
+        for i, (g, ax) in enumerate(zip(self.grids, self.axes)):
+            w = true_azm * u
+            for j, (e, axj) in enumerate(zip(exps, self.axes)):
+                if j == i:
+                    continue
+                shp = [1] * len(self.shape)
+                for k, axk in enumerate(axj):
+                    shp[axk] = self.shape[axk]
+                w = w * e.reshape(shp)
+            red = tuple(k for k in range(len(self.shape)) if k not in ax)
+            w = w.sum(dim=red) if red else w
+            ampbars.append(torch.zeros(amps[i].numel(), dtype=torch.float64, device=self.device)
+                           .index_add_(0, g.pindex.to(self.device).reshape(-1), w.reshape(-1)))
+            if azmbar is None:
+                azmbar = float((ampbars[0] * amps[0]).sum() / true_azm)
+        return xibar, ampbars, azmbar, float(ybar.sum(dtype=torch.float64))
 
     def __call__(self, p, convention=None):
         """Full model evaluation.  numpy in -> numpy out (host buffers, copies included);

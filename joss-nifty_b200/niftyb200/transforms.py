@@ -80,10 +80,11 @@ class PointOp:
     Keeps references to the tensors so they stay alive while the kernel runs."""
 
     def __init__(self, amp_mode=0, amp=None, scale=1.0, mul=None, add=None, add_scalar=0.0,
-                 dot=None, dot_out=None):
+                 dot=None, dot_out=None, bin_x=None, bin_out=None):
         self.amp_mode, self.amp, self.scale = int(amp_mode), amp, float(scale)
         self.mul, self.add, self.add_scalar = mul, add, float(add_scalar)
         self.dot, self.dot_out = dot, dot_out
+        self.bin_x, self.bin_out = bin_x, bin_out
 
     def to_c(self, lib):
         c = _lib.PointOp()
@@ -95,6 +96,8 @@ class PointOp:
         c.add_scalar = self.add_scalar
         c.dot = _ptr(lib, self.dot, "dot")
         c.dot_out = _ptr(lib, self.dot_out, "dot_out")
+        c.bin_x = _ptr(lib, self.bin_x, "bin_x")
+        c.bin_out = _ptr(lib, self.bin_out, "bin_out")
         return c
 
 
@@ -118,6 +121,7 @@ class Plan:
                                                 ctypes.byref(h)), "nb2_plan_create")
         self._h = h
         self.is_fast = bool(self.lib.nb2_plan_is_fast(h))
+        self.kind = int(self.lib.nb2_plan_kind(h))   # 0 generic, 1 fast (trailing axes), 2 fast (inner batch)
         self.ksq_size = int(self.lib.nb2_plan_ksq_size(h))
 
     def __del__(self):

@@ -177,6 +177,18 @@ def check_cf_vs_oracle(shape, dist, dt=np.float64, expect_mode=None, seed=3):
         xb = host(cf.adjoint_xi(dev(yb), tab, convention=conv))
         ref = co.adjoint(amps_o, azm_o, yb.astype(np.float64), convention=conv)[0]
         assert rel(xb, ref) <= TOL[dt], (shape, dt, conv, rel(xb, ref))
+        # full cotangent incl. the spectrum (binned reduction, distributors.py:105-112)
+        xi = p["xi"]
+        for t in (tab, cf.streaming_tables(tab)):
+            xb2, ampbars, azmbar, offbar = cf.vjp(dev(yb), t, dev(xi), convention=conv)
+            rxb, rab, razm, roff = co.adjoint(amps_o, azm_o, yb.astype(np.float64), xi=xi.astype(np.float64),
+                                              convention=conv)
+            assert rel(host(xb2), rxb) <= TOL[dt]
+            for a, b in zip(ampbars, rab):
+                assert rel(host(a), b) <= 10 * TOL[dt], (shape, dt, conv, rel(host(a), b))
+            scale = np.linalg.norm(np.concatenate([b.ravel() for b in rab])) + 1e-300
+            assert abs(azmbar - razm) <= 10 * TOL[dt] * max(abs(razm), scale)
+            assert abs(offbar - roff) <= 10 * TOL[dt] * max(abs(roff), np.linalg.norm(yb))
     # adjointness <A x, y> == <x, A^T y>  (extra.py:156-167)
     x = rng.normal(size=shape).astype(dt)
     Ax = host(cf.apply_xi(dev(x), tab, offset=0.0)).astype(np.float64)

@@ -84,3 +84,15 @@ def test_pipelined_passes(monkeypatch, stages):
     pc.check_hartley_shapes([((64, 16), None), ((16, 64, 8), None), ((64, 2, 128), None)])
     pc.check_metric((64, 64), 1 / 64)
     pc.check_metric((16, 32, 16), (1 / 16, 1 / 32, 1 / 16), np.float32)
+
+
+def test_hartley_leading_axes_inner_batch():
+    # product-space sub-transforms: leading axes, contiguous inner batch (strided passes + mirror combine)
+    import niftyb200 as nb
+    import torch
+    shapes = [((16, 8, 4), (0, 1)), ((8, 16, 2), (0, 1)), ((4, 32, 8), (1,)), ((32, 6), None), ((3, 8, 16, 4), (1, 2)),
+              ((64, 4), (0,)), ((2, 2, 2), (0, 1)), ((16, 16, 32), (0,))]
+    for shp, ax in shapes:
+        if ax is not None:
+            assert nb.Plan(shp, ax, torch.float64).kind == 2, (shp, ax)
+    pc.check_hartley_shapes([s for s in shapes if s[1] is not None])

@@ -114,3 +114,38 @@ def test_full_size_properties(shape, dt):
     z = plan.hartley(y, out=y, epi=PointOp(scale=1.0 / n))
     err = float(torch.linalg.vector_norm((z - x).double())) / nx
     assert err <= 4 * tol, err
+
+
+def test_hartley_leading_axes_inner_batch():
+    import niftyb200 as nb
+    shapes = [((16, 8, 4), (0, 1)), ((64, 128, 32), (0, 1)), ((4, 32, 8), (1,)), ((3, 8, 16, 4), (1, 2)),
+              ((1024, 16), (0,)), ((2, 2, 2), (0, 1)), ((256, 256, 2), (0, 1))]
+    for shp, ax in shapes:
+        assert nb.Plan(shp, ax, torch.float64).kind == 2, (shp, ax)
+    pc.check_hartley_shapes(shapes)
+
+
+@pytest.mark.parametrize("dt", [torch.float32])
+def test_product_space_c5_properties(dt):
+    """BASELINE configs[4] grid (2048 x 2048 space x 128 frequency): the two sub-space transforms
+    (space: leading axes + inner batch; frequency: trailing axis) at full size -- Parseval and
+    involution of each, and of their composition."""
+    from niftyb200.transforms import PointOp, get_plan
+    shape = (2048, 2048, 128)
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    x = torch.randn(shape, dtype=dt, device="cuda", generator=gen)
+    nx = float(torch.linalg.vector_norm(x.double()))
+    ps, pf = get_plan(shape, (0, 1), dt), get_plan(shape, (2,), dt)
+    assert ps.kind == 2 and pf.kind == 1
+    tol = 1e-5
+    y = ps.hartley(x)
+    ny = float(torch.linalg.vector_norm(y.double()))
+    assert abs(ny ** 2 / (2048 * 2048 * nx ** 2) - 1.0) <= 10 * tol
+    # one frequency channel against the 2-D trailing-axes transform of that channel
+    ref = get_plan((2048, 2048), None, dt).hartley(x[:, :, 5].contiguous())
+    assert float(torch.linalg.vector_norm((y[:, :, 5] - ref).double()) / torch.linalg.vector_norm(ref.double())) <= tol
+    y = pf.hartley(y, out=y)
+    y = pf.hartley(y, out=y, epi=PointOp(scale=1.0 / 128))
+    y = ps.hartley(y, out=y, epi=PointOp(scale=1.0 / (2048 * 2048)))
+    err = float(torch.linalg.vector_norm((y - x).double())) / nx
+    assert err <= 4 * tol, err
