@@ -327,7 +327,7 @@ struct RowPass {
     static constexpr int M = R1 * R2 * R3;
     static constexpr int MM = R2 * R3;
     static constexpr int PITCH = slot_pitch<R1, R2, R3>();
-    static constexpr int NPHASES = 6;
+    static constexpr int NPHASES = 7;
     static constexpr bool BIG = (R1 >= 32 || R3 >= 32);
     static constexpr int MAX_THREADS = (BIG && sizeof(T) == 8) ? 256 : 512;
     static constexpr int MIN_BLOCKS = sizeof(T) == 4 ? (BIG ? NB2_MINB256_F32 : NB2_MINB512_F32)
@@ -347,11 +347,22 @@ struct RowPass {
         int staged;   // pipelined launch: prefetch() has copied the rows into the stage buffer
     };
 
+    // per-slot data computed once per tile (phase 0) and reused by the untangle phase
+    struct SlotCache {
+        long long row;  // linear row index over (batch, N0, N1)
+        int f01;        // ksq contribution of (k0, k1)
+        int flags;      // bit 0: valid, bit 1: duplicate of its partner (self-mirrored row)
+    };
     static size_t smem_bytes(int G, int nthreads) {
-        return size_t(2 * G) * PITCH * sizeof(cplx<T>) + size_t(nthreads) * sizeof(double);
+        return size_t(2 * G) * PITCH * sizeof(cplx<T>) + size_t(nthreads) * sizeof(double) +
+               size_t(2 * G) * sizeof(SlotCache);
+    }
+    NB2_HD static SlotCache* slot_cache(const Params& p, char* smem_raw, int nthreads) {
+        return reinterpret_cast<SlotCache*>(smem_raw + size_t(2 * p.G) * PITCH * sizeof(cplx<T>) +
+                                            size_t(nthreads) * sizeof(double));
     }
     NB2_HDC static bool enabled(int ph) {
-        return ph == 0 || (ph == 1 && R2 > 1) || (ph == 2 && MM > 1) || ph >= 3;
+        return ph <= 1 || (ph == 2 && R2 > 1) || (ph == 3 && MM > 1) || ph >= 4;
     }
 
     NB2_HD static RowSlot slot_info(const Params& p, long long bid, int s) {
@@ -385,10 +396,11 @@ struct RowPass {
         return rs;
     }
 
+    // slot of output index k = k1 + R1 (k2 + R2 k3): with L = k1 MM + k2 R3 + k3 and k3 < R3, k2 < R2
+    // the padding terms are L / R3 = k1 R2 + k2 and L / (R2 R3) = k1, i.e. a fixed stride per digit
+    static constexpr int KS1 = MM + R2 + (R2 > 1 ? 1 : 0);   // slot stride of k1 (consecutive k)
     NB2_HD static int slot_of_k(int k) {
-        const int k1 = k % R1, rest = k / R1;
-        const int k2 = rest % R2, k3 = rest / R2;
-        return slot_of<R2, R3>(k1 * MM + k2 * R3 + k3);
+        return (k & (R1 - 1)) * KS1 + ((k / R1) & (R2 - 1)) * (R3 + 1) + k / (R1 * R2);
     }
 
     // asynchronous copy of the 2G rows of tile `bid` into a stage buffer (padded slot layout)
@@ -474,30 +486,36 @@ struct RowPass {
         double* red = reinterpret_cast<double*>(smem_raw + size_t(2 * p.G) * PITCH * sizeof(cplx<T>));
         const int nslots = 2 * p.G;
         if (PH == 0) {
+            // row bookkeeping of the tile, once per slot
+            for (int s = tid; s < nslots; s += nthreads) {
+                const RowSlot rs = slot_info(p, bid, s);
+                SlotCache sc;
+                sc.row = rs.row;
+                sc.f01 = int(sq_mirror(rs.k0, p.g.logN0) + sq_mirror(rs.k1, p.g.logN1));
+                sc.flags = (rs.valid ? 1 : 0) | (rs.dup ? 2 : 0);
+                slot_cache(p, smem_raw, nthreads)[s] = sc;
+            }
+        } else if (PH == 1) {
             const int nb = nslots * MM;
-            int prev_s = -1;
-            RowSlot rs{};
+            const SlotCache* cache = slot_cache(p, smem_raw, nthreads);
             for (int b = tid; b < nb; b += nthreads) {
                 const int r = b % MM, s = b / MM;
-                if (s != prev_s) {
-                    rs = slot_info(p, bid, s);
-                    prev_s = s;
-                }
-                if (!rs.valid) continue;
+                const SlotCache sc = cache[s];
+                if (!(sc.flags & 1)) continue;
                 cplx<T> x[R1];
                 if (p.staged) {
                     const cplx<T>* src = smem + s * PITCH;
                     NB2_UNROLL
                     for (int n1 = 0; n1 < R1; ++n1) x[n1] = src[slot_of<R2, R3>(r + n1 * MM)];
                 } else {
-                    const cplx<T>* src = p.in + rs.row * M + r;
+                    const cplx<T>* src = p.in + sc.row * M + r;
                     NB2_UNROLL
                     for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + n1 * MM);
                 }
                 if (p.has_pro) {
                     const long long N0N1 = 1ll << (p.g.logN0 + p.g.logN1);
-                    const long long rowitem = rs.row & (N0N1 - 1);
-                    const long long f01 = sq_mirror(rs.k0, p.g.logN0) + sq_mirror(rs.k1, p.g.logN1);
+                    const long long rowitem = sc.row & (N0N1 - 1);
+                    const long long f01 = sc.f01;
                     NB2_UNROLL
                     for (int n1 = 0; n1 < R1; ++n1) {
                         const long long m = r + n1 * MM;
@@ -535,7 +553,7 @@ struct RowPass {
                     dst[slot_of<R2, R3>(k1 * MM + r)] = v;
                 }
             }
-        } else if (PH == 1) {
+        } else if (PH == 2) {
             if (R2 > 1) {
                 const int nb = nslots * R1 * R3;
                 for (int b = tid; b < nb; b += nthreads) {
@@ -554,7 +572,7 @@ struct RowPass {
                     }
                 }
             }
-        } else if (PH == 2) {
+        } else if (PH == 3) {
             if (MM > 1) {
                 const int nb = nslots * R1 * R2;
                 for (int b = tid; b < nb; b += nthreads) {
@@ -568,7 +586,7 @@ struct RowPass {
                     for (int k3 = 0; k3 < R3; ++k3) row[slot_of<R2, R3>(k1 * MM + k2 * R3 + k3)] = x[brev<R3>(k3)];
                 }
             }
-        } else if (PH == 3) {
+        } else if (PH == 4) {
             // untangle + Hartley combine + epilogue
             double acc = 0.0;
             const long long itemrows = 1ll << (p.g.logN0 + p.g.logN1);
@@ -579,37 +597,45 @@ struct RowPass {
                 // four consecutive k per thread: 16/32-byte global accesses
                 constexpr int Q4 = M >= 4 ? M / 4 : 1;
                 const int nb = nslots * Q4;
-                long long rowbase = 0, itembase = 0;
-                int f01 = 0;
+                const SlotCache* cache = slot_cache(p, smem_raw, nthreads);
+                PointOp<T> e = p.epi;
+                e.scale = p.epi.scale * T(0.5);          // the 1/2 of the untangle step rides on the scale
                 for (int b = tid; b < nb; b += nthreads) {
                     const int k = (b % Q4) * 4, s = b / Q4;
-                    if (s != prev_s) {
-                        rs = slot_info(p, bid, s);
-                        prev_s = s;
-                        rowbase = rs.row * (2 * M);
-                        itembase = (rs.row & (itemrows - 1)) * (2 * M);
-                        f01 = int(sq_mirror(rs.k0, p.g.logN0) + sq_mirror(rs.k1, p.g.logN1));
-                    }
-                    if (!rs.valid || rs.dup) continue;
-                    const cplx<T>* za = smem + s * PITCH;
-                    const cplx<T>* zb = smem + (s ^ 1) * PITCH;
+                    const SlotCache sc = cache[s];
+                    if (sc.flags != 1) continue;          // invalid, or the duplicate of a self-mirrored row
+                    const long long rowbase = sc.row * (2 * M);
+                    const long long itembase = (sc.row & (itemrows - 1)) * (2 * M);
+                    const int f01 = sc.f01;
                     EpiLoads L1, L2;
-                    epi_fetch(p.epi, L1, f01, k, false, itembase + k, rowbase + k);
-                    epi_fetch(p.epi, L2, f01, M - k, true, itembase + M + k, rowbase + M + k);
+                    epi_fetch(e, L1, f01, k, false, itembase + k, rowbase + k);
+                    epi_fetch(e, L2, f01, M - k, true, itembase + M + k, rowbase + M + k);
+                    // a_i = Z[k + i] (this row), b_i = conj Z'[(M - k - i) mod M] (mirror row): consecutive
+                    // k are KS1 slots apart; i = 1..3 of the mirror index lie in the quad below M - k
+                    const cplx<T>* za = smem + s * PITCH + slot_of_k(k);
+                    const cplx<T>* zb = smem + (s ^ 1) * PITCH;
+                    const cplx<T>* zb0 = zb + slot_of_k((M - k) & (M - 1));
+                    const cplx<T>* zb4 = zb + slot_of_k(M - k - 4);
+                    const vec4<T> w01 = ld4_ro(reinterpret_cast<const T*>(p.tw + k));
+                    const vec4<T> w23 = ld4_ro(reinterpret_cast<const T*>(p.tw + k + 2));
                     vec4<T> h1, h2;
                     NB2_UNROLL
                     for (int i = 0; i < 4; ++i) {
-                        const cplx<T> a = za[slot_of_k(k + i)];
-                        const cplx<T> bb = conj(zb[slot_of_k((M - k - i) & (M - 1))]);
-                        const cplx<T> E = a + bb;
-                        const cplx<T> O = mul_mi(a - bb);
-                        const cplx<T> WO = ldc_ro(p.tw + k + i) * O;
-                        const cplx<T> F1 = E + WO, F2 = E - WO;
-                        h1.v[i] = T(0.5) * (F1.re + sgn * F1.im);
-                        h2.v[i] = T(0.5) * (F2.re + sgn * F2.im);
+                        const cplx<T> a = za[i * KS1];
+                        const cplx<T> bz = i == 0 ? zb0[0] : zb4[(4 - i) * KS1];
+                        const T wr = i < 2 ? w01.v[2 * i] : w23.v[2 * i - 4];
+                        const T wi = i < 2 ? w01.v[2 * i + 1] : w23.v[2 * i - 3];
+                        // E = a + conj b, O = -i (a - conj b); 2 H[k] = cas(E) + cas(W O), 2 H[k+M] = cas(E) - cas(W O)
+                        // with cas(z) = Re z + sgn Im z
+                        const T Er = a.re + bz.re, Ei = a.im - bz.im;
+                        const T Or = a.im + bz.im, Oi = bz.re - a.re;
+                        const T ce = Er + sgn * Ei;
+                        const T co = Or * (wr + sgn * wi) + Oi * (sgn * wr - wi);
+                        h1.v[i] = ce + co;
+                        h2.v[i] = ce - co;
                     }
-                    epi_apply(p.epi, L1, h1, acc, f01, k, false);
-                    epi_apply(p.epi, L2, h2, acc, f01, M - k, true);
+                    epi_apply(e, L1, h1, acc, f01, k, false);
+                    epi_apply(e, L2, h2, acc, f01, M - k, true);
                     st4_stream(p.out + rowbase + k, h1);
                     st4_stream(p.out + rowbase + M + k, h2);
                 }
@@ -638,7 +664,7 @@ struct RowPass {
                 }
             }
             if (p.epi.dot) red[tid] = acc;
-        } else if (PH == 4) {
+        } else if (PH == 5) {
             if (p.epi.dot && tid < 32) {
                 double s = 0.0;
                 for (int j = tid; j < nthreads; j += 32) s += red[j];
