@@ -129,6 +129,24 @@ template <typename T> NB2_HD void stc_stream(cplx<T>* p, cplx<T> v) {
     *p = v;
 #endif
 }
+// L2-resident intermediates (the group buffer of the L2-blocked tail): cached in L2 with the
+// default policy, bypassing L1
+template <typename T> NB2_HD cplx<T> ldc_keep(const cplx<T>* p) {
+#if defined(__CUDA_ARCH__)
+    typename vec2_of<T>::type v = __ldcg(reinterpret_cast<const typename vec2_of<T>::type*>(p));
+    return mk<T>(v.x, v.y);
+#else
+    return *p;
+#endif
+}
+template <typename T> NB2_HD void stc_keep(cplx<T>* p, cplx<T> v) {
+#if defined(__CUDA_ARCH__)
+    typename vec2_of<T>::type w; w.x = v.re; w.y = v.im;
+    __stcg(reinterpret_cast<typename vec2_of<T>::type*>(p), w);
+#else
+    *p = v;
+#endif
+}
 template <typename T> NB2_HD cplx<T> ldc_ro(const cplx<T>* p) {
 #if defined(__CUDA_ARCH__)
     typename vec2_of<T>::type v = __ldg(reinterpret_cast<const typename vec2_of<T>::type*>(p));

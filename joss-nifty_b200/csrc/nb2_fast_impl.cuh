@@ -74,7 +74,7 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         return NB2_ERR_ARG;
     }
     const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
-    const long long outer = axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
+    const long long outer = (rm && rm->grp_on) ? rm->grp_n : axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
     const long long ncols = (rm && rm->ncols) ? rm->ncols : inner;
     const long long run = (rm && rm->run) ? rm->run : ncols;
     if (ncols > inner || (ncols & (ncols - 1)) || (run & (run - 1)) || run > ncols) {
@@ -111,6 +111,11 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         p.col0 = rm ? rm->col0 : 0;                                                           \
         p.run_stride = rm ? rm->run_stride : 0;                                               \
         p.logrun = ilog2(run);                                                                \
+        p.grp_on = rm ? rm->grp_on : 0;                                                       \
+        p.keep_out = rm ? rm->keep_out : 0;                                                   \
+        p.grp_lo_a = rm ? rm->grp_lo_a : 0;                                                   \
+        p.grp_lo_n = rm ? rm->grp_lo_n : 0;                                                   \
+        p.grp_hi_a = rm ? rm->grp_hi_a : 0;                                                   \
         const size_t smem = K::smem_bytes(logw);                                              \
         p.staged = p.pro_staged = 0;                                                          \
         if (smem > kSmemLimit) {                                                              \
@@ -123,7 +128,7 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
             const bool field = pro && pro->amp_mode == 2;                                     \
             const size_t stage = smem * (field ? 2 : 1);                                      \
             const int stages = pipe_stages(stage);                                            \
-            if (!K::SINGLE && stages && ntiles >= 4ll * rt_sm_count() &&                      \
+            if (!K::SINGLE && stages && !p.grp_on && ntiles >= 4ll * rt_sm_count() &&         \
                 (sizeof(cplx<T>) << logw) >= 16 && aligned16(in) && (!field || aligned16(pro->amp))) { \
                 p.staged = 1;                                                                 \
                 p.pro_staged = field ? 1 : 0;                                                 \
@@ -153,17 +158,25 @@ int choose_G(int logm, long long Q) {
 }
 
 template <typename T>
-int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
-             rt_stream st) {
-    const int logm = pl->g.logM;
+int rows_pairs_per_cta(const nb2_plan* pl) {
     const RowPairs rp = row_pairs(pl->g);
-    int G = choose_G<T>(logm, rp.Q);
+    int G = choose_G<T>(pl->g.logM, rp.Q);
     if (const char* e = std::getenv("NB2_ROWS_G")) {
         const int v = std::atoi(e);
         if (v >= 1 && v <= 16 && 2 * v <= rp.Q + 1) G = v;
     }
+    return G;
+}
+
+template <typename T>
+int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
+             rt_stream st, const RowGroup* grp) {
+    const int logm = pl->g.logM;
+    const RowPairs rp = row_pairs(pl->g);
+    const int G = grp ? grp->G : rows_pairs_per_cta<T>(pl);
     const long long ctas_per_item = (rp.Q + G - 1) / G;
-    const long long grid = ctas_per_item * pl->g.batch;
+    const long long grid = ctas_per_item * pl->g.batch;          // partials cover the whole transform
+    const long long launch_grid = grp ? (grp->q_end - grp->q0 + G - 1) / G : grid;
     const bool want_dot = epi && epi->dot;
     if (want_dot) {
         if (!epi->dot_out) {
@@ -194,6 +207,12 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
         p.has_pro = pro ? 1 : 0;                                                              \
         p.pro = to_pointop<T>(pro, nullptr);                                                  \
         p.epi = to_pointop<T>(epi, pl->partials);                                             \
+        p.bid0 = grp ? grp->q0 / G : 0;                                                       \
+        p.q_end = grp ? grp->q_end : rp.Q;                                                    \
+        p.grp_on = grp ? 1 : 0;                                                               \
+        p.grp_lo_a = grp ? grp->lo_a : 0;                                                     \
+        p.grp_lo_n = grp ? grp->lo_n : 0;                                                     \
+        p.grp_hi_a = grp ? grp->hi_a : 0;                                                     \
         const long long nb1 = (long long)2 * G * B * C;                                       \
         const int maxt = K::MAX_THREADS;                                                      \
         const int nthreads = pipe_threads(std::min(maxt, round32(nb1)), maxt);                \
@@ -202,11 +221,11 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
         p.staged = 0;                                                                         \
         if (smem > kSmemLimit) {                                                              \
             rc = NB2_ERR_UNSUPPORTED;                                                         \
-        } else if (stages && grid >= 4ll * rt_sm_count() && aligned16(in)) {                  \
+        } else if (stages && !grp && grid >= 4ll * rt_sm_count() && aligned16(in)) {          \
             p.staged = 1;                                                                     \
             rc = rt_launch_pipe<K>(grid, 0, nthreads, smem, stages, st, p);                   \
         } else {                                                                              \
-            rc = rt_launch<K>(grid, nthreads, smem, st, p);                                   \
+            rc = rt_launch<K>(launch_grid, nthreads, smem, st, p);                            \
         }                                                                                     \
     }
     const char* alt = std::getenv("NB2_PLAN9");
@@ -221,7 +240,7 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
     }
 #undef NB2_RUN_ROWS
     if (rc) return rc;
-    if (want_dot) {
+    if (want_dot && (!grp || grp->reduce)) {
         rc = launch_final_reduce(pl->partials, grid, 1, epi->dot_out, st);
     }
     return rc;

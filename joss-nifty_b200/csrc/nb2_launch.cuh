@@ -201,6 +201,33 @@ inline int rt_sync(rt_stream s) {
     NB2_CUDA_OK(cudaStreamSynchronize(s));
     return 0;
 }
+// auxiliary streams + fork/join events (the L2-blocked tail runs its plane groups on several streams
+// so that the tail of one group's kernel overlaps the head of the next group's)
+typedef cudaEvent_t rt_event;
+inline int rt_stream_create(rt_stream* s) {
+    NB2_CUDA_OK(cudaStreamCreateWithFlags(s, cudaStreamNonBlocking));
+    return 0;
+}
+inline int rt_stream_destroy(rt_stream s) {
+    if (s) NB2_CUDA_OK(cudaStreamDestroy(s));
+    return 0;
+}
+inline int rt_event_create(rt_event* e) {
+    NB2_CUDA_OK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    return 0;
+}
+inline int rt_event_destroy(rt_event e) {
+    if (e) NB2_CUDA_OK(cudaEventDestroy(e));
+    return 0;
+}
+inline int rt_event_record(rt_event e, rt_stream s) {
+    NB2_CUDA_OK(cudaEventRecord(e, s));
+    return 0;
+}
+inline int rt_stream_wait(rt_stream s, rt_event e) {
+    NB2_CUDA_OK(cudaStreamWaitEvent(s, e, 0));
+    return 0;
+}
 // peer-visible allocations: CUDA IPC handles (64 bytes) let the other processes of the box map the
 // buffer, so that a pass can store its output straight into the peers' memory over NVLink
 inline int rt_ipc_export(void* p, void* handle64) {
@@ -280,6 +307,13 @@ inline int rt_h2d(void* d, const void* s, size_t n, rt_stream) { std::memcpy(d, 
 inline int rt_d2h(void* d, const void* s, size_t n, rt_stream) { std::memcpy(d, s, n); return 0; }
 inline int rt_d2d(void* d, const void* s, size_t n, rt_stream) { std::memmove(d, s, n); return 0; }
 inline int rt_sync(rt_stream) { return 0; }
+typedef void* rt_event;
+inline int rt_stream_create(rt_stream* s) { *s = nullptr; return 0; }
+inline int rt_stream_destroy(rt_stream) { return 0; }
+inline int rt_event_create(rt_event* e) { *e = nullptr; return 0; }
+inline int rt_event_destroy(rt_event) { return 0; }
+inline int rt_event_record(rt_event, rt_stream) { return 0; }
+inline int rt_stream_wait(rt_stream, rt_event) { return 0; }
 inline int rt_ipc_export(void*, void*) { last_error() = "peer memory needs the CUDA build"; return -3; }
 inline int rt_ipc_open(const void*, void**) { last_error() = "peer memory needs the CUDA build"; return -3; }
 inline int rt_ipc_close(void*) { return -3; }

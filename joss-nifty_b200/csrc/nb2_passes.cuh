@@ -97,6 +97,12 @@ struct StridedPass {
         const long long* out_rowoff;
         long long in_ostride, out_ostride, col0, run_stride;
         int logrun;
+        // L2-blocked tail (hartley_fast): the launch covers a GROUP of planes -- local plane o is
+        // the natural plane  o < grp_lo_n ? grp_lo_a + o : grp_hi_a + (o - grp_lo_n)  of the input
+        // and plane o of the (small, L2-resident) output buffer.  keep_out: store with the default
+        // cache policy instead of evict-first so that the next kernel finds the tile in L2.
+        int grp_on, keep_out;
+        long long grp_lo_a, grp_lo_n, grp_hi_a;
         // pipelined launch (nb2_kernel_pipe): the tile -- and, with pro_staged, the amplitude
         // field tile behind it -- has been copied into the stage buffer by prefetch()
         int staged, pro_staged;
@@ -107,10 +113,16 @@ struct StridedPass {
     }
     NB2_HDC static bool enabled(int ph) { return ph == 0 || (ph == 1 && R2 > 1) || (ph == 2 && R3 > 1); }
 
-    NB2_HD static long long tile_base(const Params& p, long long bid) {
-        const long long o = bid / p.tiles_per_outer, tile = bid - o * p.tiles_per_outer;
+    NB2_HD static long long tile_base(const Params& p, long long bid, bool local = false) {
+        long long o = bid / p.tiles_per_outer;
+        const long long tile = bid - o * p.tiles_per_outer;
+        if (p.grp_on && !local) o = o < p.grp_lo_n ? p.grp_lo_a + o : p.grp_hi_a + (o - p.grp_lo_n);
         const long long tc = tile << p.logw;
         return o * N * p.inner + p.col0 + (tc >> p.logrun) * p.run_stride + (tc & ((1ll << p.logrun) - 1));
+    }
+    NB2_HD static void store_out(const Params& p, cplx<T>* dst, cplx<T> v) {
+        if (p.keep_out) stc_keep(dst, v);
+        else stc_stream(dst, v);
     }
 
     // asynchronous copy of tile `bid` into a stage buffer, in the padded slot layout phase 0 works in
@@ -141,7 +153,8 @@ struct StridedPass {
         const int w = 1 << p.logw;
         const long long base = tile_base(p, bid);
         const long long tcol = (bid % p.tiles_per_outer) << p.logw;
-        const long long obase = p.out_rowoff ? (bid / p.tiles_per_outer) * p.out_ostride + tcol : base;
+        const long long obase = p.out_rowoff ? (bid / p.tiles_per_outer) * p.out_ostride + tcol
+                                             : (p.grp_on ? tile_base(p, bid, true) : base);
         if (PH == 0) {
             const int nb = MM << p.logw;
             for (int b = tid; b < nb; b += nthreads) {
@@ -244,7 +257,7 @@ struct StridedPass {
                     if (!SINGLE && k1 != 0) v = v * ldc_ro(p.tw + r * k1);
 #endif
                     if (SINGLE) {
-                        stc_stream(p.out + obase + c + (p.out_rowoff ? ld_ro(p.out_rowoff + k1) : (long long)k1 * p.inner), v);
+                        store_out(p, p.out + obase + c + (p.out_rowoff ? ld_ro(p.out_rowoff + k1) : (long long)k1 * p.inner), v);
                     } else {
                         smem[(slot_of<R2, R3>(k1 * MM + r) << p.logw) + c] = v;
                     }
@@ -286,10 +299,10 @@ struct StridedPass {
                         NB2_UNROLL
                         for (int k3 = 0; k3 < R3; ++k3) stc_stream(dst + ld_ro(ro + k3 * (R1 * R2)), x[brev<R3>(k3)]);
                     } else {
-                        cplx<T>* dst = p.out + base + c + (long long)(k1 + R1 * k2) * p.inner;
+                        cplx<T>* dst = p.out + obase + c + (long long)(k1 + R1 * k2) * p.inner;
                         NB2_UNROLL
                         for (int k3 = 0; k3 < R3; ++k3)
-                            stc_stream(dst + (long long)k3 * (R1 * R2) * p.inner, x[brev<R3>(k3)]);
+                            store_out(p, dst + (long long)k3 * (R1 * R2) * p.inner, x[brev<R3>(k3)]);
                     }
                 }
             }
@@ -345,11 +358,18 @@ struct RowPass {
         PointOp<T> pro;
         PointOp<T> epi;
         int staged;   // pipelined launch: prefetch() has copied the rows into the stage buffer
+        // L2-blocked tail: this launch covers the mirror pairs [bid0 * G, q_end) and reads its
+        // rows from a group buffer in which natural plane k0 is plane
+        //   k0 < grp_hi_a ? k0 - grp_lo_a : grp_lo_n + (k0 - grp_hi_a)
+        long long bid0, q_end;
+        int grp_on;
+        long long grp_lo_a, grp_lo_n, grp_hi_a;
     };
 
     // per-slot data computed once per tile (phase 0) and reused by the untangle phase
     struct SlotCache {
         long long row;  // linear row index over (batch, N0, N1)
+        long long in_row;  // row index in the input buffer (differs from `row` for group buffers)
         int f01;        // ksq contribution of (k0, k1)
         int flags;      // bit 0: valid, bit 1: duplicate of its partner (self-mirrored row)
     };
@@ -371,7 +391,7 @@ struct RowPass {
         const long long q = (bid - item * p.ctas_per_item) * p.G + (s >> 1);
         const long long N0 = 1ll << p.g.logN0, N1 = 1ll << p.g.logN1;
         RowSlot rs;
-        rs.valid = q < rp.Q;
+        rs.valid = q < rp.Q && q < p.q_end;
         rs.dup = false;
         rs.k0 = rs.k1 = rs.row = 0;
         if (!rs.valid) return rs;
@@ -485,12 +505,16 @@ struct RowPass {
         cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
         double* red = reinterpret_cast<double*>(smem_raw + size_t(2 * p.G) * PITCH * sizeof(cplx<T>));
         const int nslots = 2 * p.G;
+        bid += p.bid0;
         if (PH == 0) {
             // row bookkeeping of the tile, once per slot
             for (int s = tid; s < nslots; s += nthreads) {
                 const RowSlot rs = slot_info(p, bid, s);
                 SlotCache sc;
                 sc.row = rs.row;
+                sc.in_row = !p.grp_on ? rs.row
+                                      : (((rs.k0 < p.grp_hi_a ? rs.k0 - p.grp_lo_a : p.grp_lo_n + (rs.k0 - p.grp_hi_a))
+                                          << p.g.logN1) + rs.k1);
                 sc.f01 = int(sq_mirror(rs.k0, p.g.logN0) + sq_mirror(rs.k1, p.g.logN1));
                 sc.flags = (rs.valid ? 1 : 0) | (rs.dup ? 2 : 0);
                 slot_cache(p, smem_raw, nthreads)[s] = sc;
@@ -508,9 +532,14 @@ struct RowPass {
                     NB2_UNROLL
                     for (int n1 = 0; n1 < R1; ++n1) x[n1] = src[slot_of<R2, R3>(r + n1 * MM)];
                 } else {
-                    const cplx<T>* src = p.in + sc.row * M + r;
-                    NB2_UNROLL
-                    for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + n1 * MM);
+                    const cplx<T>* src = p.in + sc.in_row * M + r;
+                    if (p.grp_on) {
+                        NB2_UNROLL
+                        for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_keep(src + n1 * MM);
+                    } else {
+                        NB2_UNROLL
+                        for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + n1 * MM);
+                    }
                 }
                 if (p.has_pro) {
                     const long long N0N1 = 1ll << (p.g.logN0 + p.g.logN1);

@@ -86,6 +86,18 @@ def test_pipelined_passes(monkeypatch, stages):
     pc.check_metric((16, 32, 16), (1 / 16, 1 / 32, 1 / 16), np.float32)
 
 
+@pytest.mark.parametrize("planes", ["2", "4", "6", "64"])
+def test_l2_blocked_tail(monkeypatch, planes):
+    # axis-1 pass + row pass run group by group (planes k0 and N0 - k0) through the group buffer
+    monkeypatch.setenv("NB2_L2_PLANES", planes)
+    pc.check_hartley_shapes([((4, 32, 8), None), ((8, 32, 16), None), ((16, 64, 4), None), ((32, 32, 32), None)])
+    pc.check_inplace_and_roundtrip((8, 32, 16))
+    pc.check_cf_vs_oracle((16, 32, 16), 1 / 16, np.float64, None)
+    pc.check_cf_vs_oracle((16, 32, 16), (1 / 16, 1 / 32, 1 / 16), np.float32, None)
+    pc.check_metric((16, 32, 16), (1 / 16, 1 / 32, 1 / 16))
+    pc.check_metric((8, 64, 8), (1 / 8, 1 / 64, 1 / 8), np.float32)
+
+
 def test_hartley_leading_axes_inner_batch():
     # product-space sub-transforms: leading axes, contiguous inner batch (strided passes + mirror combine)
     import niftyb200 as nb

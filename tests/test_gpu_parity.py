@@ -116,6 +116,22 @@ def test_full_size_properties(shape, dt):
     assert err <= 4 * tol, err
 
 
+@pytest.mark.parametrize("planes", ["2", "6", "16"])
+def test_l2_blocked_tail(monkeypatch, planes):
+    # opt-in variant: axis-1 pass + row pass run group by group (planes k0 and N0 - k0) through an
+    # L2-resident buffer, groups alternating between two streams
+    monkeypatch.setenv("NB2_L2_PLANES", planes)
+    pc.check_hartley_shapes([((4, 32, 8), None), ((8, 32, 16), None), ((16, 64, 4), None), ((32, 32, 32), None),
+                             ((64, 128, 128), None)])
+    pc.check_inplace_and_roundtrip((8, 32, 16))
+    pc.check_inplace_and_roundtrip((128, 128, 128), np.float32)
+    pc.check_cf_vs_oracle((16, 32, 16), 1 / 16, np.float64, None)
+    pc.check_cf_vs_oracle((16, 32, 16), (1 / 16, 1 / 32, 1 / 16), np.float32, None)
+    pc.check_metric((16, 32, 16), (1 / 16, 1 / 32, 1 / 16))
+    pc.check_metric((8, 64, 8), (1 / 8, 1 / 64, 1 / 8), np.float32)
+    pc.check_cg_parity((16, 32, 16), 1 / 16, strict=False)
+
+
 def test_hartley_leading_axes_inner_batch():
     import niftyb200 as nb
     shapes = [((16, 8, 4), (0, 1)), ((64, 128, 32), (0, 1)), ((4, 32, 8), (1,)), ((3, 8, 16, 4), (1, 2)),
