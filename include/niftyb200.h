@@ -141,6 +141,8 @@ int nb2_ipc_close(void* ptr);
 
 /* Total number of kernels this library has launched in the calling process. */
 int64_t nb2_launch_count(void);
+/* How many of them were launches of the persistent TMA-fed strided pass (nb2_tma.cuh). */
+int64_t nb2_tma_launch_count(void);
 
 /* Complex-to-complex FFT, out = scale * FFT(in); forward != 0 -> exp(-i..), else exp(+i..).
  * Replaces ducc_dispatch.fftn / ifftn (src/ducc_dispatch.py:66-72; ifftn = backward, scale 1/N).

@@ -660,6 +660,7 @@ int nb2_strided_pass_remap(nb2_plan* pl, int which, const void* in, void* out, c
 }
 
 int64_t nb2_launch_count(void) { return launch_counter(); }
+int64_t nb2_tma_launch_count(void) { return tma_launch_counter(); }
 
 int nb2_c2c(nb2_plan* pl, const void* in, void* out, int forward, double scale, void* stream) {
     if (!pl || !in || !out) {

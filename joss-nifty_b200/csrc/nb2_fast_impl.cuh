@@ -2,6 +2,7 @@
 #pragma once
 
 #include "nb2_passes.cuh"
+#include "nb2_tma.cuh"
 #include "nb2_plan.h"
 #include "nb2_vector.cuh"
 
@@ -66,6 +67,44 @@ inline int pipe_threads(int nthreads, int maxt) {
     return nthreads;
 }
 
+// Persistent TMA-fed variant (nb2_tma.cuh) for the plain (un-remapped) passes of 256..1024 rows when
+// there are enough 128-byte-wide tiles to keep every SM busy.  NB2_TMA=0 falls back to StridedPass.
+template <typename T>
+int run_strided_tma(const nb2_plan* pl, int axis, int logn, long long inner, long long outer, const void* in, void* out,
+                    const nb2_pointop* pro, rt_stream st, bool* done) {
+    *done = false;
+    if (const char* e = std::getenv("NB2_TMA"))
+        if (e[0] == '0') return 0;
+    constexpr int W = sizeof(T) == 4 ? 16 : 8;
+    if (logn < 8 || logn > 10 || inner % W || !aligned16(in) || !tma_available()) return 0;
+    const long long ntiles = outer * (inner / W);
+    if (ntiles < 2ll * rt_sm_count()) return 0;
+    int rc = 0;
+#define NB2_RUN_TMA(A, C)                                        \
+    {                                                            \
+        typedef StridedTma<T, A, C> K;                           \
+        typename K::Params p;                                    \
+        p.in = (const cplx<T>*)in;                               \
+        p.out = (cplx<T>*)out;                                   \
+        p.tw = (const cplx<T>*)(axis == 0 ? pl->tw0 : pl->tw1);  \
+        p.inner = inner;                                         \
+        p.tiles_per_outer = inner / W;                           \
+        p.axis = axis;                                           \
+        p.has_pro = pro ? 1 : 0;                                 \
+        p.pro = to_pointop<T>(pro, nullptr);                     \
+        p.g = pl->g;                                             \
+        rc = rt_launch_tma<K, T>(ntiles, outer, st, p);          \
+    }
+    switch (logn) {
+        case 8: NB2_RUN_TMA(16, 16) break;
+        case 9: NB2_RUN_TMA(32, 16) break;
+        default: NB2_RUN_TMA(32, 32) break;
+    }
+#undef NB2_RUN_TMA
+    *done = rc == 0;
+    return rc;
+}
+
 template <typename T>
 int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st,
                 const RowRemap* rm) {
@@ -74,6 +113,12 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         return NB2_ERR_ARG;
     }
     const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
+    if (!rm) {
+        bool done = false;
+        const int rc = run_strided_tma<T>(pl, axis, logn, inner, axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0),
+                                          in, out, pro, st, &done);
+        if (rc || done) return rc;
+    }
     const long long outer = (rm && rm->grp_on) ? rm->grp_n : axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
     const long long ncols = (rm && rm->ncols) ? rm->ncols : inner;
     const long long run = (rm && rm->run) ? rm->run : ncols;

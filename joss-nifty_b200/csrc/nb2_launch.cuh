@@ -30,6 +30,10 @@ inline long long& launch_counter() {
     static long long n = 0;
     return n;
 }
+inline long long& tma_launch_counter() {
+    static long long n = 0;
+    return n;
+}
 
 #if !defined(NB2_EMU)
 // ------------------------------------------------------------------ device runtime

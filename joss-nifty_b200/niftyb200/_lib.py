@@ -65,6 +65,7 @@ class Library:
         "nb2_ipc_open": (c_int, [c_void_p, POINTER(c_void_p)]),
         "nb2_ipc_close": (c_int, [c_void_p]),
         "nb2_launch_count": (c_int64, []),
+        "nb2_tma_launch_count": (c_int64, []),
         "nb2_c2c": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double, c_void_p]),
         "nb2_vdot": (c_int, [c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
         "nb2_axpby": (c_int, [c_int, c_int64, c_double, c_void_p, c_double, c_void_p, c_void_p]),

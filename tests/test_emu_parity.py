@@ -98,6 +98,27 @@ def test_l2_blocked_tail(monkeypatch, planes):
     pc.check_metric((8, 64, 8), (1 / 8, 1 / 64, 1 / 8), np.float32)
 
 
+def test_tma_strided_pass(emu, monkeypatch):
+    # persistent TMA-fed strided pass (nb2_tma.cuh): 256..1024 rows, 128-byte tiles, both precisions,
+    # with the fused amplitude prologues; NB2_TMA=0 must give the same answers through StridedPass
+    n0 = emu.nb2_tma_launch_count()
+    shapes = [((256, 256), None), ((512, 64), None), ((1024, 128), None), ((4, 256, 64), None), ((256, 4, 64), None),
+              ((256, 256, 32), None)]
+    pc.check_hartley_shapes(shapes)
+    assert emu.nb2_tma_launch_count() > n0
+    n0 = emu.nb2_tma_launch_count()
+    pc.check_cf_vs_oracle((256, 256), 1 / 256, np.float64, None)
+    pc.check_cf_vs_oracle((256, 8, 64), (1 / 256, 1 / 8, 1 / 64), np.float32, None)
+    pc.check_metric((256, 256), 1 / 256)
+    pc.check_metric((512, 8, 32), (1 / 512, 1 / 8, 1 / 32), np.float32)
+    pc.check_inplace_and_roundtrip((256, 256))
+    assert emu.nb2_tma_launch_count() > n0
+    n0 = emu.nb2_tma_launch_count()
+    monkeypatch.setenv("NB2_TMA", "0")
+    pc.check_hartley_shapes(shapes[:2])
+    assert emu.nb2_tma_launch_count() == n0
+
+
 def test_hartley_leading_axes_inner_batch():
     # product-space sub-transforms: leading axes, contiguous inner batch (strided passes + mirror combine)
     import niftyb200 as nb

@@ -132,6 +132,28 @@ def test_l2_blocked_tail(monkeypatch, planes):
     pc.check_cg_parity((16, 32, 16), 1 / 16, strict=False)
 
 
+def test_tma_strided_pass(cuda, monkeypatch):
+    # persistent TMA-fed strided pass (nb2_tma.cuh): 256..1024 rows, both precisions, fused prologues;
+    # NB2_TMA=0 must give the same answers through StridedPass
+    n0 = cuda.nb2_tma_launch_count()
+    shapes = [((1024, 16, 1024), None), ((16, 1024, 1024), None), ((512, 32, 512), None), ((32, 512, 512), None),
+              ((256, 64, 512), None), ((64, 256, 512), None), ((1024, 16384), None), ((256, 256, 256), None)]
+    pc.check_hartley_shapes(shapes)
+    assert cuda.nb2_tma_launch_count() >= n0 + 2 * len(shapes)
+    n0 = cuda.nb2_tma_launch_count()
+    pc.check_cf_vs_oracle((256, 64, 512), (1 / 256, 1 / 64, 1 / 512), np.float64, None)
+    pc.check_cf_vs_oracle((1024, 16, 1024), (1 / 1024, 1 / 16, 1 / 1024), np.float32, None)
+    pc.check_metric((512, 32, 512), (1 / 512, 1 / 32, 1 / 512))
+    pc.check_metric((1024, 16, 1024), (1 / 1024, 1 / 16, 1 / 1024), np.float32)
+    pc.check_inplace_and_roundtrip((256, 256, 256), np.float32)
+    pc.check_inplace_and_roundtrip((512, 32, 512))
+    assert cuda.nb2_tma_launch_count() > n0
+    n0 = cuda.nb2_tma_launch_count()
+    monkeypatch.setenv("NB2_TMA", "0")
+    pc.check_hartley_shapes(shapes[:2])
+    assert cuda.nb2_tma_launch_count() == n0
+
+
 def test_hartley_leading_axes_inner_batch():
     import niftyb200 as nb
     shapes = [((16, 8, 4), (0, 1)), ((64, 128, 32), (0, 1)), ((4, 32, 8), (1,)), ((3, 8, 16, 4), (1, 2)),
