@@ -313,13 +313,14 @@ def run_b200(args):
                     continue
                 passes[names[which]] = tk(lambda w=which: plan.run_pass(w, a, b))
             if len(shape) > 1:
-                pros = PointOp(tabs.amp_mode, tabs.amp, tabs.azm)
+                pros = PointOp(tabs.amp_mode, tabs.amp, tabs.azm, amp_sym=tabs.sym)
                 passes["StridedPass(first axis)+amplitude field"] = tk(lambda: plan.run_pass(3 - len(shape), a, b, pro=pros))
                 passes["StridedPass(first axis)+amplitude gather"] = tk(lambda: plan.run_pass(3 - len(shape), a, b, pro=pro))
             passes["RowPass+weight (metric fwd epilogue)"] = tk(lambda: plan.run_pass(
                 2, a, b, epi=PointOp(scale=cf.dvol, mul=M.w)))
             passes["RowPass+amplitude field+add+dot (metric adj epilogue)"] = tk(lambda: plan.run_pass(
-                2, a, b, epi=PointOp(tabs.amp_mode, tabs.amp, tabs.azm * cf.dvol, add=x0, dot=x0, dot_out=M._curv)))
+                2, a, b, epi=PointOp(tabs.amp_mode, tabs.amp, tabs.azm * cf.dvol, add=x0, dot=x0, dot_out=M._curv,
+                                     amp_sym=tabs.sym)))
         t_upd = tk(lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r))
         t_axp = tk(lambda: loop.vec.axpby(1.0, loop.r, 1.0, b))
         # the kernels that run inside one CG iteration (the gather variant is reported, not used there)

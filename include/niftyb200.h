@@ -48,10 +48,16 @@ typedef struct nb2_plan nb2_plan;
  *               axes (isotropic grids; replaces PowerDistributor's gather through the int64
  *               pindex, src/operators/distributors.py:114-119, src/domains/power_space.py:170-198);
  *               fast path only
- *   amp_mode 2: amp = full-size factor field of one batch item (any grid) */
+ *   amp_mode 2: amp = full-size factor field of one batch item (any grid).
+ *               amp_flags & NB2_AMP_SYMMETRIC: the caller guarantees field[k] == field[-k mod N] along
+ *               every transformed axis (true for every amplitude that is a function of the per-axis
+ *               mode lengths, i.e. every PowerDistributor output, rg_space.py:105-116).  The fast-path
+ *               kernels then read the canonical member of each mirror pair of rows, so the second
+ *               read of a pair is served by L2 instead of HBM.  Results are bit-identical. */
+#define NB2_AMP_SYMMETRIC 1
 typedef struct nb2_pointop {
     int32_t amp_mode;
-    int32_t reserved;
+    int32_t amp_flags;   /* NB2_AMP_SYMMETRIC or 0 */
     const void* amp;
     double scale;
     const void* mul;

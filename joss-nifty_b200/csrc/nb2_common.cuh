@@ -191,6 +191,23 @@ template <typename T> NB2_HD vec4<T> ld4_ro(const T* p) {
 #endif
     return r;
 }
+// default L2 policy, bypassing L1 (data that another CTA will ask for again soon)
+template <typename T> NB2_HD vec4<T> ld4_keep(const T* p) {
+    vec4<T> r;
+#if defined(__CUDA_ARCH__)
+    if (sizeof(T) == 4) {
+        const float4 t = __ldcg(reinterpret_cast<const float4*>(p));
+        r.v[0] = T(t.x); r.v[1] = T(t.y); r.v[2] = T(t.z); r.v[3] = T(t.w);
+    } else {
+        const double2 t0 = __ldcg(reinterpret_cast<const double2*>(p));
+        const double2 t1 = __ldcg(reinterpret_cast<const double2*>(p) + 1);
+        r.v[0] = T(t0.x); r.v[1] = T(t0.y); r.v[2] = T(t1.x); r.v[3] = T(t1.y);
+    }
+#else
+    for (int i = 0; i < 4; ++i) r.v[i] = p[i];
+#endif
+    return r;
+}
 template <typename T> NB2_HD void st4_stream(T* p, const vec4<T>& r) {
 #if defined(__CUDA_ARCH__)
     if (sizeof(T) == 4) {

@@ -77,6 +77,7 @@ int run_strided_tma(const nb2_plan* pl, int axis, int logn, long long inner, lon
         if (e[0] == '0') return 0;
     constexpr int W = sizeof(T) == 4 ? 16 : 8;
     if (logn < 8 || logn > 10 || inner % W || !aligned16(in) || !tma_available()) return 0;
+    if (pro && pro->amp_mode == 1) return 0;   // table gather: the batched loads of StridedPass are faster
     const long long ntiles = outer * (inner / W);
     if (ntiles < 2ll * rt_sm_count()) return 0;
     int rc = 0;

@@ -63,6 +63,22 @@ template <int R, typename T> NB2_HD void tw_powers(cplx<T> w1, cplx<T> (&w)[R]) 
     }
 }
 
+// Rows of a streamed amplitude field (amp_mode 2) along the transformed axis of a strided pass.
+// sym (NB2_AMP_SYMMETRIC): row j > N/2 equals row N - j, so the canonical row is read instead -- with
+// the default L2 policy, because its other reader (same CTA, a little earlier or later) finds it there.
+template <typename T>
+struct FieldRows {
+    const cplx<T>* base;   // element (row 0, this thread's column)
+    long long inner;
+    int n;
+    bool sym;
+    NB2_HD FieldRows(const cplx<T>* b, long long in, int nn, bool s) : base(b), inner(in), n(nn), sym(s) {}
+    NB2_HD cplx<T> load(int row) const {
+        if (sym) return ldc_keep(base + (long long)(row <= n - row ? row : n - row) * inner);
+        return ldc_stream(base + (long long)row * inner);
+    }
+};
+
 // ============================================================================ StridedPass
 template <typename T, int R1, int R2, int R3>
 struct StridedPass {
@@ -188,18 +204,16 @@ struct StridedPass {
                         }
                     } else if (p.pro.amp_mode == 2) {
                         const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
-                        const cplx<T>* fsrc = reinterpret_cast<const cplx<T>*>(p.pro.amp) +
-                                              ((base + c + (long long)r * p.inner) & itemmask);
-                        const long long fstride = (long long)MM * p.inner;
+                        const FieldRows<T> fr(reinterpret_cast<const cplx<T>*>(p.pro.amp) + ((base + c) & itemmask), p.inner,
+                                              N, p.pro.amp_sym && !(p.axis == 0 ? p.g.shift0 : p.g.shift1));
                         cplx<T> f[2][PB];
                         NB2_UNROLL
-                        for (int i = 0; i < PB; ++i) f[0][i] = ldc_stream(fsrc + i * fstride);
+                        for (int i = 0; i < PB; ++i) f[0][i] = fr.load(r + i * MM);
                         NB2_UNROLL
                         for (int g = 0; g < NBATCH; ++g) {
                             if (g + 1 < NBATCH) {
                                 NB2_UNROLL
-                                for (int i = 0; i < PB; ++i)
-                                    f[(g + 1) & 1][i] = ldc_stream(fsrc + ((g + 1) * PB + i) * fstride);
+                                for (int i = 0; i < PB; ++i) f[(g + 1) & 1][i] = fr.load(r + ((g + 1) * PB + i) * MM);
                             }
                             NB2_UNROLL
                             for (int i = 0; i < PB; ++i) {
@@ -370,6 +384,7 @@ struct RowPass {
     struct SlotCache {
         long long row;  // linear row index over (batch, N0, N1)
         long long in_row;  // row index in the input buffer (differs from `row` for group buffers)
+        long long frow;    // row (inside one item) whose amplitude-field values this slot uses
         int f01;        // ksq contribution of (k0, k1)
         int flags;      // bit 0: valid, bit 1: duplicate of its partner (self-mirrored row)
     };
@@ -475,7 +490,7 @@ struct RowPass {
                 L.f.v[i] = ld_ro(e.amp + f01 + km * km);
             }
         } else if (e.amp_mode == 2) {
-            L.f = ld4_stream(e.amp + item);
+            L.f = e.amp_sym ? ld4_keep(e.amp + item) : ld4_stream(e.amp + item);
         }
         if (e.mul) L.m = ld4_stream(e.mul + idx);
         if (e.add) L.a = ld4_stream(e.add + idx);
@@ -516,6 +531,17 @@ struct RowPass {
                                       : (((rs.k0 < p.grp_hi_a ? rs.k0 - p.grp_lo_a : p.grp_lo_n + (rs.k0 - p.grp_hi_a))
                                           << p.g.logN1) + rs.k1);
                 sc.f01 = int(sq_mirror(rs.k0, p.g.logN0) + sq_mirror(rs.k1, p.g.logN1));
+                {
+                    // NB2_AMP_SYMMETRIC: the field rows (+-k0, +-k1) are equal -- every one of them reads
+                    // the canonical row (min(k0, N0 - k0), min(k1, N1 - k1)); its repeats come from L2
+                    const long long N0 = 1ll << p.g.logN0, N1 = 1ll << p.g.logN1;
+                    long long f0 = rs.k0, f1 = rs.k1;
+                    if (p.epi.amp_sym && !p.g.shift0 && !p.g.shift1) {
+                        f0 = f0 <= N0 - f0 ? f0 : N0 - f0;
+                        f1 = f1 <= N1 - f1 ? f1 : N1 - f1;
+                    }
+                    sc.frow = (f0 << p.g.logN1) + f1;
+                }
                 sc.flags = (rs.valid ? 1 : 0) | (rs.dup ? 2 : 0);
                 slot_cache(p, smem_raw, nthreads)[s] = sc;
             }
@@ -634,7 +660,7 @@ struct RowPass {
                     const SlotCache sc = cache[s];
                     if (sc.flags != 1) continue;          // invalid, or the duplicate of a self-mirrored row
                     const long long rowbase = sc.row * (2 * M);
-                    const long long itembase = (sc.row & (itemrows - 1)) * (2 * M);
+                    const long long itembase = sc.frow * (2 * M);   // == the slot's own row unless amp_sym
                     const int f01 = sc.f01;
                     EpiLoads L1, L2;
                     epi_fetch(e, L1, f01, k, false, itembase + k, rowbase + k);

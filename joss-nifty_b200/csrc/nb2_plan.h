@@ -76,6 +76,7 @@ template <typename T>
 PointOp<T> to_pointop(const nb2_pointop* o, double* partials) {
     PointOp<T> r;
     r.amp_mode = o ? o->amp_mode : 0;
+    r.amp_sym = (o && o->amp_mode == 2 && (o->amp_flags & NB2_AMP_SYMMETRIC)) ? 1 : 0;
     r.amp = o ? (const T*)o->amp : nullptr;
     r.scale = o ? (T)o->scale : T(1);
     r.mul = o ? (const T*)o->mul : nullptr;

@@ -20,6 +20,7 @@ namespace nb2 {
 template <typename T>
 struct PointOp {
     int amp_mode;        // 0: none, 1: table[ksq], 2: full-size field (one batch item, broadcast over batch)
+    int amp_sym;         // amp_mode 2 only: field[k] == field[-k] along the transformed axes (NB2_AMP_SYMMETRIC)
     const T* amp;        // table or field
     T scale;             // multiplies the value (volume factor, azm, ...)
     const T* mul;        // optional element-wise multiplier (full array incl. batch), epilogue only

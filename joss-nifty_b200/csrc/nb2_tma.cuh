@@ -82,10 +82,10 @@ struct StridedTma {
         long long o, tc;
         const long long base = tile_base(p, tile, o, tc);
         const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
-        const cplx<T>* fsrc = reinterpret_cast<const cplx<T>*>(p.pro.amp) + ((base + c + (long long)r * p.inner) & itemmask);
-        const long long fstride = (long long)MM * p.inner;
+        const FieldRows<T> fr(reinterpret_cast<const cplx<T>*>(p.pro.amp) + ((base + c) & itemmask), p.inner, N,
+                              p.pro.amp_sym && !(p.axis == 0 ? p.g.shift0 : p.g.shift1));
         NB2_UNROLL
-        for (int i = 0; i < PB; ++i) R.f0[i] = ldc_stream(fsrc + i * fstride);
+        for (int i = 0; i < PB; ++i) R.f0[i] = fr.load(r + i * MM);
     }
 
     // ---- stage 0b: tile rows from P into registers
@@ -105,9 +105,8 @@ struct StridedTma {
             const long long base = tile_base(p, tile, o, tc);
             if (p.pro.amp_mode == 2) {
                 const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
-                const cplx<T>* fsrc =
-                    reinterpret_cast<const cplx<T>*>(p.pro.amp) + ((base + c + (long long)r * p.inner) & itemmask);
-                const long long fstride = (long long)MM * p.inner;
+                const FieldRows<T> fr(reinterpret_cast<const cplx<T>*>(p.pro.amp) + ((base + c) & itemmask), p.inner, N,
+                                      p.pro.amp_sym && !(p.axis == 0 ? p.g.shift0 : p.g.shift1));
                 cplx<T> f[2][PB];
                 NB2_UNROLL
                 for (int i = 0; i < PB; ++i) f[0][i] = R.f0[i];
@@ -115,7 +114,7 @@ struct StridedTma {
                 for (int g = 0; g < NBATCH; ++g) {
                     if (g + 1 < NBATCH) {
                         NB2_UNROLL
-                        for (int i = 0; i < PB; ++i) f[(g + 1) & 1][i] = ldc_stream(fsrc + ((g + 1) * PB + i) * fstride);
+                        for (int i = 0; i < PB; ++i) f[(g + 1) & 1][i] = fr.load(r + ((g + 1) * PB + i) * MM);
                     }
                     NB2_UNROLL
                     for (int i = 0; i < PB; ++i) {

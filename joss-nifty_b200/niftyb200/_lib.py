@@ -23,7 +23,7 @@ class PointOp(ctypes.Structure):
 
     _fields_ = [
         ("amp_mode", c_int32),
-        ("reserved", c_int32),
+        ("amp_flags", c_int32),
         ("amp", c_void_p),
         ("scale", c_double),
         ("mul", c_void_p),

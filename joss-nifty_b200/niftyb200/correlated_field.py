@@ -189,8 +189,11 @@ class CorrelatedFieldMaker:
 class Tables:
     """Everything the hot tail needs for one expansion point: device-resident."""
 
-    def __init__(self, amp_mode, amp, azm, amps):
+    def __init__(self, amp_mode, amp, azm, amps, sym=False):
         self.amp_mode, self.amp, self.azm, self.amps = amp_mode, amp, float(azm), amps
+        # amp_mode-2 fields built from per-axis mode lengths satisfy field[k] == field[-k] along every
+        # axis (rg_space.py:105-116): the kernels may read each mirror pair of rows once (NB2_AMP_SYMMETRIC)
+        self.sym = bool(sym) and amp_mode == 2
 
 
 class CorrelatedField:
@@ -250,7 +253,7 @@ class CorrelatedField:
         for a, g in zip(amps, self.grids):
             e = g.expand(a, torch.float64)
             full = e if full is None else torch.tensordot(full, e, dims=0)    # outer_amplitude :681-688
-        return Tables(2, full.to(self.dtype).contiguous(), azm, amps)
+        return Tables(2, full.to(self.dtype).contiguous(), azm, amps, sym=True)
 
     def streaming_tables(self, tab):
         """Tables with the gather resolved once: ``field = azm * amp[pindex]`` as a full-size
@@ -259,7 +262,7 @@ class CorrelatedField:
         if tab.amp_mode != 1:
             return tab
         field = self.plans[0].expand_table(tab.amp, scale=tab.azm)
-        st = Tables(2, field, 1.0, tab.amps)
+        st = Tables(2, field, 1.0, tab.amps, sym=True)
         st.azm_value = tab.azm        # the factor folded into the field
         return st
 
@@ -267,7 +270,7 @@ class CorrelatedField:
     def apply_xi(self, xi, tab, out=None, convention=None, offset=None, mul=None):
         """``offset + prod_g (1/V_g) hartley_g(azm * amp[pindex] * xi)`` on device tensors."""
         off = self.offset_mean if offset is None else offset
-        pro = PointOp(tab.amp_mode, tab.amp, tab.azm)
+        pro = PointOp(tab.amp_mode, tab.amp, tab.azm, amp_sym=getattr(tab, "sym", False))
         if self.single:
             return self.plans[0].hartley(xi, out=out, convention=convention, pro=pro,
                                          epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))
@@ -280,7 +283,8 @@ class CorrelatedField:
     def adjoint_xi(self, ybar, tab, out=None, convention=None, add=None, dot=None, dot_out=None):
         """xi-block of the VJP: ``azm * amp[pindex] * prod_g (1/V_g) hartley_g(ybar)`` (Hartley is
         symmetric: harmonic_operators.py:213-217).  Optional fused ``+ add`` and ``dot``."""
-        epi = PointOp(tab.amp_mode, tab.amp, tab.azm * self.dvol, add=add, dot=dot, dot_out=dot_out)
+        epi = PointOp(tab.amp_mode, tab.amp, tab.azm * self.dvol, add=add, dot=dot, dot_out=dot_out,
+                      amp_sym=getattr(tab, "sym", False))
         if self.single:
             return self.plans[0].hartley(ybar, out=out, convention=convention, epi=epi)
         cur = self.plans[-1].hartley(ybar, out=out, convention=convention)
@@ -301,7 +305,8 @@ class CorrelatedField:
         if self.single and self.grids[0].isotropic and self.plans[0].is_fast:
             g = self.grids[0]
             bins = torch.zeros(self.plans[0].ksq_size, dtype=torch.float64, device=self.device)
-            epi = PointOp(tab.amp_mode, tab.amp, tab.azm * self.dvol, bin_x=xi, bin_out=bins)
+            epi = PointOp(tab.amp_mode, tab.amp, tab.azm * self.dvol, bin_x=xi, bin_out=bins,
+                          amp_sym=getattr(tab, "sym", False))
             xibar = self.plans[0].hartley(ybar, convention=convention, epi=epi)
             # bins[ksq] = sum_i xi_i * (azm' * h_i) over the points of that ksq, azm' = tab.azm
             per_bin = bins[g.unique_ksq.to(self.device)]

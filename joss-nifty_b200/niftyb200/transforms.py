@@ -80,8 +80,9 @@ class PointOp:
     Keeps references to the tensors so they stay alive while the kernel runs."""
 
     def __init__(self, amp_mode=0, amp=None, scale=1.0, mul=None, add=None, add_scalar=0.0,
-                 dot=None, dot_out=None, bin_x=None, bin_out=None):
+                 dot=None, dot_out=None, bin_x=None, bin_out=None, amp_sym=False):
         self.amp_mode, self.amp, self.scale = int(amp_mode), amp, float(scale)
+        self.amp_sym = bool(amp_sym)      # NB2_AMP_SYMMETRIC: amp_mode-2 field with field[k] == field[-k]
         self.mul, self.add, self.add_scalar = mul, add, float(add_scalar)
         self.dot, self.dot_out = dot, dot_out
         self.bin_x, self.bin_out = bin_x, bin_out
@@ -89,6 +90,7 @@ class PointOp:
     def to_c(self, lib):
         c = _lib.PointOp()
         c.amp_mode = self.amp_mode
+        c.amp_flags = 1 if (self.amp_sym and self.amp_mode == 2) else 0
         c.amp = _ptr(lib, self.amp, "amp")
         c.scale = self.scale
         c.mul = _ptr(lib, self.mul, "mul")

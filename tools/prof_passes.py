@@ -26,12 +26,13 @@ epi_f = PointOp(scale=cf.dvol, add_scalar=0.0, mul=M.w)
 curv = torch.zeros((), dtype=torch.float64, device="cuda")
 epi_a = PointOp(tab.amp_mode, tab.amp, tab.azm * cf.dvol, add=x0, dot=x0, dot_out=curv)
 only = os.environ.get("PROF_ONLY")
+SYM = M.tab.sym and os.environ.get("PROF_SYM", "1") != "0"   # NB2_AMP_SYMMETRIC reads of the streamed field
 cases = [("strided0", lambda: plan.run_pass(0, a, b)), ("strided1", lambda: plan.run_pass(1, a, b)),
          ("rows", lambda: plan.run_pass(2, a, b)), ("strided0+amp", lambda: plan.run_pass(0, a, b, pro=pro)),
          ("rows+mul", lambda: plan.run_pass(2, a, b, epi=epi_f)), ("rows+amp+add+dot", lambda: plan.run_pass(2, a, b, epi=epi_a)),
-         ("strided0+field", lambda: plan.run_pass(0, a, b, pro=PointOp(M.tab.amp_mode, M.tab.amp, M.tab.azm))),
+         ("strided0+field", lambda: plan.run_pass(0, a, b, pro=PointOp(M.tab.amp_mode, M.tab.amp, M.tab.azm, amp_sym=SYM))),
          ("rows+field+add+dot", lambda: plan.run_pass(2, a, b, epi=PointOp(M.tab.amp_mode, M.tab.amp, M.tab.azm * cf.dvol,
-                                                                             add=x0, dot=x0, dot_out=curv))),
+                                                                             add=x0, dot=x0, dot_out=curv, amp_sym=SYM))),
          ("cg_update", lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r)),
          ("axpby", lambda: loop.vec.axpby(1.0, loop.r, 1.0, b))]
 if os.environ.get("PROF_NCU"):
