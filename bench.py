@@ -327,13 +327,33 @@ def run_b200(args):
         # ALGORITHMIC bytes per launch: every full-size operand once
         # (the curvature dot re-reads the array that is added, so add+dot count once)
         kbytes = {k: (2 + ("field" in k) + ("weight" in k) + ("add" in k)) * N * s for k in passes}
-        in_step = {k: v for k, v in passes.items() if v and "gather" not in k}
-        dom = max(in_step, key=lambda k: in_step[k]) if in_step else None
-        if dom:
-            ach = kbytes[dom] / (passes[dom] * 1e-3) / 1e9
-            out["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
-                               "frac": ach / peak, "traffic": None, "peak_source": peak_src,
-                               "algorithmic_bytes_per_launch": kbytes[dom]}
+        # The launches of ONE CG iteration grouped by kernel function; the dominant kernel is the one with
+        # the largest share of the step.  achieved = algorithmic bytes per launch / average launch duration.
+        f0 = "StridedPass(first axis)+amplitude field"
+        groups = {}
+        if len(shape) == 3 and all(passes.get(k) for k in (f0, names[0], names[1])):
+            groups["strided pass (StridedTma / StridedPass): first axis + amplitude field, axis 1, axis 0, axis 1"] = \
+                [f0, names[1], names[0], names[1]]
+        elif len(shape) == 2 and passes.get(f0) and passes.get(names[1]):
+            groups["strided pass (StridedTma / StridedPass): axis 1 + amplitude field, axis 1"] = [f0, names[1]]
+        rk = ["RowPass+weight (metric fwd epilogue)", "RowPass+amplitude field+add+dot (metric adj epilogue)"]
+        if all(passes.get(k) for k in rk):
+            groups["row pass (RowPass): + weight, + amplitude field + add + curvature dot"] = rk
+        gsum = {g: (sum(passes[k] for k in ks), sum(kbytes[k] for k in ks), len(ks)) for g, ks in groups.items()}
+        gsum["CgUpdate (+3 dots)"] = (t_upd, 7 * N * s, 1)
+        gsum["Axpby"] = (t_axp, 3 * N * s, 1)
+        dom = max(gsum, key=lambda g: gsum[g][0])
+        t_dom, b_dom, n_dom = gsum[dom]
+        ach = b_dom / (t_dom * 1e-3) / 1e9
+        # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, one `ncu --set full` capture,
+        # profiles/r1_ncu_full_v3_passes_f32_1024.csv), known for the headline grid only
+        traffic = None
+        if shape == (1024, 1024, 1024) and args.dtype == "f32" and dom.startswith("strided"):
+            traffic = (10.701343e9 + 8.532932e9 + 8.541014e9 + 8.532932e9) / 4
+        out["roofline"] = {"bound": "hbm", "kernel": dom, "launches_per_step": n_dom, "achieved": ach, "peak": peak,
+                           "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
+                           "algorithmic_bytes_per_launch": b_dom / n_dom, "avg_launch_ms": t_dom / n_dom,
+                           "share_of_step": {g: v[0] / sum(x[0] for x in gsum.values()) for g, v in gsum.items()}}
         out["extra"].update({
             "fwd_applies_per_s": 1000.0 / t_fwd, "adj_applies_per_s": 1000.0 / t_adj,
             "fwd_adj_pairs_per_s": 1000.0 / (t_fwd + t_adj),

@@ -96,6 +96,15 @@ template <int BYTES> NB2_HD void cp_async(void* smem_dst, const void* gmem_src) 
     for (int i = 0; i < BYTES; ++i) ((char*)smem_dst)[i] = ((const char*)gmem_src)[i];
 #endif
 }
+// Bulk L2 prefetch (cp.async.bulk.prefetch.L2): asks the memory system to bring `bytes` (multiple of
+// 16, 16-byte aligned) into L2 without occupying registers, shared memory or a load slot.
+NB2_HD void prefetch_l2(const void* gmem_src, unsigned bytes) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");
+#else
+    (void)gmem_src; (void)bytes;
+#endif
+}
 NB2_HD void cp_async_commit() {
 #if defined(__CUDA_ARCH__)
     asm volatile("cp.async.commit_group;" ::: "memory");

@@ -203,6 +203,34 @@ int choose_G(int logm, long long Q) {
     return G;
 }
 
+// rows of at least 16 bytes, a multiple of 16
+#define M_BYTES_OK(M, T) ((size_t(M) * sizeof(cplx<T>)) % 16 == 0)
+// L2 prefetch distance of the row pass (cp.async.bulk.prefetch.L2 of a later CTA's rows).  MEASURED on
+// B200 (profiles/r1_rowpass_l2_prefetch.log): no gain at any distance -- the row pass is bound by issue
+// slots and shared-memory traffic, not by DRAM latency -- so it is OFF unless NB2_ROWS_LA=n asks for a
+// distance of n CTAs (NB2_ROWS_LA=auto: the number of CTAs resident at once).
+template <class K>
+long long rows_lookahead(int nthreads, size_t smem) {
+    const char* e = std::getenv("NB2_ROWS_LA");
+    if (!e) return 0;
+    if (e[0] != 'a') return std::atoll(e);
+#if !defined(NB2_EMU)
+    static thread_local int c_threads = 0, c_per_sm = 0;     // per kernel instantiation
+    static thread_local size_t c_smem = 0;
+    if (c_threads != nthreads || c_smem != smem) {
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb2_kernel<K>, nthreads, smem) != cudaSuccess)
+            per_sm = 0;
+        c_threads = nthreads;
+        c_smem = smem;
+        c_per_sm = per_sm;
+    }
+    return (long long)c_per_sm * rt_sm_count();
+#else
+    return 8;
+#endif
+}
+
 template <typename T>
 int rows_pairs_per_cta(const nb2_plan* pl) {
     const RowPairs rp = row_pairs(pl->g);
@@ -256,6 +284,8 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
         p.bid0 = grp ? grp->q0 / G : 0;                                                       \
         p.q_end = grp ? grp->q_end : rp.Q;                                                    \
         p.grp_on = grp ? 1 : 0;                                                               \
+        p.la = 0;                                                                             \
+        p.bid_end = p.bid0 + launch_grid;                                                     \
         p.grp_lo_a = grp ? grp->lo_a : 0;                                                     \
         p.grp_lo_n = grp ? grp->lo_n : 0;                                                     \
         p.grp_hi_a = grp ? grp->hi_a : 0;                                                     \
@@ -271,6 +301,8 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
             p.staged = 1;                                                                     \
             rc = rt_launch_pipe<K>(grid, 0, nthreads, smem, stages, st, p);                   \
         } else {                                                                              \
+            if (!grp && M_BYTES_OK(A * B * C, T) && launch_grid >= 8ll * rt_sm_count())        \
+                p.la = rows_lookahead<K>(nthreads, smem);                                     \
             rc = rt_launch<K>(launch_grid, nthreads, smem, st, p);                            \
         }                                                                                     \
     }

@@ -376,6 +376,9 @@ struct RowPass {
         // rows from a group buffer in which natural plane k0 is plane
         //   k0 < grp_hi_a ? k0 - grp_lo_a : grp_lo_n + (k0 - grp_hi_a)
         long long bid0, q_end;
+        // L2 prefetch distance in CTAs (0: off): CTA b asks for the rows -- input and streamed epilogue
+        // operands -- of CTA b + la, which becomes resident about when this one retires
+        long long la, bid_end;
         int grp_on;
         long long grp_lo_a, grp_lo_n, grp_hi_a;
     };
@@ -544,6 +547,19 @@ struct RowPass {
                 }
                 sc.flags = (rs.valid ? 1 : 0) | (rs.dup ? 2 : 0);
                 slot_cache(p, smem_raw, nthreads)[s] = sc;
+                if (p.la > 0 && bid + p.la < p.bid_end) {
+                    const RowSlot rf = slot_info(p, bid + p.la, s);
+                    if (rf.valid && !rf.dup) {
+                        const unsigned rb = unsigned(M * sizeof(cplx<T>));
+                        prefetch_l2(p.in + rf.row * M, rb);
+                        if (p.epi.mul) prefetch_l2(p.epi.mul + rf.row * (2 * M), rb);
+                        if (p.epi.add) prefetch_l2(p.epi.add + rf.row * (2 * M), rb);
+                        if (p.epi.dot && p.epi.dot != p.epi.add) prefetch_l2(p.epi.dot + rf.row * (2 * M), rb);
+                        if (p.epi.bin_x) prefetch_l2(p.epi.bin_x + rf.row * (2 * M), rb);
+                        if (p.epi.amp_mode == 2 && !p.epi.amp_sym)
+                            prefetch_l2(p.epi.amp + (rf.row & ((1ll << (p.g.logN0 + p.g.logN1)) - 1)) * (2 * M), rb);
+                    }
+                }
             }
         } else if (PH == 1) {
             const int nb = nslots * MM;
