@@ -133,6 +133,17 @@ int nb2_strided_pass_remap(nb2_plan* plan, int which, const void* in, void* out,
                            int64_t out_outer_stride, int64_t col0, int64_t ncols, int64_t run, int64_t run_stride,
                            void* stream);
 
+/* Scatter form of the same idea (peer-memory exchange): natural input; output row j of outer item o,
+ * natural complex column col (0 <= col < inner, M = complex length of the last axis) is stored at
+ *   out + out_rowoff[j] + (out_outer_off ? out_outer_off[o] : 0)
+ *       + (out_col_off ? out_col_off[col / M] + col % M : col)
+ * so that a rank can store every row straight into its owner's buffer IN THE OWNER'S NATURAL LAYOUT
+ * (the pass after the exchange then needs no table).  Tables are device int64 arrays of complex
+ * offsets; out_rowoff is mandatory.  Cannot run in place. */
+int nb2_strided_pass_scatter(nb2_plan* plan, int which, const void* in, void* out, const nb2_pointop* pro,
+                             const int64_t* out_rowoff, const int64_t* out_outer_off, const int64_t* out_col_off,
+                             void* stream);
+
 /* Peer-visible device buffers for the slab exchange: with row-offset tables that point into the
  * peers' mapped buffers (offsets relative to `out`, unified virtual addressing), the strided pass
  * before the exchange stores its output straight into the other GPUs' memory over NVLink -- the

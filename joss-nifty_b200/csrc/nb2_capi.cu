@@ -659,6 +659,26 @@ int nb2_strided_pass_remap(nb2_plan* pl, int which, const void* in, void* out, c
                                 : run_strided<double>(pl, which, in, out, pro, st, &rm);
 }
 
+int nb2_strided_pass_scatter(nb2_plan* pl, int which, const void* in, void* out, const nb2_pointop* pro,
+                             const int64_t* out_rowoff, const int64_t* out_outer_off, const int64_t* out_col_off,
+                             void* stream) {
+    if (!pl || !in || !out || !out_rowoff || which < 0 || which > 1 || in == out) {
+        last_error() = "nb2_strided_pass_scatter: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (!pl->fast || (which == 0 && !pl->g.logN0) || (which == 1 && !pl->g.logN1)) {
+        last_error() = "nb2_strided_pass_scatter: pass not part of this plan";
+        return NB2_ERR_UNSUPPORTED;
+    }
+    RowRemap rm;
+    rm.out_rowoff = (const long long*)out_rowoff;
+    rm.out_ooff = (const long long*)out_outer_off;
+    rm.out_coloff = (const long long*)out_col_off;
+    rt_stream st = (rt_stream)stream;
+    return pl->dtype == NB2_F32 ? run_strided<float>(pl, which, in, out, pro, st, &rm)
+                                : run_strided<double>(pl, which, in, out, pro, st, &rm);
+}
+
 int64_t nb2_launch_count(void) { return launch_counter(); }
 int64_t nb2_tma_launch_count(void) { return tma_launch_counter(); }
 

@@ -71,13 +71,14 @@ inline int pipe_threads(int nthreads, int maxt) {
 // there are enough 128-byte-wide tiles to keep every SM busy.  NB2_TMA=0 falls back to StridedPass.
 template <typename T>
 int run_strided_tma(const nb2_plan* pl, int axis, int logn, long long inner, long long outer, const void* in, void* out,
-                    const nb2_pointop* pro, rt_stream st, bool* done) {
+                    const nb2_pointop* pro, rt_stream st, bool* done, const RowRemap* rm = nullptr) {
     *done = false;
     if (const char* e = std::getenv("NB2_TMA"))
         if (e[0] == '0') return 0;
     constexpr int W = sizeof(T) == 4 ? 16 : 8;
     if (logn < 8 || logn > 10 || inner % W || !aligned16(in) || !tma_available()) return 0;
     if (pro && pro->amp_mode == 1) return 0;   // table gather: the batched loads of StridedPass are faster
+    if (rm && rm->out_coloff && (1ll << pl->g.logM) < W) return 0;   // a tile must not straddle column blocks
     const long long ntiles = outer * (inner / W);
     if (ntiles < 2ll * rt_sm_count()) return 0;
     int rc = 0;
@@ -94,6 +95,10 @@ int run_strided_tma(const nb2_plan* pl, int axis, int logn, long long inner, lon
         p.has_pro = pro ? 1 : 0;                                 \
         p.pro = to_pointop<T>(pro, nullptr);                     \
         p.g = pl->g;                                             \
+        p.out_rowoff = rm ? rm->out_rowoff : nullptr;            \
+        p.out_ooff = rm ? rm->out_ooff : nullptr;                \
+        p.out_coloff = rm ? rm->out_coloff : nullptr;            \
+        p.out_ostride = rm ? rm->out_ostride : 0;                \
         rc = rt_launch_tma<K, T>(ntiles, outer, st, p);          \
     }
     switch (logn) {
@@ -114,10 +119,11 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         return NB2_ERR_ARG;
     }
     const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
-    if (!rm) {
+    // natural input, all columns: the TMA kernel (its stores may be scattered through the out tables)
+    if (!rm || (!rm->in_rowoff && !rm->ncols && !rm->grp_on && !rm->col0)) {
         bool done = false;
         const int rc = run_strided_tma<T>(pl, axis, logn, inner, axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0),
-                                          in, out, pro, st, &done);
+                                          in, out, pro, st, &done, rm);
         if (rc || done) return rc;
     }
     const long long outer = (rm && rm->grp_on) ? rm->grp_n : axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
@@ -129,6 +135,7 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
     }
     int logw = choose_logw<T>(logn, inner, rm && rm->out_rowoff);
     while ((1ll << logw) > run) --logw;
+    if (rm && rm->out_coloff && logw > pl->g.logM) logw = pl->g.logM;   // a tile must not straddle column blocks
     // developer tuning knobs (not part of the API): tile width / alternative radix plan
     if (const char* e = std::getenv("NB2_STRIDED_LOGW")) {
         const int v = std::atoi(e);
@@ -152,6 +159,8 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         p.g = pl->g;                                                                          \
         p.in_rowoff = rm ? rm->in_rowoff : nullptr;                                           \
         p.out_rowoff = rm ? rm->out_rowoff : nullptr;                                         \
+        p.out_ooff = rm ? rm->out_ooff : nullptr;                                             \
+        p.out_coloff = rm ? rm->out_coloff : nullptr;                                         \
         p.in_ostride = rm ? rm->in_ostride : 0;                                               \
         p.out_ostride = rm ? rm->out_ostride : 0;                                             \
         p.col0 = rm ? rm->col0 : 0;                                                           \

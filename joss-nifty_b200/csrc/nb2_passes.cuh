@@ -111,6 +111,11 @@ struct StridedPass {
         //   col0 + (j >> logrun) * run_stride + (j & (run - 1)),  run = 1 << logrun.
         const long long* in_rowoff;
         const long long* out_rowoff;
+        // scatter form of the output remap (nb2_strided_pass_scatter): with out_rowoff, outer item o
+        // starts at out_ooff[o] (instead of o * out_ostride) and natural column col lies at
+        // out_coloff[col >> logM] + (col & (M - 1)) (instead of col); NULL = the default rule
+        const long long* out_ooff;
+        const long long* out_coloff;
         long long in_ostride, out_ostride, col0, run_stride;
         int logrun;
         // L2-blocked tail (hartley_fast): the launch covers a GROUP of planes -- local plane o is
@@ -135,6 +140,11 @@ struct StridedPass {
         if (p.grp_on && !local) o = o < p.grp_lo_n ? p.grp_lo_a + o : p.grp_hi_a + (o - p.grp_lo_n);
         const long long tc = tile << p.logw;
         return o * N * p.inner + p.col0 + (tc >> p.logrun) * p.run_stride + (tc & ((1ll << p.logrun) - 1));
+    }
+    NB2_HD static long long out_origin(const Params& p, long long o, long long tcol) {
+        const long long oo = p.out_ooff ? ld_ro(p.out_ooff + o) : o * p.out_ostride;
+        const long long cc = p.out_coloff ? ld_ro(p.out_coloff + (tcol >> p.g.logM)) + (tcol & ((1ll << p.g.logM) - 1)) : tcol;
+        return oo + cc;
     }
     NB2_HD static void store_out(const Params& p, cplx<T>* dst, cplx<T> v) {
         if (p.keep_out) stc_keep(dst, v);
@@ -169,7 +179,7 @@ struct StridedPass {
         const int w = 1 << p.logw;
         const long long base = tile_base(p, bid);
         const long long tcol = (bid % p.tiles_per_outer) << p.logw;
-        const long long obase = p.out_rowoff ? (bid / p.tiles_per_outer) * p.out_ostride + tcol
+        const long long obase = p.out_rowoff ? out_origin(p, bid / p.tiles_per_outer, tcol)
                                              : (p.grp_on ? tile_base(p, bid, true) : base);
         if (PH == 0) {
             const int nb = MM << p.logw;

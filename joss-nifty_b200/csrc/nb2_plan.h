@@ -50,6 +50,8 @@ struct RowRemap {
     long long in_ostride = 0;
     const long long* out_rowoff = nullptr;
     long long out_ostride = 0;
+    const long long* out_ooff = nullptr;     // scatter form: per-outer-item and per-column-block origins
+    const long long* out_coloff = nullptr;
     // column subset of the natural side: ncols dense columns (0 = every column) in runs of `run`
     // contiguous columns (0 = one run) whose starts are `run_stride` apart, the first at col0
     long long col0 = 0, ncols = 0, run = 0, run_stride = 0;

@@ -60,6 +60,12 @@ struct StridedTma {
         int has_pro;
         PointOp<T> pro;
         Geom g;
+        // scatter of the output rows (slab exchange, see StridedPass::Params): row k of outer item o and
+        // column col goes to out_rowoff[k] + out_ooff[o] + out_coloff[col >> logM] + (col & (M - 1))
+        const long long* out_rowoff;
+        const long long* out_ooff;
+        const long long* out_coloff;
+        long long out_ostride;
     };
 
     // registers that live across the barriers of one tile
@@ -174,9 +180,19 @@ struct StridedTma {
             const int k1 = r + i * R3;
             cplx<T>(&y)[R3] = reinterpret_cast<cplx<T>(&)[R3]>(R.x[i * R3]);
             fft_reg<R3, true>(y);
-            cplx<T>* dst = p.out + base + c + (long long)k1 * p.inner;
-            NB2_UNROLL
-            for (int k3 = 0; k3 < R3; ++k3) stc_stream(dst + (long long)k3 * R1 * p.inner, y[brev<R3>(k3)]);
+            if (p.out_rowoff) {
+                const long long oo = p.out_ooff ? ld_ro(p.out_ooff + o) : o * p.out_ostride;
+                const long long cc =
+                    p.out_coloff ? ld_ro(p.out_coloff + (tc >> p.g.logM)) + (tc & ((1ll << p.g.logM) - 1)) : tc;
+                cplx<T>* dst = p.out + oo + cc + c;
+                const long long* ro = p.out_rowoff + k1;
+                NB2_UNROLL
+                for (int k3 = 0; k3 < R3; ++k3) stc_stream(dst + ld_ro(ro + k3 * R1), y[brev<R3>(k3)]);
+            } else {
+                cplx<T>* dst = p.out + base + c + (long long)k1 * p.inner;
+                NB2_UNROLL
+                for (int k3 = 0; k3 < R3; ++k3) stc_stream(dst + (long long)k3 * R1 * p.inner, y[brev<R3>(k3)]);
+            }
         }
     }
 };

@@ -64,6 +64,8 @@ class Library:
         "nb2_ipc_export": (c_int, [c_void_p, c_void_p]),
         "nb2_ipc_open": (c_int, [c_void_p, POINTER(c_void_p)]),
         "nb2_ipc_close": (c_int, [c_void_p]),
+        "nb2_strided_pass_scatter": (c_int, [c_void_p, c_int, c_void_p, c_void_p, POINTER(PointOp), c_void_p, c_void_p,
+                                     c_void_p, c_void_p]),
         "nb2_launch_count": (c_int64, []),
         "nb2_tma_launch_count": (c_int64, []),
         "nb2_c2c": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double, c_void_p]),

@@ -180,16 +180,24 @@ class SlabHartley:
         if use_p2p:
             esz = torch.empty((), dtype=dtype).element_size()
             self.peer = PeerExchange(comm, P * self.n0 * self.n1 * N2 * esz)
+            # The sending pass writes every row into its owner's buffer IN THE OWNER'S NATURAL LAYOUT
+            # (nb2_strided_pass_scatter), so the receiving pass is a plain pass (TMA kernel, no table):
+            #   X -> Y: row k1 of local plane l0 -> rank q = owner(k1), element (k0, l1, m) of its (N0, n1, M)
+            #   Y -> X: row k0 of local column block l1 -> rank q = owner(k0), element (l0, k1, m) of its (n0, N1, M)
             self.p2p_x, self.p2p_y = [], []       # per buffer: out-row tables of the pass before the exchange
             for b in range(PeerExchange.NBUF):
-                tx = np.empty(N1, dtype=np.int64)   # X -> Y: row k1 of plane l0 -> rank q, block `r`
-                ty = np.empty(N0, dtype=np.int64)   # Y -> X: row k0 -> rank q, block `r`
+                tx = np.empty(N1, dtype=np.int64)
+                ty = np.empty(N0, dtype=np.int64)
                 for q in range(P):
                     rel = self.peer.rel(b, q, 2 * esz)
-                    tx[self.s1.owned(q)] = rel + (r * self.n0 * self.n1 + np.arange(self.n1)) * M
-                    ty[self.s0.owned(q)] = rel + (r * self.n0 + np.arange(self.n0)) * self.n1 * M
+                    tx[self.s1.owned(q)] = rel + np.arange(self.n1) * M
+                    ty[self.s0.owned(q)] = rel + np.arange(self.n0) * N1 * M
                 self.p2p_x.append(torch.from_numpy(tx).to(dev))
                 self.p2p_y.append(torch.from_numpy(ty).to(dev))
+            # origin of local plane l0 (global k0) in a Y-layout buffer / of local column block l1 (global k1)
+            # in an X-layout buffer
+            self.p2p_x_outer = torch.from_numpy(self.s0.owned(r) * self.n1 * M).to(dev)
+            self.p2p_y_col = torch.from_numpy(self.s1.owned(r) * M).to(dev)
 
     def _exchange(self, before, after):
         """before(c) fills send[c]; after(c) consumes recv[c]; the all-to-alls overlap both."""
@@ -210,9 +218,9 @@ class SlabHartley:
             self.peer.turn = (b + 1) % PeerExchange.NBUF
             mine = self.peer.mine(b)
             # axis 1 (local) with the stores going to the owners of the k1 planes, over NVLink
-            self.plan_x.run_strided_remap(1, x, mine, pro, out_rowoff=self.p2p_x[b], out_ostride=self.ostride1)
+            self.plan_x.run_strided_scatter(1, x, mine, pro, out_rowoff=self.p2p_x[b], out_outer_off=self.p2p_x_outer)
             self.peer.arrive()
-            self.plan_y.run_strided_remap(0, mine, out, in_rowoff=self.rowoff0)
+            self.plan_y.run_pass(0, mine, out)
             return self.plan_y.run_pass(2, out, out, convention, epi=epi)
         self._exchange(
             lambda c: self.plan_x.run_strided_remap(1, x, self.send[c], pro, out_rowoff=self.rowoff1,
@@ -228,9 +236,9 @@ class SlabHartley:
             b = self.peer.turn
             self.peer.turn = (b + 1) % PeerExchange.NBUF
             mine = self.peer.mine(b)
-            self.plan_y.run_strided_remap(0, y, mine, pro, out_rowoff=self.p2p_y[b])
+            self.plan_y.run_strided_scatter(0, y, mine, pro, out_rowoff=self.p2p_y[b], out_col_off=self.p2p_y_col)
             self.peer.arrive()
-            self.plan_x.run_strided_remap(1, mine, out, in_rowoff=self.rowoff1, in_ostride=self.ostride1)
+            self.plan_x.run_pass(1, mine, out)
             return self.plan_x.run_pass(2, out, out, convention, epi=epi)
         self._exchange(
             lambda c: self.plan_y.run_strided_remap(0, y, self.send[c], pro, out_rowoff=self.rowoff0, col0=c * mc,

@@ -193,6 +193,18 @@ class Plan:
         self.lib.check(rc, "nb2_strided_pass_remap")
         return out
 
+    def run_strided_scatter(self, which, x, out, pro=None, out_rowoff=None, out_outer_off=None, out_col_off=None):
+        """Strided pass ``which`` with natural input whose output rows are scattered through offset
+        tables (``nb2_strided_pass_scatter``): the slab exchange written in the receiver's layout."""
+        cpro = pro.to_c(self.lib) if pro is not None else None
+        tab = lambda t, n: _ptr(self.lib, t, n) if t is not None else None   # noqa: E731
+        rc = self.lib.nb2_strided_pass_scatter(
+            self._h, int(which), _ptr(self.lib, x, "x"), _ptr(self.lib, out, "out"),
+            ctypes.byref(cpro) if cpro is not None else None, tab(out_rowoff, "out_rowoff"),
+            tab(out_outer_off, "out_outer_off"), tab(out_col_off, "out_col_off"), _stream(x))
+        self.lib.check(rc, "nb2_strided_pass_scatter")
+        return out
+
     def c2c(self, z, forward=True, scale=1.0, out=None):
         """Complex FFT of the complex tensor ``z`` (device) over the plan's axes."""
         if tuple(z.shape) != self.shape or z.dtype != _CPLX_OF[self.code]:

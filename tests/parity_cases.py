@@ -346,3 +346,33 @@ def check_cg_failure_modes():
     e, status = nb.ConjugateGradient(nb.GradientNormController(iteration_limit=5))(
         nb.QuadraticEnergy(j.clone(), neg, j))
     assert status == cgm.ERROR
+
+
+def check_strided_scatter(dt=np.float32):
+    """nb2_strided_pass_scatter == the plain strided pass followed by a permutation of rows, outer
+    items and column blocks (the receiver-natural layout of the peer-memory slab exchange)."""
+    tdt = torch.float32 if dt == np.float32 else torch.float64
+    rng = np.random.default_rng(11)
+    for shape, which in (((4, 256, 64), 1), ((256, 4, 64), 0), ((2, 512, 64), 1), ((16, 8, 32), 1), ((8, 16, 32), 0)):
+        n0, n1, n2 = shape
+        M = n2 // 2
+        x = dev(rng.normal(size=shape).astype(dt))
+        plan = get_plan(shape, None, tdt)
+        ref = torch.empty_like(x)
+        plan.run_pass(which, x, ref)
+        ref = ref.cpu().numpy().reshape(n0, n1, M, 2)
+        out = dev(np.full(shape, np.nan, dtype=dt))
+        ti = lambda a: dev(np.ascontiguousarray(a, dtype=np.int64))   # noqa: E731
+        if which == 1:
+            rp, op = rng.permutation(n1), rng.permutation(n0)
+            plan.run_strided_scatter(1, x, out, out_rowoff=ti(rp * M), out_outer_off=ti(op * n1 * M))
+            got = out.cpu().numpy().reshape(n0, n1, M, 2)
+            want = np.empty_like(ref)
+            want[np.ix_(op, rp)] = ref
+        else:
+            rp, cp = rng.permutation(n0), rng.permutation(n1)
+            plan.run_strided_scatter(0, x, out, out_rowoff=ti(rp * n1 * M), out_col_off=ti(cp * M))
+            got = out.cpu().numpy().reshape(n0, n1, M, 2)
+            want = np.empty_like(ref)
+            want[np.ix_(rp, cp)] = ref
+        assert np.array_equal(got, want), (shape, which, dt)

@@ -119,6 +119,15 @@ def test_tma_strided_pass(emu, monkeypatch):
     assert emu.nb2_tma_launch_count() == n0
 
 
+def test_strided_scatter(emu, monkeypatch):
+    n0 = emu.nb2_tma_launch_count()
+    pc.check_strided_scatter(np.float32)
+    pc.check_strided_scatter(np.float64)
+    assert emu.nb2_tma_launch_count() > n0          # the 256/512-row cases go through the TMA kernel
+    monkeypatch.setenv("NB2_TMA", "0")
+    pc.check_strided_scatter(np.float32)
+
+
 def test_hartley_leading_axes_inner_batch():
     # product-space sub-transforms: leading axes, contiguous inner batch (strided passes + mirror combine)
     import niftyb200 as nb

@@ -154,6 +154,13 @@ def test_tma_strided_pass(cuda, monkeypatch):
     assert cuda.nb2_tma_launch_count() == n0
 
 
+def test_strided_scatter(cuda, monkeypatch):
+    pc.check_strided_scatter(np.float32)
+    pc.check_strided_scatter(np.float64)
+    monkeypatch.setenv("NB2_TMA", "0")
+    pc.check_strided_scatter(np.float32)
+
+
 def test_hartley_leading_axes_inner_batch():
     import niftyb200 as nb
     shapes = [((16, 8, 4), (0, 1)), ((64, 128, 32), (0, 1)), ((4, 32, 8), (1,)), ((3, 8, 16, 4), (1, 2)),

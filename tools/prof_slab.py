@@ -49,13 +49,13 @@ if ht.peer is None:
                                               in_ostride=ht.ostride1, col0=c * mc, ncols=mc) for c in range(ht.chunks)])
 else:
     mine = ht.peer.mine(0)
-    res["passA_x(axis1->peers)"] = tm(lambda: ht.plan_x.run_strided_remap(1, x0, mine, None, out_rowoff=ht.p2p_x[0],
-                                                                          out_ostride=ht.ostride1))
+    res["passA_x(axis1->peers)"] = tm(lambda: ht.plan_x.run_strided_scatter(1, x0, mine, None, out_rowoff=ht.p2p_x[0],
+                                                                            out_outer_off=ht.p2p_x_outer))
     res["arrive"] = tm(lambda: ht.peer.arrive())
-    res["passB_y(mine->axis0)"] = tm(lambda: ht.plan_y.run_strided_remap(0, mine, y, in_rowoff=ht.rowoff0))
-    res["passA_y(axis0->peers)"] = tm(lambda: ht.plan_y.run_strided_remap(0, y, mine, None, out_rowoff=ht.p2p_y[0]))
-    res["passB_x(mine->axis1)"] = tm(lambda: ht.plan_x.run_strided_remap(1, mine, xo, in_rowoff=ht.rowoff1,
-                                                                         in_ostride=ht.ostride1))
+    res["passB_y(mine->axis0)"] = tm(lambda: ht.plan_y.run_pass(0, mine, y))
+    res["passA_y(axis0->peers)"] = tm(lambda: ht.plan_y.run_strided_scatter(0, y, mine, None, out_rowoff=ht.p2p_y[0],
+                                                                            out_col_off=ht.p2p_y_col))
+    res["passB_x(mine->axis1)"] = tm(lambda: ht.plan_x.run_pass(1, mine, xo))
 res["rows_y"] = tm(lambda: ht.plan_y.run_pass(2, y, y))
 res["rows_x"] = tm(lambda: ht.plan_x.run_pass(2, xo, xo))
 res["cg_update"] = tm(lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r))
