@@ -79,6 +79,13 @@ int run_strided_tma(const nb2_plan* pl, int axis, int logn, long long inner, lon
     if (logn < 8 || logn > 10 || inner % W || !aligned16(in) || !tma_available()) return 0;
     if (pro && pro->amp_mode == 1) return 0;   // table gather: the batched loads of StridedPass are faster
     if (rm && rm->out_coloff && (1ll << pl->g.logM) < W) return 0;   // a tile must not straddle column blocks
+    if (rm && rm->out_rowoff) {
+        // Scattered (peer-memory) stores: measured at 2 and 8 GPUs the many small CTAs of StridedPass hide the
+        // NVLink store latency better than one persistent CTA per SM (0.69 vs 0.75 ms per sending pass at
+        // 8 GPUs, profiles/r1_prof_slab_n8_p2p*.log), so the TMA kernel takes them only on request
+        const char* e = std::getenv("NB2_TMA_SCATTER");
+        if (!e || e[0] != '1') return 0;
+    }
     const long long ntiles = outer * (inner / W);
     if (ntiles < 2ll * rt_sm_count()) return 0;
     int rc = 0;

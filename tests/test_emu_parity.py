@@ -120,6 +120,8 @@ def test_tma_strided_pass(emu, monkeypatch):
 
 
 def test_strided_scatter(emu, monkeypatch):
+    pc.check_strided_scatter(np.float32)            # default: StridedPass with the scatter tables
+    monkeypatch.setenv("NB2_TMA_SCATTER", "1")
     n0 = emu.nb2_tma_launch_count()
     pc.check_strided_scatter(np.float32)
     pc.check_strided_scatter(np.float64)

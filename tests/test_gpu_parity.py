@@ -156,6 +156,8 @@ def test_tma_strided_pass(cuda, monkeypatch):
 
 def test_strided_scatter(cuda, monkeypatch):
     pc.check_strided_scatter(np.float32)
+    monkeypatch.setenv("NB2_TMA_SCATTER", "1")
+    pc.check_strided_scatter(np.float32)
     pc.check_strided_scatter(np.float64)
     monkeypatch.setenv("NB2_TMA", "0")
     pc.check_strided_scatter(np.float32)
