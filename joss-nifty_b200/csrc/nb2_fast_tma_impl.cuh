@@ -27,6 +27,11 @@ int run_strided_tma(const nb2_plan* pl, int axis, int logn, long long inner, lon
     }
     const long long ntiles = outer * (inner / W);
     if (ntiles < 2ll * rt_sm_count()) return 0;
+    // symmetric streamed amplitude field: staged through shared memory by TMA (NB2_TMA_FX=0: register loads)
+    bool fx = pro && pro->amp_mode == 2 && (pro->amp_flags & NB2_AMP_SYMMETRIC) && aligned16(pro->amp) &&
+              !(axis == 0 ? pl->g.shift0 : pl->g.shift1);
+    if (const char* e = std::getenv("NB2_TMA_FX"))
+        if (e[0] == '0') fx = false;
     int rc = 0;
 #define NB2_RUN_TMA(A, C)                                        \
     {                                                            \
@@ -45,6 +50,8 @@ int run_strided_tma(const nb2_plan* pl, int axis, int logn, long long inner, lon
         p.out_ooff = rm ? rm->out_ooff : nullptr;                \
         p.out_coloff = rm ? rm->out_coloff : nullptr;            \
         p.out_ostride = rm ? rm->out_ostride : 0;                \
+        p.fx = fx ? 1 : 0;                                       \
+        p.f_outer_mask = axis == 0 ? 0 : (1ll << pl->g.logN0) - 1; \
         rc = rt_launch_tma<K, T>(ntiles, outer, st, p);          \
     }
     switch (logn) {

@@ -45,10 +45,20 @@ struct StridedTma {
     static constexpr size_t P_BYTES = size_t(N) * ROW_BYTES;
     static constexpr int XROWS = N + R1;                              // one pad row per R3 rows
     static constexpr size_t X_BYTES = size_t(XROWS) * (ROW_BYTES / 2);
-    static constexpr size_t SMEM = P_BYTES + X_BYTES + 16;            // + the mbarrier
+    static constexpr size_t SMEM = P_BYTES + X_BYTES + 16;            // + the two mbarriers
     static constexpr int PB = R1 >= 8 ? 8 : R1;                       // prologue batch (rows)
     static constexpr int NBATCH = R1 / PB;
     static constexpr int MIN_BLOCKS = (SMEM <= 110 * 1024 && NTHREADS <= 256) ? 2 : 1;
+    // Mirror-symmetric amplitude field through shared memory ("fx"): only rows 0..N/2 of the field tile are
+    // needed (row j > N/2 equals row N - j); these N/2 + 1 rows of 128 bytes fit exactly into the
+    // transposition buffer X, which is idle between the last read of one tile and the first write of the
+    // next.  They are fetched by TMA (N/2 rows in boxes of FBOX_ROWS + a tail box of FTAIL_ROWS rows).
+    static constexpr int HALF = N / 2;
+    static constexpr int FBOX_ROWS = HALF < 256 ? HALF : 256;
+    static constexpr int NFBOX = HALF / FBOX_ROWS;
+    static constexpr int FTAIL_ROWS = 8;
+    static constexpr size_t F_BYTES = size_t(HALF + FTAIL_ROWS) * ROW_BYTES;
+    static_assert(F_BYTES <= X_BYTES, "the half field tile must fit into the transposition buffer");
 
     struct Params {
         const cplx<T>* in;
@@ -66,6 +76,8 @@ struct StridedTma {
         const long long* out_ooff;
         const long long* out_coloff;
         long long out_ostride;
+        int fx;                     // amplitude field (amp_mode 2, symmetric) staged in X by TMA / the emulator
+        long long f_outer_mask;     // outer index of the field tile = o & f_outer_mask (the field has no batch)
     };
 
     // registers that live across the barriers of one tile
@@ -83,7 +95,7 @@ struct StridedTma {
 
     // ---- stage 0a: amplitude factors of the first row batch (global loads issued before the wait)
     NB2_HD static void pro_begin(const Params& p, long long tile, int tid, Regs& R) {
-        if (!p.has_pro || p.pro.amp_mode != 2) return;
+        if (!p.has_pro || p.pro.amp_mode != 2 || p.fx) return;
         const int c = tid & (W - 1), r = tid >> LOGW;
         long long o, tc;
         const long long base = tile_base(p, tile, o, tc);
@@ -95,11 +107,22 @@ struct StridedTma {
     }
 
     // ---- stage 0b: tile rows from P into registers
-    NB2_HD static void load_tile(int tid, const char* Praw, Regs& R) {
+    NB2_HD static void load_tile(const Params& p, int tid, const char* Praw, const char* Fraw, Regs& R) {
         const cplx<T>* P = reinterpret_cast<const cplx<T>*>(Praw);
         const int c = tid & (W - 1), r = tid >> LOGW;
-        NB2_UNROLL
-        for (int n1 = 0; n1 < R1; ++n1) R.x[n1] = P[((r + n1 * MM) << LOGW) + c];
+        if (p.fx) {
+            const cplx<T>* F = reinterpret_cast<const cplx<T>*>(Fraw);   // rows 0..N/2 of the field tile, dense
+            NB2_UNROLL
+            for (int n1 = 0; n1 < R1; ++n1) {
+                const int row = r + n1 * MM, fr = row <= N - row ? row : N - row;
+                const cplx<T> v = P[(row << LOGW) + c], f = F[(fr << LOGW) + c];
+                R.x[n1].re = v.re * (f.re * p.pro.scale);
+                R.x[n1].im = v.im * (f.im * p.pro.scale);
+            }
+        } else {
+            NB2_UNROLL
+            for (int n1 = 0; n1 < R1; ++n1) R.x[n1] = P[((r + n1 * MM) << LOGW) + c];
+        }
     }
 
     // ---- stage 1: prologue, radix-R1 step, inter-step twiddles (in place, bit-reversed order)
@@ -109,7 +132,9 @@ struct StridedTma {
         if (p.has_pro) {
             long long o, tc;
             const long long base = tile_base(p, tile, o, tc);
-            if (p.pro.amp_mode == 2) {
+            if (p.pro.amp_mode == 2 && p.fx) {
+                // applied in load_tile
+            } else if (p.pro.amp_mode == 2) {
                 const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
                 const FieldRows<T> fr(reinterpret_cast<const cplx<T>*>(p.pro.amp) + ((base + c) & itemmask), p.inner, N,
                                       p.pro.amp_sym && !(p.axis == 0 ? p.g.shift0 : p.g.shift1));
@@ -228,11 +253,13 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, v
 
 template <class K>
 __global__ void __launch_bounds__(K::NTHREADS, K::MIN_BLOCKS)
-    nb2_kernel_tma(const __grid_constant__ CUtensorMap map, const typename K::Params p, long long ntiles) {
+    nb2_kernel_tma(const __grid_constant__ CUtensorMap map, const __grid_constant__ CUtensorMap mapf,
+                   const __grid_constant__ CUtensorMap mapft, const typename K::Params p, long long ntiles) {
     extern __shared__ __align__(128) char nb2_smem[];
     char* P = nb2_smem;
     char* X = nb2_smem + K::P_BYTES;
     void* bar = nb2_smem + K::P_BYTES + K::X_BYTES;
+    void* barf = nb2_smem + K::P_BYTES + K::X_BYTES + 8;
     const int tid = (int)threadIdx.x;
     const bool lower = (tid & (K::W - 1)) < K::HW;
     auto issue = [&](long long tile) {
@@ -243,21 +270,37 @@ __global__ void __launch_bounds__(K::NTHREADS, K::MIN_BLOCKS)
         for (int b = 0; b < K::NBOX; ++b)
             tma_load_3d(P + size_t(b) * K::BOX_ROWS * K::ROW_BYTES, &map, bar, c0, b * K::BOX_ROWS, (int)o);
     };
+    // rows 0 .. N/2 of the amplitude-field tile into X (fx)
+    auto issue_f = [&](long long tile) {
+        const long long o = tile / p.tiles_per_outer;
+        const int c0 = int((tile - o * p.tiles_per_outer) * K::BOX_ELEMS);
+        const int of = int(o & p.f_outer_mask);
+        mbar_expect_tx(barf, (unsigned)K::F_BYTES);
+#pragma unroll
+        for (int b = 0; b < K::NFBOX; ++b)
+            tma_load_3d(X + size_t(b) * K::FBOX_ROWS * K::ROW_BYTES, &mapf, barf, c0, b * K::FBOX_ROWS, of);
+        tma_load_3d(X + size_t(K::HALF) * K::ROW_BYTES, &mapft, barf, c0, K::HALF, of);
+    };
     if (tid == 0) {
         mbar_init(bar, 1);
+        mbar_init(barf, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     long long t = blockIdx.x;
-    if (tid == 0 && t < ntiles) issue(t);
+    if (tid == 0 && t < ntiles) {
+        issue(t);
+        if (p.fx) issue_f(t);
+    }
     unsigned parity = 0;
     for (; t < ntiles; t += gridDim.x) {
         typename K::Regs R;
         K::pro_begin(p, t, tid, R);
         mbar_wait(bar, parity);
+        if (p.fx) mbar_wait(barf, parity);
         parity ^= 1u;
-        K::load_tile(tid, P, R);
-        __syncthreads();   // P is free (and the previous tile's readers of X are done)
+        K::load_tile(p, tid, P, X, R);
+        __syncthreads();   // P and X are free (the previous tile's readers of X are done as well)
         if (tid == 0 && t + gridDim.x < ntiles) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             issue(t + gridDim.x);
@@ -270,6 +313,13 @@ __global__ void __launch_bounds__(K::NTHREADS, K::MIN_BLOCKS)
         if (!lower) K::xwrite(tid, X, R);
         __syncthreads();
         if (!lower) K::xread(tid, X, R);
+        if (p.fx) {
+            __syncthreads();   // X is free until the next tile's transposition: fetch its field rows now
+            if (tid == 0 && t + gridDim.x < ntiles) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                issue_f(t + gridDim.x);
+            }
+        }
         K::step2(p, t, tid, R);
     }
 }
@@ -289,9 +339,9 @@ inline nb2_encode_tiled_fn tma_encoder() {
     return fn;
 }
 
-// 3-D tensor map over the scalars of the complex array: (2 * inner, N, outer), box (128 bytes, BOX_ROWS, 1)
+// 3-D tensor map over the scalars of a complex array: (2 * inner, N, outer), box (128 bytes, box_rows, 1)
 template <class K, typename T>
-inline int tma_make_map(CUtensorMap* map, const void* in, long long inner, long long outer) {
+inline int tma_make_map(CUtensorMap* map, const void* in, long long inner, long long outer, int box_rows) {
     nb2_encode_tiled_fn enc = tma_encoder();
     if (!enc) {
         last_error() = "cuTensorMapEncodeTiled is not available";
@@ -299,7 +349,7 @@ inline int tma_make_map(CUtensorMap* map, const void* in, long long inner, long 
     }
     const cuuint64_t dims[3] = {cuuint64_t(2 * inner), cuuint64_t(K::N), cuuint64_t(outer)};
     const cuuint64_t strides[2] = {cuuint64_t(2 * inner) * sizeof(T), cuuint64_t(2 * inner) * sizeof(T) * K::N};
-    const cuuint32_t box[3] = {cuuint32_t(K::BOX_ELEMS), cuuint32_t(K::BOX_ROWS), 1};
+    const cuuint32_t box[3] = {cuuint32_t(K::BOX_ELEMS), cuuint32_t(box_rows), 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     const CUresult r = enc(map, sizeof(T) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3,
                            const_cast<void*>(in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -314,8 +364,14 @@ inline int tma_make_map(CUtensorMap* map, const void* in, long long inner, long 
 template <class K, typename T>
 inline int rt_launch_tma(long long ntiles, long long outer, rt_stream stream, const typename K::Params& p) {
     if (ntiles <= 0) return 0;
-    CUtensorMap map;
-    if (tma_make_map<K, T>(&map, p.in, p.inner, outer)) return -2;
+    CUtensorMap map, mapf, mapft;
+    if (tma_make_map<K, T>(&map, p.in, p.inner, outer, K::BOX_ROWS)) return -2;
+    if (p.fx) {
+        if (tma_make_map<K, T>(&mapf, p.pro.amp, p.inner, p.f_outer_mask + 1, K::FBOX_ROWS)) return -2;
+        if (tma_make_map<K, T>(&mapft, p.pro.amp, p.inner, p.f_outer_mask + 1, K::FTAIL_ROWS)) return -2;
+    } else {
+        mapf = mapft = map;
+    }
     static thread_local bool configured = false;
     if (!configured) {
         NB2_CUDA_OK(cudaFuncSetAttribute(nb2_kernel_tma<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K::SMEM));
@@ -328,7 +384,7 @@ inline int rt_launch_tma(long long ntiles, long long outer, rt_stream stream, co
     }
     long long grid = (long long)per_sm * rt_sm_count();
     if (grid > ntiles) grid = ntiles;
-    nb2_kernel_tma<K><<<(unsigned)grid, K::NTHREADS, K::SMEM, stream>>>(map, p, ntiles);
+    nb2_kernel_tma<K><<<(unsigned)grid, K::NTHREADS, K::SMEM, stream>>>(map, mapf, mapft, p, ntiles);
     NB2_CUDA_OK(cudaGetLastError());
     ++launch_counter();
     ++tma_launch_counter();
@@ -351,11 +407,18 @@ inline int rt_launch_tma(long long ntiles, long long, rt_stream, const typename 
         const long long base = K::tile_base(p, tile, o, tc);
         for (int row = 0; row < K::N; ++row)
             std::memcpy(Pbuf.data() + size_t(row) * K::ROW_BYTES, p.in + base + (long long)row * p.inner, K::ROW_BYTES);
+        if (p.fx) {   // what the field TMA does: rows 0 .. N/2 of the field tile, dense, into X
+            const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
+            const cplx<T>* f = reinterpret_cast<const cplx<T>*>(p.pro.amp) + (base & itemmask);
+            for (int row = 0; row <= K::HALF; ++row)
+                std::memcpy(Xbuf.data() + size_t(row) * K::ROW_BYTES, f + (long long)row * p.inner, K::ROW_BYTES);
+        }
         auto lower = [](int tid) { return (tid & (K::W - 1)) < K::HW; };
         for (int tid = 0; tid < K::NTHREADS; ++tid) {
             K::pro_begin(p, tile, tid, regs[tid]);
-            K::load_tile(tid, Pbuf.data(), regs[tid]);
+            K::load_tile(p, tid, Pbuf.data(), Xbuf.data(), regs[tid]);
         }
+        std::memset(Xbuf.data(), 0xAB, K::X_BYTES);
         for (int tid = 0; tid < K::NTHREADS; ++tid) {
             K::step1(p, tile, tid, regs[tid]);
             if (lower(tid)) K::xwrite(tid, Xbuf.data(), regs[tid]);
