@@ -23,6 +23,7 @@ for p in (ROOT, os.path.join(ROOT, "joss-nifty_b200")):
 
 import numpy as np  # noqa: E402
 
+FUSED = "StridedPass(first axis)+amplitude field+direction update (fused axpby)"
 METRIC = "metric_cg_iters_per_s"
 UNIT = "CG iterations/s"
 # demos/1_tomography.py:21-34 hyper-parameters
@@ -316,6 +317,10 @@ def run_b200(args):
                 pros = PointOp(tabs.amp_mode, tabs.amp, tabs.azm, amp_sym=tabs.sym)
                 passes["StridedPass(first axis)+amplitude field"] = tk(lambda: plan.run_pass(3 - len(shape), a, b, pro=pros))
                 passes["StridedPass(first axis)+amplitude gather"] = tk(lambda: plan.run_pass(3 - len(shape), a, b, pro=pro))
+                if getattr(M, "fused_direction_update", False):
+                    # the first pass of the metric apply as the CG loop runs it: d <- r + beta d in place, x field
+                    prod = PointOp(tabs.amp_mode, tabs.amp, tabs.azm, amp_sym=tabs.sym, pre_add=j, pre_scale=0.5, pre_out=a)
+                    passes[FUSED] = tk(lambda: plan.run_pass(3 - len(shape), a, b, pro=prod))
             passes["RowPass+weight (metric fwd epilogue)"] = tk(lambda: plan.run_pass(
                 2, a, b, epi=PointOp(scale=cf.dvol, mul=M.w)))
             passes["RowPass+amplitude field+add+dot (metric adj epilogue)"] = tk(lambda: plan.run_pass(
@@ -326,10 +331,12 @@ def run_b200(args):
         # the kernels that run inside one CG iteration (the gather variant is reported, not used there)
         # ALGORITHMIC bytes per launch: every full-size operand once
         # (the curvature dot re-reads the array that is added, so add+dot count once)
-        kbytes = {k: (2 + ("field" in k) + ("weight" in k) + ("add" in k)) * N * s for k in passes}
+        kbytes = {k: (2 + ("field" in k) + ("weight" in k) + ("add" in k) + 2 * ("direction update" in k)) * N * s
+                  for k in passes}
         # The launches of ONE CG iteration grouped by kernel function; the dominant kernel is the one with
         # the largest share of the step.  achieved = algorithmic bytes per launch / average launch duration.
-        f0 = "StridedPass(first axis)+amplitude field"
+        fused = bool(passes.get(FUSED))
+        f0 = FUSED if fused else "StridedPass(first axis)+amplitude field"
         groups = {}
         if len(shape) == 3 and all(passes.get(k) for k in (f0, names[0], names[1])):
             groups["strided pass (StridedTma / StridedPass): first axis + amplitude field, axis 1, axis 0, axis 1"] = \
@@ -341,14 +348,15 @@ def run_b200(args):
             groups["row pass (RowPass): + weight, + amplitude field + add + curvature dot"] = rk
         gsum = {g: (sum(passes[k] for k in ks), sum(kbytes[k] for k in ks), len(ks)) for g, ks in groups.items()}
         gsum["CgUpdate (+3 dots)"] = (t_upd, 7 * N * s, 1)
-        gsum["Axpby"] = (t_axp, 3 * N * s, 1)
+        if not fused:       # otherwise the direction update rides on the first strided pass
+            gsum["Axpby"] = (t_axp, 3 * N * s, 1)
         dom = max(gsum, key=lambda g: gsum[g][0])
         t_dom, b_dom, n_dom = gsum[dom]
         ach = b_dom / (t_dom * 1e-3) / 1e9
         # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, one `ncu --set full` capture,
         # profiles/r1_ncu_full_v3_passes_f32_1024.csv), known for the headline grid only
         traffic = None
-        if shape == (1024, 1024, 1024) and args.dtype == "f32" and dom.startswith("strided"):
+        if shape == (1024, 1024, 1024) and args.dtype == "f32" and dom.startswith("strided") and not fused:
             traffic = (10.701343e9 + 8.532932e9 + 8.541014e9 + 8.532932e9) / 4
         out["roofline"] = {"bound": "hbm", "kernel": dom, "launches_per_step": n_dom, "achieved": ach, "peak": peak,
                            "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,

@@ -73,6 +73,16 @@ typedef struct nb2_pointop {
      * zero it first).  NULL = off. */
     const void* bin_x;
     double* bin_out;
+    /* Fused direction update of the conjugate gradient (PROLOGUE of a fast-path transform whose first
+     * pass is a strided pass, i.e. >= 2 transformed axes; NULL = off): before anything else
+     *   in'[i] = pre_add[i] + pre_scale * in[i]        (d = r + beta d, conjugate_gradient.py:124,
+     *                                                    re/conjugate_gradient.py:205)
+     * and, if pre_out != NULL, in'[i] is also stored to pre_out[i] (pre_out may be `in` itself: the
+     * update then happens in place while the transform reads it).  pre_add / pre_out are full-size
+     * arrays like `in`.  Saves the separate axpby sweep (one read of d). */
+    const void* pre_add;
+    double pre_scale;
+    void* pre_out;
 } nb2_pointop;
 
 int nb2_version(void);

@@ -566,12 +566,33 @@ int64_t nb2_plan_ksq_size(const nb2_plan* pl) {
     return 1 + h0 * h0 + h1 * h1 + h2 * h2;
 }
 
+// pre_add / pre_out (fused direction update) belong to the prologue of a transform that starts with a
+// strided pass; `strided_first`: such a pass exists in what is about to run
+static int check_pre_update(const nb2_plan* pl, const nb2_pointop* pro, const nb2_pointop* epi, const void* out,
+                            bool strided_first) {
+    if (epi && (epi->pre_add || epi->pre_out)) {
+        last_error() = "nb2_pointop.pre_add / pre_out are prologue fields";
+        return NB2_ERR_ARG;
+    }
+    if (!pro || (!pro->pre_add && !pro->pre_out)) return NB2_OK;
+    if (!pro->pre_add || pro->pre_out == out) {
+        last_error() = "nb2_pointop.pre_out needs pre_add and must not alias the output of the transform";
+        return NB2_ERR_ARG;
+    }
+    if (!strided_first || !(pl->fast || pl->inner)) {
+        last_error() = "nb2_pointop.pre_add: the transform must start with a strided pass of the fast path";
+        return NB2_ERR_UNSUPPORTED;
+    }
+    return NB2_OK;
+}
+
 int nb2_hartley(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
                 void* stream) {
     if (!pl || !in || !out || (conv != 0 && conv != 1)) {
         last_error() = "nb2_hartley: invalid argument";
         return NB2_ERR_ARG;
     }
+    if (int rc = check_pre_update(pl, pro, epi, out, pl->g.logN0 > 0 || pl->g.logN1 > 0)) return rc;
     rt_stream st = (rt_stream)stream;
     if ((pro && pro->bin_x) || (epi && epi->bin_x && (!pl->fast || !epi->bin_out))) {
         last_error() = "nb2_hartley: the binned reduction (bin_x/bin_out) is an epilogue of fast-path plans";
@@ -617,6 +638,7 @@ int nb2_hartley_pass(nb2_plan* pl, int which, const void* in, void* out, int con
         last_error() = "nb2_hartley_pass: pass not part of this plan";
         return NB2_ERR_UNSUPPORTED;
     }
+    if (int rc = check_pre_update(pl, pro, epi, out, which < 2)) return rc;
     rt_stream st = (rt_stream)stream;
     if (which < 2)
         return pl->dtype == NB2_F32 ? run_strided<float>(pl, which, in, out, pro, st)
@@ -640,6 +662,10 @@ int nb2_strided_pass_remap(nb2_plan* pl, int which, const void* in, void* out, c
     if (col0 < 0 || ncols < 0 || run < 0 || run_stride < 0) {
         last_error() = "nb2_strided_pass_remap: negative column range";
         return NB2_ERR_ARG;
+    }
+    if (pro && (pro->pre_add || pro->pre_out)) {
+        last_error() = "nb2_strided_pass_remap: the fused direction update needs natural input rows";
+        return NB2_ERR_UNSUPPORTED;
     }
     if ((in_rowoff || out_rowoff) && in == out) {
         last_error() = "nb2_strided_pass_remap: a remapped pass cannot run in place";
@@ -670,6 +696,7 @@ int nb2_strided_pass_scatter(nb2_plan* pl, int which, const void* in, void* out,
         last_error() = "nb2_strided_pass_scatter: pass not part of this plan";
         return NB2_ERR_UNSUPPORTED;
     }
+    if (int rc = check_pre_update(pl, pro, nullptr, out, true)) return rc;
     RowRemap rm;
     rm.out_rowoff = (const long long*)out_rowoff;
     rm.out_ooff = (const long long*)out_outer_off;

@@ -144,7 +144,7 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
             const bool field = pro && pro->amp_mode == 2;                                     \
             const size_t stage = smem * (field ? 2 : 1);                                      \
             const int stages = pipe_stages(stage);                                            \
-            if (!K::SINGLE && stages && !p.grp_on && ntiles >= 4ll * rt_sm_count() &&         \
+            if (!K::SINGLE && stages && !p.grp_on && !(pro && pro->pre_add) && ntiles >= 4ll * rt_sm_count() && \
                 (sizeof(cplx<T>) << logw) >= 16 && aligned16(in) && (!field || aligned16(pro->amp))) { \
                 p.staged = 1;                                                                 \
                 p.pro_staged = field ? 1 : 0;                                                 \

@@ -32,6 +32,8 @@ int run_strided_tma(const nb2_plan* pl, int axis, int logn, long long inner, lon
               !(axis == 0 ? pl->g.shift0 : pl->g.shift1);
     if (const char* e = std::getenv("NB2_TMA_FX"))
         if (e[0] == '0') fx = false;
+    // fused direction update: the field (if any) must come through X, the registers stream r
+    if (pro && pro->pre_add && pro->amp_mode == 2 && !fx) return 0;
     int rc = 0;
 #define NB2_RUN_TMA(A, C)                                        \
     {                                                            \

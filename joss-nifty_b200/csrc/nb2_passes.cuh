@@ -199,6 +199,19 @@ struct StridedPass {
                     NB2_UNROLL
                     for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + (long long)n1 * MM * p.inner);
                 }
+                if (p.has_pro && p.pro.pre_add) {
+                    // fused direction update d = r + beta d (natural rows only): same element, same thread
+                    const long long e0 = base + c + (long long)r * p.inner;
+                    const cplx<T>* rs = reinterpret_cast<const cplx<T>*>(p.pro.pre_add) + e0;
+                    cplx<T>* dd = p.pro.pre_out ? reinterpret_cast<cplx<T>*>(p.pro.pre_out) + e0 : nullptr;
+                    NB2_UNROLL
+                    for (int n1 = 0; n1 < R1; ++n1) {
+                        const cplx<T> rr = ldc_stream(rs + (long long)n1 * MM * p.inner);
+                        x[n1].re = rr.re + p.pro.pre_scale * x[n1].re;
+                        x[n1].im = rr.im + p.pro.pre_scale * x[n1].im;
+                        if (dd) stc_stream(dd + (long long)n1 * MM * p.inner, x[n1]);
+                    }
+                }
                 if (p.has_pro) {
                     // amplitude factors are fetched in batches of PB rows, two batches in flight,
                     // so that their latency overlaps instead of serialising per row

@@ -34,6 +34,10 @@ struct PointOp {
     // in the ksq parametrisation of the bins; fp64 atomics
     const T* bin_x;
     double* bin_out;
+    // prologue of a strided pass only: in' = pre_add + pre_scale * in, stored to pre_out if set
+    const T* pre_add;
+    T pre_scale;
+    T* pre_out;
 };
 
 NB2_HD void atomic_add_f64(double* p, double v) {

@@ -95,6 +95,16 @@ struct StridedTma {
 
     // ---- stage 0a: amplitude factors of the first row batch (global loads issued before the wait)
     NB2_HD static void pro_begin(const Params& p, long long tile, int tid, Regs& R) {
+        if (p.has_pro && p.pro.pre_add) {
+            // fused direction update: first batch of r (the field, if any, comes through X: fx)
+            const int c = tid & (W - 1), r = tid >> LOGW;
+            long long o, tc;
+            const long long base = tile_base(p, tile, o, tc);
+            const cplx<T>* rs = reinterpret_cast<const cplx<T>*>(p.pro.pre_add) + base + c + (long long)r * p.inner;
+            NB2_UNROLL
+            for (int i = 0; i < PB; ++i) R.f0[i] = ldc_stream(rs + (long long)i * MM * p.inner);
+            return;
+        }
         if (!p.has_pro || p.pro.amp_mode != 2 || p.fx) return;
         const int c = tid & (W - 1), r = tid >> LOGW;
         long long o, tc;
@@ -107,9 +117,44 @@ struct StridedTma {
     }
 
     // ---- stage 0b: tile rows from P into registers
-    NB2_HD static void load_tile(const Params& p, int tid, const char* Praw, const char* Fraw, Regs& R) {
+    NB2_HD static void load_tile(const Params& p, long long tile, int tid, const char* Praw, const char* Fraw, Regs& R) {
         const cplx<T>* P = reinterpret_cast<const cplx<T>*>(Praw);
         const int c = tid & (W - 1), r = tid >> LOGW;
+        if (p.has_pro && p.pro.pre_add) {
+            // d' = r + beta d for the tile (d from P, r streamed in batches of PB rows, two in flight), stored
+            // back to pre_out; then the field factor from X (fx) -- a plain scale is left to step1
+            long long o, tc;
+            const long long base = tile_base(p, tile, o, tc);
+            const long long e0 = base + c + (long long)r * p.inner, rstride = (long long)MM * p.inner;
+            const cplx<T>* rs = reinterpret_cast<const cplx<T>*>(p.pro.pre_add) + e0;
+            cplx<T>* dd = p.pro.pre_out ? reinterpret_cast<cplx<T>*>(p.pro.pre_out) + e0 : nullptr;
+            const cplx<T>* F = reinterpret_cast<const cplx<T>*>(Fraw);
+            cplx<T> rr[2][PB];
+            NB2_UNROLL
+            for (int i = 0; i < PB; ++i) rr[0][i] = R.f0[i];
+            NB2_UNROLL
+            for (int g = 0; g < NBATCH; ++g) {
+                if (g + 1 < NBATCH) {
+                    NB2_UNROLL
+                    for (int i = 0; i < PB; ++i) rr[(g + 1) & 1][i] = ldc_stream(rs + ((g + 1) * PB + i) * rstride);
+                }
+                NB2_UNROLL
+                for (int i = 0; i < PB; ++i) {
+                    const int n1 = g * PB + i, row = r + n1 * MM;
+                    cplx<T> v = P[(row << LOGW) + c];
+                    v.re = rr[g & 1][i].re + p.pro.pre_scale * v.re;
+                    v.im = rr[g & 1][i].im + p.pro.pre_scale * v.im;
+                    if (dd) stc_stream(dd + n1 * rstride, v);
+                    if (p.fx) {
+                        const cplx<T> f = F[((row <= N - row ? row : N - row) << LOGW) + c];
+                        v.re *= f.re * p.pro.scale;
+                        v.im *= f.im * p.pro.scale;
+                    }
+                    R.x[n1] = v;
+                }
+            }
+            return;
+        }
         if (p.fx) {
             const cplx<T>* F = reinterpret_cast<const cplx<T>*>(Fraw);   // rows 0..N/2 of the field tile, dense
             NB2_UNROLL
@@ -299,7 +344,7 @@ __global__ void __launch_bounds__(K::NTHREADS, K::MIN_BLOCKS)
         mbar_wait(bar, parity);
         if (p.fx) mbar_wait(barf, parity);
         parity ^= 1u;
-        K::load_tile(p, tid, P, X, R);
+        K::load_tile(p, t, tid, P, X, R);
         __syncthreads();   // P and X are free (the previous tile's readers of X are done as well)
         if (tid == 0 && t + gridDim.x < ntiles) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -416,7 +461,7 @@ inline int rt_launch_tma(long long ntiles, long long, rt_stream, const typename 
         auto lower = [](int tid) { return (tid & (K::W - 1)) < K::HW; };
         for (int tid = 0; tid < K::NTHREADS; ++tid) {
             K::pro_begin(p, tile, tid, regs[tid]);
-            K::load_tile(p, tid, Pbuf.data(), Xbuf.data(), regs[tid]);
+            K::load_tile(p, tile, tid, Pbuf.data(), Xbuf.data(), regs[tid]);
         }
         std::memset(Xbuf.data(), 0xAB, K::X_BYTES);
         for (int tid = 0; tid < K::NTHREADS; ++tid) {

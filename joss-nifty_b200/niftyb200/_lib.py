@@ -33,6 +33,9 @@ class PointOp(ctypes.Structure):
         ("dot_out", c_void_p),
         ("bin_x", c_void_p),
         ("bin_out", c_void_p),
+        ("pre_add", c_void_p),
+        ("pre_scale", c_double),
+        ("pre_out", c_void_p),
     ]
 
 

@@ -65,9 +65,16 @@ class _Vec:
         return y
 
 
-def _apply_with_curv(A, d, q):
+def _apply_with_curv(A, d, q, pending=None, vec=None):
+    """``q = A d`` and ``d.q``.  ``pending = (s, beta)``: the deferred direction update ``d <- s + beta d``
+    of the previous iteration, done inside the first pass of ``A`` when it can carry it
+    (``A.fused_direction_update``), else by the axpby kernel right here."""
+    if pending is not None and not getattr(A, "fused_direction_update", False):
+        vec.axpby(1.0, pending[0], pending[1], d)
+        pending = None
     if hasattr(A, "apply_with_curvature"):
-        q, curv = A.apply_with_curvature(d, out=q)
+        q, curv = A.apply_with_curvature(d, out=q, pre=pending) if pending is not None else \
+            A.apply_with_curvature(d, out=q)
         return q, float(curv.cpu())
     res = A(d)
     if res.data_ptr() != q.data_ptr():
@@ -223,8 +230,10 @@ class ConjugateGradient:
             return QuadraticEnergy(x, A, energy._b, _grad=r, _value=value, _gradnorm=float(np.sqrt(gamma_rr)))
 
         ii = 0
+        pending = None    # deferred direction update (s, beta): done with the next A d
         while True:
-            q, curv = _apply_with_curv(A, d, q)                       # :84-85
+            q, curv = _apply_with_curv(A, d, q, pending, vec)         # :84-85 (+ the deferred :124)
+            pending = None
             if np.isnan(curv) or curv == 0.0:                          # :86-91
                 return energy, ERROR
             alpha = previous_gamma / curv
@@ -253,7 +262,7 @@ class ConjugateGradient:
             status = controller.check(energy)                          # :120
             if status != CONTINUE:
                 return energy, status
-            vec.axpby(1.0, s, max(0.0, gamma / previous_gamma), d)     # :124
+            pending = (s, max(0.0, gamma / previous_gamma))            # :124, applied with the next A d
             previous_gamma = gamma
 
 
@@ -320,10 +329,12 @@ def _cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5
                                                                tol, atol, getattr(mat, "comm", None))
     vec, pos, r, d, q, energy, nfev, previous_gamma = _cg_setup(mat, j, x0)
     info, i = -1, 0
+    pending = None    # deferred direction update (r, beta): done with the next mat(d)
     if previous_gamma == 0:
         return CGResults(pos, 0, nfev, 0, True)
     for i in range(1, maxiter + 1):
-        q, curv = _apply_with_curv(mat, d, q)                          # :147-150
+        q, curv = _apply_with_curv(mat, d, q, pending, vec)            # :147-150 (+ the deferred :205)
+        pending = None
         nfev += 1
         if curv == 0.0:                                                # :151-156
             if _raise_nonposdef:
@@ -370,7 +381,7 @@ def _cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5
             info = 0
             break
         energy = new_energy
-        vec.axpby(1.0, r, max(0.0, gamma / previous_gamma), d)         # :205
+        pending = (r, max(0.0, gamma / previous_gamma))                # :205, applied with the next mat(d)
         previous_gamma = gamma
     info = i if info == -1 else info
     return CGResults(pos, i, nfev, info, info == 0)
@@ -393,10 +404,12 @@ def _static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, t
                                                                tol, atol, getattr(mat, "comm", None))
     vec, pos, r, d, q, energy, nfev, gamma = _cg_setup(mat, j, x0)
     info, i = (0 if gamma == 0.0 else -2), 0
+    pending = None    # deferred direction update (r, beta): done with the next mat(d)
     while info < -1:
         previous_gamma, previous_energy = gamma, energy
         i += 1
-        q, curv = _apply_with_curv(mat, d, q)                          # :270-271
+        q, curv = _apply_with_curv(mat, d, q, pending, vec)            # :270-271 (+ the deferred :315)
+        pending = None
         if curv == 0.0:
             info = -1
         with np.errstate(divide="ignore", invalid="ignore"):
@@ -426,7 +439,7 @@ def _static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, t
             info = i
         with np.errstate(divide="ignore", invalid="ignore"):
             beta = max(0.0, float(np.float64(gamma) / np.float64(previous_gamma)))
-        vec.axpby(1.0, r, beta, d)                                     # :315
+        pending = (r, beta)                                            # :315, applied with the next mat(d)
     nfev += i + i // N_RESET
     return CGResults(pos, i, nfev, info, info == 0)
 
@@ -441,12 +454,14 @@ class CGLoop:
         self.mat, self.j = mat, j
         (self.vec, self.pos, self.r, self.d, self.q, self.energy, self.nfev, self.gamma) = _cg_setup(mat, j, x0)
         self.i = 0
+        self.pending = None    # deferred direction update (r, beta), applied with the next metric apply
 
     def run(self, n):
         mat, vec, j = self.mat, self.vec, self.j
         for _ in range(n):
             self.i += 1
-            self.q, curv = _apply_with_curv(mat, self.d, self.q)
+            self.q, curv = _apply_with_curv(mat, self.d, self.q, self.pending, vec)
+            self.pending = None
             self.nfev += 1
             alpha = self.gamma / curv
             if self.i % N_RESET == 0:
@@ -457,6 +472,6 @@ class CGLoop:
             else:
                 gamma, xr, xb = vec.update(0, alpha, self.d, self.q, j, self.pos, self.r)
             self.energy = 0.5 * (xr - xb)
-            vec.axpby(1.0, self.r, max(0.0, gamma / self.gamma), self.d)
+            self.pending = (self.r, max(0.0, gamma / self.gamma))
             self.gamma = gamma
         return self

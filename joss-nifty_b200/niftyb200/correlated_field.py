@@ -267,10 +267,26 @@ class CorrelatedField:
         return st
 
     # ---- hot tail ---------------------------------------------------------------------
-    def apply_xi(self, xi, tab, out=None, convention=None, offset=None, mul=None):
-        """``offset + prod_g (1/V_g) hartley_g(azm * amp[pindex] * xi)`` on device tensors."""
+    @property
+    def fuses_direction_update(self):
+        """True when the first pass of :meth:`apply_xi` is a strided pass of the fast path, which can
+        carry the CG direction update ``xi <- pre[0] + pre[1] * xi`` (``nb2_pointop.pre_add``)."""
+        pl = self.plans[0]
+        nax = sum(1 for a in pl.axes if self.shape[a] > 1)
+        return (pl.kind == 1 and nax >= 2) or (pl.kind == 2 and nax >= 1)
+
+    def apply_xi(self, xi, tab, out=None, convention=None, offset=None, mul=None, pre=None):
+        """``offset + prod_g (1/V_g) hartley_g(azm * amp[pindex] * xi)`` on device tensors.
+
+        ``pre = (r, beta)``: first ``xi <- r + beta * xi`` IN PLACE (the conjugate-gradient direction
+        update, conjugate_gradient.py:124), fused into the first pass; needs
+        :attr:`fuses_direction_update` and ``out is not xi``."""
         off = self.offset_mean if offset is None else offset
         pro = PointOp(tab.amp_mode, tab.amp, tab.azm, amp_sym=getattr(tab, "sym", False))
+        if pre is not None:
+            if not self.fuses_direction_update:
+                raise ValueError("this field's transform cannot carry the fused direction update")
+            pro.pre_add, pro.pre_scale, pro.pre_out = pre[0], float(pre[1]), xi
         if self.single:
             return self.plans[0].hartley(xi, out=out, convention=convention, pro=pro,
                                          epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))

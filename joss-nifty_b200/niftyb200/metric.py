@@ -16,6 +16,8 @@ of the forward transform, the amplitude multiply, the ``+ t`` and the CG curvatu
 on the last store of the adjoint transform.
 """
 
+import os
+
 import torch
 
 from .transforms import PointOp
@@ -49,9 +51,15 @@ class CFMetric:
         self._curv = torch.zeros((), dtype=torch.float64, device=cf.device)
         self.shape, self.dtype, self.device = self.latent_shape, cf.dtype, cf.device
         self.napply = 0
+        # the CG loops hand their pending direction update d <- r + beta d to apply_with_curvature(pre=...)
+        # (NIFTYB200_FUSED_AXPBY=0: keep the separate axpby kernel -- A/B measurements)
+        self.fused_direction_update = (bool(getattr(cf, "fuses_direction_update", False)) and self.comm is None
+                                       and os.environ.get("NIFTYB200_FUSED_AXPBY", "1") != "0")
 
-    def forward_weighted(self, t, out):
-        """``w * H A t`` (offset excluded: this is the Jacobian)."""
+    def forward_weighted(self, t, out, pre=None):
+        """``w * H A t`` (offset excluded: this is the Jacobian); ``pre``: see ``CorrelatedField.apply_xi``."""
+        if pre is not None:
+            return self.cf.apply_xi(t, self.tab, out=out, convention=self.convention, offset=0.0, mul=self.w, pre=pre)
         return self.cf.apply_xi(t, self.tab, out=out, convention=self.convention, offset=0.0, mul=self.w)
 
     def __call__(self, t, out=None):
@@ -59,11 +67,12 @@ class CFMetric:
         u = self.forward_weighted(t, self._u)
         return self.cf.adjoint_xi(u, self.tab, out=out, convention=self.convention, add=t)
 
-    def apply_with_curvature(self, t, out=None):
+    def apply_with_curvature(self, t, out=None, pre=None):
         """Returns ``(M t, t.(M t))``; the dot product is fused into the last store.  The
-        curvature is a 0-d fp64 device tensor."""
+        curvature is a 0-d fp64 device tensor.  ``pre = (r, beta)``: ``t <- r + beta t`` in place first
+        (fused into the first pass; only when :attr:`fused_direction_update`)."""
         self.napply += 1
-        u = self.forward_weighted(t, self._u)
+        u = self.forward_weighted(t, self._u, pre)
         q = self.cf.adjoint_xi(u, self.tab, out=out, convention=self.convention, add=t, dot=t,
                                dot_out=self._curv)
         return q, self._curv

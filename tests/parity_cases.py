@@ -376,3 +376,25 @@ def check_strided_scatter(dt=np.float32):
             want = np.empty_like(ref)
             want[np.ix_(rp, cp)] = ref
         assert np.array_equal(got, want), (shape, which, dt)
+
+
+def check_fused_direction_update(shape, dist, dt=np.float64):
+    """apply_with_curvature(d, pre=(r, beta)) == axpby(d = r + beta d) followed by the plain apply:
+    the updated d (stored in place), M d and the curvature (nb2_pointop.pre_add)."""
+    M, Mo, j, x0 = metric_pair(shape, dist, dt)
+    assert M.fused_direction_update
+    rng = np.random.default_rng(5)
+    d0, r = rng.normal(size=shape).astype(dt), rng.normal(size=shape).astype(dt)
+    beta = 0.37
+    d1, d2 = dev(d0.copy()), dev(d0.copy())      # dev() is zero-copy on the CPU emulator
+    q1, c1 = M.apply_with_curvature(d1, pre=(dev(r), beta))
+    q1, c1 = q1.clone(), float(c1.cpu())
+    cgm = sys.modules["niftyb200.cg"]
+    cgm._Vec(d2).axpby(1.0, dev(r), beta, d2)
+    q2, c2 = M.apply_with_curvature(d2)
+    tol = 1e-13 if dt == np.float64 else 2e-6
+    want = r.astype(np.float64) + beta * d0.astype(np.float64)
+    assert rel(host(d1), want) <= tol and rel(host(d1), host(d2)) <= tol
+    assert rel(host(q1), host(q2)) <= 10 * tol and abs(c1 - float(c2.cpu())) <= 10 * tol * abs(c1)
+    # and against the oracle
+    assert rel(host(q1), Mo(want)) <= TOL[dt]

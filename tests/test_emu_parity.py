@@ -130,6 +130,15 @@ def test_strided_scatter(emu, monkeypatch):
     pc.check_strided_scatter(np.float32)
 
 
+@pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((8, 8, 16), (1 / 8, 1 / 8, 1 / 16)), ((256, 256), 1 / 256),
+                                        ((512, 8, 32), (1 / 512, 1 / 8, 1 / 32))])
+def test_fused_direction_update(shape, dist):
+    # CG direction update d = r + beta d carried by the first pass (StridedPass on the small grids,
+    # the TMA kernel with the field in shared memory on the 256/512-row ones)
+    pc.check_fused_direction_update(shape, dist)
+    pc.check_fused_direction_update(shape, dist, np.float32)
+
+
 def test_hartley_leading_axes_inner_batch():
     # product-space sub-transforms: leading axes, contiguous inner batch (strided passes + mirror combine)
     import niftyb200 as nb

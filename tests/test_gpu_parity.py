@@ -163,6 +163,13 @@ def test_strided_scatter(cuda, monkeypatch):
     pc.check_strided_scatter(np.float32)
 
 
+@pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((8, 8, 16), (1 / 8, 1 / 8, 1 / 16)), ((4096, 256), 1 / 4096),
+                                        ((1024, 16, 1024), (1 / 1024, 1 / 16, 1 / 1024)), ((256, 256, 256), 1 / 256)])
+def test_fused_direction_update(shape, dist):
+    pc.check_fused_direction_update(shape, dist)
+    pc.check_fused_direction_update(shape, dist, np.float32)
+
+
 def test_hartley_leading_axes_inner_batch():
     import niftyb200 as nb
     shapes = [((16, 8, 4), (0, 1)), ((64, 128, 32), (0, 1)), ((4, 32, 8), (1,)), ((3, 8, 16, 4), (1, 2)),
