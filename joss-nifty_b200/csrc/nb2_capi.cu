@@ -664,8 +664,11 @@ int nb2_strided_pass_remap(nb2_plan* pl, int which, const void* in, void* out, c
         return NB2_ERR_ARG;
     }
     if (pro && (pro->pre_add || pro->pre_out)) {
-        last_error() = "nb2_strided_pass_remap: the fused direction update needs natural input rows";
-        return NB2_ERR_UNSUPPORTED;
+        if (in_rowoff) {
+            last_error() = "nb2_strided_pass_remap: the fused direction update needs natural input rows";
+            return NB2_ERR_UNSUPPORTED;
+        }
+        if (int rc = check_pre_update(pl, pro, nullptr, out, true)) return rc;
     }
     if ((in_rowoff || out_rowoff) && in == out) {
         last_error() = "nb2_strided_pass_remap: a remapped pass cannot run in place";

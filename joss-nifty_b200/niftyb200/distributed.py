@@ -317,10 +317,19 @@ class SlabCorrelatedField:
             field[i] = (tab.azm * table[f12 + f0[i]]).to(self.dtype)
         return SlabTables(field, tab.amps, tab.azm)
 
-    def apply_xi(self, xi, tab, out=None, convention=None, offset=None, mul=None):
+    # The first pass of x_to_y is a strided pass over natural local rows and CAN carry d <- r + beta d
+    # (apply_xi(pre=...) works and is parity-tested), but MEASURED at 2 GPUs the sending pass, already bound
+    # by its NVLink stores, loses more than the saved axpby sweep gains (82.9 vs 90.4 CG it/s,
+    # profiles/r1_bench_f32_n2_fused_vs_unfused.log) -> off unless NIFTYB200_SLAB_FUSED_AXPBY=1
+    fuses_direction_update = os.environ.get("NIFTYB200_SLAB_FUSED_AXPBY", "0") == "1"
+
+    def apply_xi(self, xi, tab, out=None, convention=None, offset=None, mul=None, pre=None):
         off = self.offset_mean if offset is None else offset
         out = torch.empty(self.position_shape, dtype=self.dtype, device=self.device) if out is None else out
-        return self.ht.x_to_y(xi, out, convention, pro=PointOp(2, tab.amp, 1.0),
+        pro = PointOp(2, tab.amp, 1.0)
+        if pre is not None:
+            pro.pre_add, pro.pre_scale, pro.pre_out = pre[0], float(pre[1]), xi
+        return self.ht.x_to_y(xi, out, convention, pro=pro,
                               epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))
 
     def adjoint_xi(self, ybar, tab, out=None, convention=None, add=None, dot=None, dot_out=None):

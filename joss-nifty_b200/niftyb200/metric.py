@@ -53,7 +53,7 @@ class CFMetric:
         self.napply = 0
         # the CG loops hand their pending direction update d <- r + beta d to apply_with_curvature(pre=...)
         # (NIFTYB200_FUSED_AXPBY=0: keep the separate axpby kernel -- A/B measurements)
-        self.fused_direction_update = (bool(getattr(cf, "fuses_direction_update", False)) and self.comm is None
+        self.fused_direction_update = (bool(getattr(cf, "fuses_direction_update", False))
                                        and os.environ.get("NIFTYB200_FUSED_AXPBY", "1") != "0")
 
     def forward_weighted(self, t, out, pre=None):
