@@ -9,6 +9,7 @@ ones: rel-L2 <= 1e-12 (fp64) / 1e-5 (fp32) for applies, identical CG iteration c
 import sys
 
 import numpy as np
+import pytest
 import torch
 
 import niftyb200 as nb
@@ -398,3 +399,29 @@ def check_fused_direction_update(shape, dist, dt=np.float64):
     assert rel(host(q1), host(q2)) <= 10 * tol and abs(c1 - float(c2.cpu())) <= 10 * tol * abs(c1)
     # and against the oracle
     assert rel(host(q1), Mo(want)) <= TOL[dt]
+
+
+def check_new_entry_point_errors():
+    """Argument / support errors of the prologue update and the scatter pass surface as NativeError
+    with the library's message (the C ABI returns NB2_ERR_ARG / NB2_ERR_UNSUPPORTED)."""
+    from niftyb200._lib import NativeError
+    x, r = dev(np.ones((8, 16))), dev(np.ones((8, 16)))
+    out = torch.empty_like(x)
+    plan = get_plan((8, 16), None, x.dtype)
+    with pytest.raises(NativeError, match="prologue"):         # pre_add in an epilogue
+        plan.hartley(x, out=out, epi=PointOp(pre_add=r, pre_scale=1.0))
+    with pytest.raises(NativeError, match="alias"):            # pre_out == out
+        plan.hartley(x, out=out, pro=PointOp(pre_add=r, pre_scale=1.0, pre_out=out))
+    with pytest.raises(NativeError, match="alias|needs pre_add"):   # pre_out without pre_add
+        plan.hartley(x, out=out, pro=PointOp(pre_out=x))
+    x1 = dev(np.ones(64))
+    with pytest.raises(NativeError, match="strided pass"):     # 1-D: the first pass is the row pass
+        get_plan((64,), None, x1.dtype).hartley(x1, pro=PointOp(pre_add=x1.clone(), pre_scale=1.0))
+    xg = dev(np.ones((6, 10)))
+    with pytest.raises(NativeError, match="strided pass"):     # generic (non power-of-two) plan
+        get_plan((6, 10), None, xg.dtype).hartley(xg, pro=PointOp(pre_add=xg.clone(), pre_scale=1.0))
+    tab = dev(np.zeros(8, dtype=np.int64))
+    with pytest.raises(NativeError, match="invalid argument"):  # in place
+        plan.run_strided_scatter(1, x, x, out_rowoff=tab)
+    with pytest.raises(NativeError, match="not part of this plan"):   # (8, 16) is 2-D: no axis-0 pass
+        plan.run_strided_scatter(0, x, out, out_rowoff=tab)

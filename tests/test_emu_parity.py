@@ -139,6 +139,10 @@ def test_fused_direction_update(shape, dist):
     pc.check_fused_direction_update(shape, dist, np.float32)
 
 
+def test_new_entry_point_errors():
+    pc.check_new_entry_point_errors()
+
+
 def test_hartley_leading_axes_inner_batch():
     # product-space sub-transforms: leading axes, contiguous inner batch (strided passes + mirror combine)
     import niftyb200 as nb

@@ -170,6 +170,10 @@ def test_fused_direction_update(shape, dist):
     pc.check_fused_direction_update(shape, dist, np.float32)
 
 
+def test_new_entry_point_errors():
+    pc.check_new_entry_point_errors()
+
+
 def test_hartley_leading_axes_inner_batch():
     import niftyb200 as nb
     shapes = [((16, 8, 4), (0, 1)), ((64, 128, 32), (0, 1)), ((4, 32, 8), (1,)), ((3, 8, 16, 4), (1, 2)),
