@@ -237,9 +237,10 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
         }
     }
     int rc = 0;
-#define NB2_RUN_ROWS(A, B, C)                                                                 \
+#define NB2_RUN_ROWS(A, B, C) NB2_RUN_ROWS_E(A, B, C, -1)
+#define NB2_RUN_ROWS_E(A, B, C, E)                                                            \
     {                                                                                         \
-        typedef RowPass<T, A, B, C> K;                                                        \
+        typedef RowPass<T, A, B, C, E> K;                                                     \
         typename K::Params p;                                                                 \
         p.in = (const cplx<T>*)in;                                                            \
         p.out = (T*)out;                                                                      \
@@ -267,17 +268,40 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
         p.staged = 0;                                                                         \
         if (smem > kSmemLimit) {                                                              \
             rc = NB2_ERR_UNSUPPORTED;                                                         \
-        } else if (stages && !grp && grid >= 4ll * rt_sm_count() && aligned16(in)) {          \
-            p.staged = 1;                                                                     \
-            rc = rt_launch_pipe<K>(grid, 0, nthreads, smem, stages, st, p);                   \
+        } else if ((E) < 0 && stages && !grp && grid >= 4ll * rt_sm_count() && aligned16(in)) { \
+            if constexpr ((E) < 0) {                                                          \
+                p.staged = 1;                                                                 \
+                rc = rt_launch_pipe<K>(grid, 0, nthreads, smem, stages, st, p);               \
+            }                                                                                 \
         } else {                                                                              \
             if (!grp && M_BYTES_OK(A * B * C, T) && launch_grid >= 8ll * rt_sm_count())        \
                 p.la = rows_lookahead<K>(nthreads, smem);                                     \
             rc = rt_launch<K>(launch_grid, nthreads, smem, st, p);                            \
         }                                                                                     \
     }
+    // compile-time epilogues for the three operand sets of the hot path (plain transform, metric forward
+    // `* weight`, metric adjoint `* field + add, dot`) on rows of 512..2048 scalars; NB2_ROWS_SPEC=0: generic
+    int mask = -1;
+    if (logm >= 8 && logm <= 10) {
+        if (!epi) {
+            mask = 0;
+        } else if (!epi->bin_x && epi->amp_mode != 1 && (!epi->dot || epi->dot == epi->add)) {
+            mask = (epi->amp_mode == 2 ? 1 : 0) | (epi->mul ? 2 : 0) | (epi->add ? 4 : 0) | (epi->dot ? 8 : 0);
+        }
+        if (mask != 0 && mask != 2 && mask != 13) mask = -1;
+        if (const char* e = std::getenv("NB2_ROWS_SPEC"))
+            if (e[0] == '0') mask = -1;
+    }
+#define NB2_ROWS_MASKS(A, B, C)                                                  \
+    if (mask == 0) NB2_RUN_ROWS_E(A, B, C, 0)                                    \
+    else if (mask == 2) NB2_RUN_ROWS_E(A, B, C, 2)                               \
+    else NB2_RUN_ROWS_E(A, B, C, 13)
     const char* alt = std::getenv("NB2_PLAN9");
-    if (logm == 9 && alt && alt[0] == 'a') {
+    if (mask >= 0 && !(logm == 9 && alt)) {
+        if (logm == 8) { NB2_ROWS_MASKS(16, 1, 16) }
+        else if (logm == 9) { NB2_ROWS_MASKS(32, 1, 16) }
+        else { NB2_ROWS_MASKS(32, 1, 32) }
+    } else if (logm == 9 && alt && alt[0] == 'a') {
         NB2_RUN_ROWS(16, 2, 16)
     } else if (logm == 9 && alt && alt[0] == 'b') {
         NB2_RUN_ROWS(8, 8, 8)
@@ -286,6 +310,8 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
     } else {
         NB2_PLAN_SWITCH(logm, NB2_RUN_ROWS)
     }
+#undef NB2_ROWS_MASKS
+#undef NB2_RUN_ROWS_E
 #undef NB2_RUN_ROWS
     if (rc) return rc;
     if (want_dot && (!grp || grp->reduce)) {

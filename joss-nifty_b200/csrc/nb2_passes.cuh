@@ -372,7 +372,16 @@ struct RowSlot {
     long long k0, k1, row;  // row: linear row index over (batch, N0, N1)
 };
 
-template <typename T, int R1, int R2, int R3>
+// EPI >= 0: the epilogue operands are known at compile time (bit 0 streamed amplitude field, bit 1 mul,
+// bit 2 add, bit 3 dot with dot == add; no ksq table, no binned reduction), which removes the per-element
+// operand tests of the untangle phase -- the phase that executes 57 % of the kernel's instructions.
+// EPI < 0: everything decided at run time.
+#if defined(__CUDA_ARCH__)
+#define NB2_ASSUME(c) __builtin_assume(c)
+#else
+#define NB2_ASSUME(c) do { if (!(c)) __builtin_unreachable(); } while (0)
+#endif
+template <typename T, int R1, int R2, int R3, int EPI = -1>
 struct RowPass {
     static constexpr int M = R1 * R2 * R3;
     static constexpr int MM = R2 * R3;
@@ -694,6 +703,13 @@ struct RowPass {
                 const SlotCache* cache = slot_cache(p, smem_raw, nthreads);
                 PointOp<T> e = p.epi;
                 e.scale = p.epi.scale * T(0.5);          // the 1/2 of the untangle step rides on the scale
+                if (EPI >= 0) {
+                    e.amp_mode = (EPI & 1) ? 2 : 0;
+                    if (EPI & 2) NB2_ASSUME(e.mul != nullptr); else e.mul = nullptr;
+                    if (EPI & 4) NB2_ASSUME(e.add != nullptr); else e.add = nullptr;
+                    e.dot = (EPI & 8) ? e.add : nullptr;
+                    e.bin_x = nullptr;
+                }
                 for (int b = tid; b < nb; b += nthreads) {
                     const int k = (b % Q4) * 4, s = b / Q4;
                     const SlotCache sc = cache[s];

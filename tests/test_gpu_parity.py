@@ -170,6 +170,18 @@ def test_fused_direction_update(shape, dist):
     pc.check_fused_direction_update(shape, dist, np.float32)
 
 
+def test_row_pass_compile_time_epilogues(monkeypatch):
+    # rows of 512 / 1024 / 2048 scalars take the RowPass instantiations with compile-time epilogues
+    # (plain, * weight, * field + add + dot); NB2_ROWS_SPEC=0 must give the same answers generically
+    for spec in ("1", "0"):
+        monkeypatch.setenv("NB2_ROWS_SPEC", spec)
+        pc.check_hartley_shapes([((512,), None), ((4, 1024), None), ((2, 2, 2048), None)])
+        pc.check_metric((8, 512), (1 / 8, 1 / 512))
+        pc.check_metric((4, 4, 1024), (1 / 4, 1 / 4, 1 / 1024), np.float32)
+        pc.check_cf_vs_oracle((2, 2048), (1 / 2, 1 / 2048), np.float64, None)
+        pc.check_fused_direction_update((8, 512), (1 / 8, 1 / 512))
+
+
 def test_new_entry_point_errors():
     pc.check_new_entry_point_errors()
 
