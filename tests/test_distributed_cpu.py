@@ -30,6 +30,13 @@ def test_slab_two_ranks_gloo_chunked_exchange(monkeypatch):
     check(res)
 
 
+def test_slab_two_ranks_gloo_long_rows():
+    # rows of 512 scalars: the row pass with compile-time epilogues (EPI = 2 / 13) on the shifted-mirror
+    # geometry of the slabs
+    res = dist_worker.launch(2, "gloo", conftest.build_emulator(), (8, 8, 512), port=29545)
+    check(res, strict=False)
+
+
 def test_slab_four_ranks_gloo():
     res = dist_worker.launch(4, "gloo", conftest.build_emulator(), (16, 16, 8), port=29541)
     check(res)
