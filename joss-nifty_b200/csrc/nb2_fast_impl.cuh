@@ -212,9 +212,25 @@ int rows_pairs_per_cta(const nb2_plan* pl) {
     return G;
 }
 
+// The row pass is compiled in three parts (separate translation units, so that the build runs them in
+// parallel): PART 0 = rows of up to 256 scalars, PART 1 = 512..2048 scalars (with the compile-time
+// epilogues), PART 2 = longer rows (three-step plans).
+template <typename T, int PART>
+int run_rows_part(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
+                  rt_stream st, const RowGroup* grp);
+
 template <typename T>
 int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
              rt_stream st, const RowGroup* grp) {
+    const int logm = pl->g.logM;
+    if (logm <= 7) return run_rows_part<T, 0>(pl, in, out, conv, pro, epi, st, grp);
+    if (logm <= 10) return run_rows_part<T, 1>(pl, in, out, conv, pro, epi, st, grp);
+    return run_rows_part<T, 2>(pl, in, out, conv, pro, epi, st, grp);
+}
+
+template <typename T, int PART>
+int run_rows_part(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
+                  rt_stream st, const RowGroup* grp) {
     const int logm = pl->g.logM;
     const RowPairs rp = row_pairs(pl->g);
     const int G = grp ? grp->G : rows_pairs_per_cta<T>(pl);
@@ -297,18 +313,43 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
     else if (mask == 2) NB2_RUN_ROWS_E(A, B, C, 2)                               \
     else NB2_RUN_ROWS_E(A, B, C, 13)
     const char* alt = std::getenv("NB2_PLAN9");
-    if (mask >= 0 && !(logm == 9 && alt)) {
-        if (logm == 8) { NB2_ROWS_MASKS(16, 1, 16) }
-        else if (logm == 9) { NB2_ROWS_MASKS(32, 1, 16) }
-        else { NB2_ROWS_MASKS(32, 1, 32) }
-    } else if (logm == 9 && alt && alt[0] == 'a') {
-        NB2_RUN_ROWS(16, 2, 16)
-    } else if (logm == 9 && alt && alt[0] == 'b') {
-        NB2_RUN_ROWS(8, 8, 8)
-    } else if (logm == 9 && alt && alt[0] == 'c') {
-        NB2_RUN_ROWS(16, 1, 32)
+    if constexpr (PART == 0) {
+        switch (logm) {
+            case 1: NB2_RUN_ROWS(2, 1, 1) break;
+            case 2: NB2_RUN_ROWS(4, 1, 1) break;
+            case 3: NB2_RUN_ROWS(8, 1, 1) break;
+            case 4: NB2_RUN_ROWS(16, 1, 1) break;
+            case 5: NB2_RUN_ROWS(32, 1, 1) break;
+            case 6: NB2_RUN_ROWS(8, 1, 8) break;
+            case 7: NB2_RUN_ROWS(16, 1, 8) break;
+            default: rc = NB2_ERR_UNSUPPORTED; break;
+        }
+    } else if constexpr (PART == 1) {
+        if (mask >= 0 && !(logm == 9 && alt)) {
+            if (logm == 8) { NB2_ROWS_MASKS(16, 1, 16) }
+            else if (logm == 9) { NB2_ROWS_MASKS(32, 1, 16) }
+            else { NB2_ROWS_MASKS(32, 1, 32) }
+        } else if (logm == 9 && alt && alt[0] == 'a') {
+            NB2_RUN_ROWS(16, 2, 16)
+        } else if (logm == 9 && alt && alt[0] == 'b') {
+            NB2_RUN_ROWS(8, 8, 8)
+        } else if (logm == 9 && alt && alt[0] == 'c') {
+            NB2_RUN_ROWS(16, 1, 32)
+        } else {
+            switch (logm) {
+                case 8: NB2_RUN_ROWS(16, 1, 16) break;
+                case 9: NB2_RUN_ROWS(32, 1, 16) break;
+                case 10: NB2_RUN_ROWS(32, 1, 32) break;
+                default: rc = NB2_ERR_UNSUPPORTED; break;
+            }
+        }
     } else {
-        NB2_PLAN_SWITCH(logm, NB2_RUN_ROWS)
+        switch (logm) {
+            case 11: NB2_RUN_ROWS(16, 8, 16) break;
+            case 12: NB2_RUN_ROWS(16, 16, 16) break;
+            case 13: NB2_RUN_ROWS(32, 16, 16) break;
+            default: rc = NB2_ERR_UNSUPPORTED; break;
+        }
     }
 #undef NB2_ROWS_MASKS
 #undef NB2_RUN_ROWS_E
