@@ -151,6 +151,22 @@ def test_row_pass_compile_time_epilogues(monkeypatch):
         pc.check_fused_direction_update((8, 512), (1 / 8, 1 / 512))
 
 
+def test_hartley_random_pow2_shapes():
+    # seeded sweep over power-of-two shapes and axis subsets: every radix plan up to 2048-scalar rows, all
+    # three row-pass parts, strided passes with and without a leading batch
+    rng = np.random.default_rng(2024)
+    cases = []
+    while len(cases) < 40:
+        nd = int(rng.integers(1, 4))
+        shape = tuple(int(2 ** rng.integers(0, 7)) for _ in range(nd - 1)) + (int(2 ** rng.integers(1, 12)),)
+        if np.prod(shape) > 1 << 16:
+            continue
+        first = int(rng.integers(0, nd))                    # transform the trailing axes first..nd-1
+        cases.append((shape, None if first == 0 else tuple(range(first, nd))))
+    pc.check_hartley_shapes(cases, dtypes=(np.float64,))
+    pc.check_hartley_shapes(cases[::3], dtypes=(np.float32,))
+
+
 def test_new_entry_point_errors():
     pc.check_new_entry_point_errors()
 
