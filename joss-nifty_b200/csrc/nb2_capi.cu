@@ -2,6 +2,8 @@
 //
 // Built with nvcc for sm_100a into libniftyb200.so.  With -DNB2_EMU (host compiler) the
 // same file builds the sequential thread emulator used by the CPU-only index tests.
+#include <mutex>
+
 #include "nb2_generic.cuh"
 #include "nb2_plan.h"
 #include "nb2_passes.cuh"
@@ -11,28 +13,35 @@ using namespace nb2;
 
 namespace {
 
+// Reduction scratch of the vector kernels (nb2_vdot, nb2_cg_update): one buffer per DEVICE, shared by all
+// host threads and streams of the process -- the vector kernels and the plans are single-stream objects:
+// two reductions must not be in flight on different streams of one device at the same time.
 struct Ctx {
-    double* partials = nullptr;  // reduction scratch for the vector kernels
+    double* partials = nullptr;
     long long npartials = 0;
-    int sms = 0;
 };
 Ctx& ctx() {
-    static thread_local Ctx c;
-    return c;
+    static Ctx c[kMaxDevices];
+    return c[rt_device() % kMaxDevices];
 }
 int ensure_ctx() {
+    static std::mutex m;
     Ctx& c = ctx();
     if (!c.partials) {
-        c.sms = rt_sm_count();
-        c.npartials = (long long)c.sms * 8 * 4;
-        if (rt_malloc((void**)&c.partials, c.npartials * sizeof(double))) return NB2_ERR_CUDA;
+        std::lock_guard<std::mutex> lock(m);
+        if (!c.partials) {
+            const long long n = (long long)rt_sm_count() * 8 * 4;
+            double* p = nullptr;
+            if (rt_malloc((void**)&p, n * sizeof(double))) return NB2_ERR_CUDA;
+            c.npartials = n;
+            c.partials = p;
+        }
     }
     return 0;
 }
 long long vec_grid(long long n) {
-    Ctx& c = ctx();
     const long long want = (n + kVecThreads - 1) / kVecThreads;
-    return std::max(1ll, std::min(want, (long long)c.sms * 8));
+    return std::max(1ll, std::min(want, (long long)rt_sm_count() * 8));
 }
 
 }  // namespace
@@ -83,104 +92,12 @@ int upload_table(void** dev, long long n, long long denom) {
     return rt_h2d(*dev, h.data(), n * sizeof(cplx<T>), nullptr);
 }
 
-// Planes per group of the L2-blocked tail (0: off).  The axis-1 pass and the row pass of a 3-D
-// transform are run group by group -- a few planes k0 together with their mirror planes N0 - k0 --
-// through a small buffer that stays resident in the 126 MB L2, so the intermediate between the two
-// passes never travels to HBM: the transform moves 4 N s bytes instead of 6 N s.
-// MEASURED (B200, 1024^3 fp32, profiles/r1_l2_blocked_tail.log): the ~256 small launches per transform
-// (20-25 us each, 1.7 waves) lose more in ramp-up/tail than the saved HBM traffic gains, even spread
-// over 2-4 streams: 6.37 ms vs 6.27 ms for the three full-size passes.  Therefore OPT-IN:
-// NB2_L2_PLANES=n runs groups of n planes (tests use it on small grids); unset / 0 disables.
-template <typename T>
-long long l2_group_planes(const nb2_plan* pl) {
-    const Geom& g = pl->g;
-    if (g.batch != 1 || g.shift0 || g.shift1 || g.logN0 < 2 || g.logN1 < 5) return 0;
-    const long long N0 = 1ll << g.logN0;
-    const char* e = std::getenv("NB2_L2_PLANES");
-    if (!e) return 0;
-    long long gp = std::atoll(e) & ~1ll;
-    if (gp > N0 - 2) gp = N0 - 2;
-    return gp < 2 ? 0 : gp;
-}
-
-template <typename T>
-int hartley_fast_l2(nb2_plan* pl, long long gp, const void* in, void* out, int conv, const nb2_pointop* pro,
-                    const nb2_pointop* epi, rt_stream st) {
-    int rc;
-    const Geom& g = pl->g;
-    const long long N0 = 1ll << g.logN0, N1 = 1ll << g.logN1;
-    const size_t plane = sizeof(cplx<T>) << (g.logN1 + g.logM);
-    // the groups alternate between S auxiliary streams (each with its own group buffer) so that one
-    // group's kernels fill the tail of the other's; NB2_L2_STREAMS=1 keeps everything on `st`
-    int S = 2;
-    if (const char* e = std::getenv("NB2_L2_STREAMS")) S = std::max(1, std::min(nb2_plan::kMaxAux, std::atoi(e)));
-    if (pl->l2buf_bytes < plane * gp * S) {
-        if (rt_sync(st)) return NB2_ERR_CUDA;
-        for (int k = 0; k < pl->naux; ++k)
-            if (rt_sync(pl->aux[k])) return NB2_ERR_CUDA;
-        if (rt_free(pl->l2buf)) return NB2_ERR_CUDA;
-        pl->l2buf = nullptr;
-        pl->l2buf_bytes = 0;
-        if (rt_malloc(&pl->l2buf, plane * gp * S)) return NB2_ERR_CUDA;
-        pl->l2buf_bytes = plane * gp * S;
-    }
-    if (S > 1) {
-        if (!pl->ev_fork && rt_event_create(&pl->ev_fork)) return NB2_ERR_CUDA;
-        for (; pl->naux < S; ++pl->naux)
-            if (rt_stream_create(&pl->aux[pl->naux]) || rt_event_create(&pl->ev_join[pl->naux])) return NB2_ERR_CUDA;
-    }
-    if ((rc = run_strided<T>(pl, 0, in, out, pro, st))) return rc;
-    if (S > 1) {
-        if (rt_event_record(pl->ev_fork, st)) return NB2_ERR_CUDA;
-        for (int k = 0; k < S; ++k)
-            if (rt_stream_wait(pl->aux[k], pl->ev_fork)) return NB2_ERR_CUDA;
-    }
-    const RowPairs rp = row_pairs(g);
-    RowGroup rg;
-    rg.G = rows_pairs_per_cta<T>(pl);
-    const long long half = gp / 2;
-    // groups of `half` planes k0 in [a, b) plus their mirrors; the last group is {0, N0/2}
-    long long gi = 0;
-    for (long long a = 1;; a += half, ++gi) {
-        const bool last = a >= N0 / 2;
-        const long long b = last ? 0 : std::min(a + half, N0 / 2);
-        const int k = int(gi % S);
-        rt_stream gs = S > 1 ? pl->aux[k] : st;
-        void* buf = (char*)pl->l2buf + plane * gp * k;
-        RowRemap rm;
-        rm.grp_on = rm.keep_out = 1;
-        rm.grp_lo_a = last ? 0 : a;
-        rm.grp_lo_n = last ? 1 : b - a;
-        rm.grp_hi_a = last ? N0 / 2 : N0 - b + 1;
-        rm.grp_n = 2 * rm.grp_lo_n;
-        if ((rc = run_strided<T>(pl, 1, out, buf, nullptr, gs, &rm))) return rc;
-        rg.q0 = last ? rp.nmid : (a - 1) * N1;
-        rg.q_end = last ? rp.Q : (b - 1) * N1;
-        rg.lo_a = rm.grp_lo_a;
-        rg.lo_n = rm.grp_lo_n;
-        rg.hi_a = rm.grp_hi_a;
-        rg.reduce = false;
-        if ((rc = run_rows<T>(pl, buf, out, conv, nullptr, epi, gs, &rg))) return rc;
-        if (last) break;
-    }
-    if (S > 1) {
-        for (int k = 0; k < S; ++k)
-            if (rt_event_record(pl->ev_join[k], pl->aux[k]) || rt_stream_wait(st, pl->ev_join[k])) return NB2_ERR_CUDA;
-    }
-    if (epi && epi->dot) {
-        const long long grid = (rp.Q + rg.G - 1) / rg.G;
-        return launch_final_reduce(pl->partials, grid, 1, epi->dot_out, st);
-    }
-    return NB2_OK;
-}
-
 template <typename T>
 int hartley_fast(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
                  rt_stream st) {
     const void* cur = in;
     const nb2_pointop* p = pro;
     int rc;
-    if (const long long gp = l2_group_planes<T>(pl)) return hartley_fast_l2<T>(pl, gp, in, out, conv, pro, epi, st);
     if (pl->g.logN0 > 0) {
         if ((rc = run_strided<T>(pl, 0, cur, out, p, st))) return rc;
         cur = out;
@@ -419,6 +336,12 @@ int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* ax
     if (!pl) return NB2_ERR_ARG;
     pl->ndim = ndim;
     pl->dtype = dtype;
+    {
+        const char* e;
+        if ((e = std::getenv("NB2_TMA"))) pl->knob_tma = e[0] != '0';
+        if ((e = std::getenv("NB2_TMA_SCATTER"))) pl->knob_tma_scatter = e[0] == '1';
+        if ((e = std::getenv("NB2_TMA_FX"))) pl->knob_tma_fx = e[0] != '0';
+    }
     for (int i = 0; i < ndim; ++i) {
         if (shape[i] < 1) {
             delete pl;
@@ -534,12 +457,6 @@ int nb2_plan_destroy(nb2_plan* pl) {
     rt_free(pl->tw1);
     rt_free(pl->twr);
     rt_free(pl->partials);
-    rt_free(pl->l2buf);
-    for (int k = 0; k < pl->naux; ++k) {
-        rt_stream_destroy(pl->aux[k]);
-        rt_event_destroy(pl->ev_join[k]);
-    }
-    rt_event_destroy(pl->ev_fork);
     rt_free(pl->work0);
     rt_free(pl->work1);
     for (int t = 0; t < kMaxDim; ++t) rt_free(pl->roots[t]);
@@ -790,7 +707,10 @@ int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, c
 }
 
 int nb2_hartley_host(nb2_plan* pl, const void* in_host, void* out_host, int conv, double scale) {
-    if (!pl || !in_host || !out_host) return NB2_ERR_ARG;
+    if (!pl || !in_host || !out_host || (conv != 0 && conv != 1)) {
+        last_error() = "nb2_hartley_host: invalid argument";
+        return NB2_ERR_ARG;
+    }
     const size_t es = pl->dtype == NB2_F32 ? 4 : 8;
     void* buf = nullptr;
     if (rt_malloc(&buf, pl->total * es)) return NB2_ERR_CUDA;
@@ -804,7 +724,10 @@ int nb2_hartley_host(nb2_plan* pl, const void* in_host, void* out_host, int conv
 }
 
 int nb2_c2c_host(nb2_plan* pl, const void* in_host, void* out_host, int forward, double scale) {
-    if (!pl || !in_host || !out_host) return NB2_ERR_ARG;
+    if (!pl || !in_host || !out_host) {
+        last_error() = "nb2_c2c_host: invalid argument";
+        return NB2_ERR_ARG;
+    }
     const size_t es = pl->dtype == NB2_F32 ? 8 : 16;
     void* buf = nullptr;
     if (rt_malloc(&buf, pl->total * es)) return NB2_ERR_CUDA;

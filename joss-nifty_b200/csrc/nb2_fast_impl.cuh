@@ -44,28 +44,6 @@ int choose_logw(int logn, long long inner, bool remote_out = false) {
     return logw;
 }
 
-// ---------------------------------------------------------------- pipelined (persistent) launches
-constexpr size_t kPipeSmem = 226 * 1024;
-// number of stage buffers of a persistent CTA (0: do not pipeline); NB2_PIPE=0 / NB2_STAGES=n: tuning knobs
-inline int pipe_stages(size_t stage_bytes) {
-    // measured on B200 (1024^3 fp32): the persistent cp.async variant is slower than many small
-    // CTAs for these passes (fewer compute warps per SM; 8-byte copies for padded fp32 rows), so it
-    // is opt-in (NB2_PIPE=1) and kept for launches that must leave SMs free
-    const char* pe = std::getenv("NB2_PIPE");
-    if (!pe || pe[0] != '1') return 0;
-    int want = 3;
-    if (const char* e = std::getenv("NB2_STAGES")) want = std::atoi(e);
-    while (want >= 2 && stage_bytes * want > kPipeSmem) --want;
-    return want >= 2 ? want : 0;
-}
-inline int pipe_threads(int nthreads, int maxt) {
-    if (const char* e = std::getenv("NB2_THREADS")) {
-        const int v = std::atoi(e);
-        if (v >= 32 && v <= maxt && v % 32 == 0) return v;
-    }
-    return nthreads;
-}
-
 // Persistent TMA-fed variant (nb2_tma.cuh); defined in nb2_fast_tma_impl.cuh and instantiated in its own
 // translation units (nb2_fast_tma_f32.cu / _f64.cu) so that the build compiles it in parallel.
 template <typename T>
@@ -81,13 +59,13 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
     }
     const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
     // natural input, all columns: the TMA kernel (its stores may be scattered through the out tables)
-    if (!rm || (!rm->in_rowoff && !rm->ncols && !rm->grp_on && !rm->col0)) {
+    if (!rm || (!rm->in_rowoff && !rm->ncols && !rm->col0)) {
         bool done = false;
         const int rc = run_strided_tma<T>(pl, axis, logn, inner, axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0),
                                           in, out, pro, st, &done, rm);
         if (rc || done) return rc;
     }
-    const long long outer = (rm && rm->grp_on) ? rm->grp_n : axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
+    const long long outer = axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0);
     const long long ncols = (rm && rm->ncols) ? rm->ncols : inner;
     const long long run = (rm && rm->run) ? rm->run : ncols;
     if (ncols > inner || (ncols & (ncols - 1)) || (run & (run - 1)) || run > ncols) {
@@ -97,12 +75,6 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
     int logw = choose_logw<T>(logn, inner, rm && rm->out_rowoff);
     while ((1ll << logw) > run) --logw;
     if (rm && rm->out_coloff && logw > pl->g.logM) logw = pl->g.logM;   // a tile must not straddle column blocks
-    // developer tuning knobs (not part of the API): tile width / alternative radix plan
-    if (const char* e = std::getenv("NB2_STRIDED_LOGW")) {
-        const int v = std::atoi(e);
-        if (v >= 0 && (1ll << v) <= run) logw = v;
-    }
-    const char* alt = std::getenv("NB2_PLAN10");
     int rc = 0;
 #define NB2_RUN_STRIDED(A, B, C)                                                              \
     {                                                                                         \
@@ -127,40 +99,16 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         p.col0 = rm ? rm->col0 : 0;                                                           \
         p.run_stride = rm ? rm->run_stride : 0;                                               \
         p.logrun = ilog2(run);                                                                \
-        p.grp_on = rm ? rm->grp_on : 0;                                                       \
-        p.keep_out = rm ? rm->keep_out : 0;                                                   \
-        p.grp_lo_a = rm ? rm->grp_lo_a : 0;                                                   \
-        p.grp_lo_n = rm ? rm->grp_lo_n : 0;                                                   \
-        p.grp_hi_a = rm ? rm->grp_hi_a : 0;                                                   \
         const size_t smem = K::smem_bytes(logw);                                              \
-        p.staged = p.pro_staged = 0;                                                          \
         if (smem > kSmemLimit) {                                                              \
             rc = NB2_ERR_UNSUPPORTED;                                                         \
         } else {                                                                              \
             const long long nb1 = (long long)(B * C) << logw;                                 \
-            const int maxt = K::MAX_THREADS;                                                  \
-            const int nthreads = pipe_threads(std::min(maxt, round32(nb1)), maxt);            \
-            const long long ntiles = outer * p.tiles_per_outer;                               \
-            const bool field = pro && pro->amp_mode == 2;                                     \
-            const size_t stage = smem * (field ? 2 : 1);                                      \
-            const int stages = pipe_stages(stage);                                            \
-            if (!K::SINGLE && stages && !p.grp_on && !(pro && pro->pre_add) && ntiles >= 4ll * rt_sm_count() && \
-                (sizeof(cplx<T>) << logw) >= 16 && aligned16(in) && (!field || aligned16(pro->amp))) { \
-                p.staged = 1;                                                                 \
-                p.pro_staged = field ? 1 : 0;                                                 \
-                rc = rt_launch_pipe<K>(ntiles, 0, nthreads, stage, stages, st, p);            \
-            } else {                                                                          \
-                rc = rt_launch<K>(ntiles, nthreads, smem, st, p);                             \
-            }                                                                                 \
+            const int nthreads = std::min((int)K::MAX_THREADS, round32(nb1));                 \
+            rc = rt_launch<K>(outer * p.tiles_per_outer, nthreads, smem, st, p);              \
         }                                                                                     \
     }
-    if (logn == 10 && alt && alt[0] == 'a') {
-        NB2_RUN_STRIDED(16, 4, 16)
-    } else if (logn == 10 && alt && alt[0] == 'b') {
-        NB2_RUN_STRIDED(8, 16, 8)
-    } else {
-        NB2_PLAN_SWITCH(logn, NB2_RUN_STRIDED)
-    }
+    NB2_PLAN_SWITCH(logn, NB2_RUN_STRIDED)
 #undef NB2_RUN_STRIDED
     return rc;
 }
@@ -173,43 +121,10 @@ int choose_G(int logm, long long Q) {
     return G;
 }
 
-// rows of at least 16 bytes, a multiple of 16
-#define M_BYTES_OK(M, T) ((size_t(M) * sizeof(cplx<T>)) % 16 == 0)
-// L2 prefetch distance of the row pass (cp.async.bulk.prefetch.L2 of a later CTA's rows).  MEASURED on
-// B200 (profiles/r1_rowpass_l2_prefetch.log): no gain at any distance -- the row pass is bound by issue
-// slots and shared-memory traffic, not by DRAM latency -- so it is OFF unless NB2_ROWS_LA=n asks for a
-// distance of n CTAs (NB2_ROWS_LA=auto: the number of CTAs resident at once).
-template <class K>
-long long rows_lookahead(int nthreads, size_t smem) {
-    const char* e = std::getenv("NB2_ROWS_LA");
-    if (!e) return 0;
-    if (e[0] != 'a') return std::atoll(e);
-#if !defined(NB2_EMU)
-    static thread_local int c_threads = 0, c_per_sm = 0;     // per kernel instantiation
-    static thread_local size_t c_smem = 0;
-    if (c_threads != nthreads || c_smem != smem) {
-        int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb2_kernel<K>, nthreads, smem) != cudaSuccess)
-            per_sm = 0;
-        c_threads = nthreads;
-        c_smem = smem;
-        c_per_sm = per_sm;
-    }
-    return (long long)c_per_sm * rt_sm_count();
-#else
-    return 8;
-#endif
-}
-
 template <typename T>
 int rows_pairs_per_cta(const nb2_plan* pl) {
     const RowPairs rp = row_pairs(pl->g);
-    int G = choose_G<T>(pl->g.logM, rp.Q);
-    if (const char* e = std::getenv("NB2_ROWS_G")) {
-        const int v = std::atoi(e);
-        if (v >= 1 && v <= 16 && 2 * v <= rp.Q + 1) G = v;
-    }
-    return G;
+    return choose_G<T>(pl->g.logM, rp.Q);
 }
 
 // The row pass is compiled in three parts (separate translation units, so that the build runs them in
@@ -217,26 +132,25 @@ int rows_pairs_per_cta(const nb2_plan* pl) {
 // epilogues), PART 2 = longer rows (three-step plans).
 template <typename T, int PART>
 int run_rows_part(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
-                  rt_stream st, const RowGroup* grp);
+                  rt_stream st);
 
 template <typename T>
 int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
-             rt_stream st, const RowGroup* grp) {
+             rt_stream st) {
     const int logm = pl->g.logM;
-    if (logm <= 7) return run_rows_part<T, 0>(pl, in, out, conv, pro, epi, st, grp);
-    if (logm <= 10) return run_rows_part<T, 1>(pl, in, out, conv, pro, epi, st, grp);
-    return run_rows_part<T, 2>(pl, in, out, conv, pro, epi, st, grp);
+    if (logm <= 7) return run_rows_part<T, 0>(pl, in, out, conv, pro, epi, st);
+    if (logm <= 10) return run_rows_part<T, 1>(pl, in, out, conv, pro, epi, st);
+    return run_rows_part<T, 2>(pl, in, out, conv, pro, epi, st);
 }
 
 template <typename T, int PART>
 int run_rows_part(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
-                  rt_stream st, const RowGroup* grp) {
+                  rt_stream st) {
     const int logm = pl->g.logM;
     const RowPairs rp = row_pairs(pl->g);
-    const int G = grp ? grp->G : rows_pairs_per_cta<T>(pl);
+    const int G = rows_pairs_per_cta<T>(pl);
     const long long ctas_per_item = (rp.Q + G - 1) / G;
-    const long long grid = ctas_per_item * pl->g.batch;          // partials cover the whole transform
-    const long long launch_grid = grp ? (grp->q_end - grp->q0 + G - 1) / G : grid;
+    const long long grid = ctas_per_item * pl->g.batch;
     const bool want_dot = epi && epi->dot;
     if (want_dot) {
         if (!epi->dot_out) {
@@ -268,35 +182,17 @@ int run_rows_part(nb2_plan* pl, const void* in, void* out, int conv, const nb2_p
         p.has_pro = pro ? 1 : 0;                                                              \
         p.pro = to_pointop<T>(pro, nullptr);                                                  \
         p.epi = to_pointop<T>(epi, pl->partials);                                             \
-        p.bid0 = grp ? grp->q0 / G : 0;                                                       \
-        p.q_end = grp ? grp->q_end : rp.Q;                                                    \
-        p.grp_on = grp ? 1 : 0;                                                               \
-        p.la = 0;                                                                             \
-        p.bid_end = p.bid0 + launch_grid;                                                     \
-        p.grp_lo_a = grp ? grp->lo_a : 0;                                                     \
-        p.grp_lo_n = grp ? grp->lo_n : 0;                                                     \
-        p.grp_hi_a = grp ? grp->hi_a : 0;                                                     \
         const long long nb1 = (long long)2 * G * B * C;                                       \
-        const int maxt = K::MAX_THREADS;                                                      \
-        const int nthreads = pipe_threads(std::min(maxt, round32(nb1)), maxt);                \
+        const int nthreads = std::min((int)K::MAX_THREADS, round32(nb1));                     \
         const size_t smem = (K::smem_bytes(G, nthreads) + 15) & ~size_t(15);                  \
-        const int stages = pipe_stages(smem);                                                 \
-        p.staged = 0;                                                                         \
         if (smem > kSmemLimit) {                                                              \
             rc = NB2_ERR_UNSUPPORTED;                                                         \
-        } else if ((E) < 0 && stages && !grp && grid >= 4ll * rt_sm_count() && aligned16(in)) { \
-            if constexpr ((E) < 0) {                                                          \
-                p.staged = 1;                                                                 \
-                rc = rt_launch_pipe<K>(grid, 0, nthreads, smem, stages, st, p);               \
-            }                                                                                 \
         } else {                                                                              \
-            if (!grp && M_BYTES_OK(A * B * C, T) && launch_grid >= 8ll * rt_sm_count())        \
-                p.la = rows_lookahead<K>(nthreads, smem);                                     \
-            rc = rt_launch<K>(launch_grid, nthreads, smem, st, p);                            \
+            rc = rt_launch<K>(grid, nthreads, smem, st, p);                                   \
         }                                                                                     \
     }
     // compile-time epilogues for the three operand sets of the hot path (plain transform, metric forward
-    // `* weight`, metric adjoint `* field + add, dot`) on rows of 512..2048 scalars; NB2_ROWS_SPEC=0: generic
+    // `* weight`, metric adjoint `* field + add, dot`) on rows of 512..2048 scalars
     int mask = -1;
     if (logm >= 8 && logm <= 10) {
         if (!epi) {
@@ -305,14 +201,11 @@ int run_rows_part(nb2_plan* pl, const void* in, void* out, int conv, const nb2_p
             mask = (epi->amp_mode == 2 ? 1 : 0) | (epi->mul ? 2 : 0) | (epi->add ? 4 : 0) | (epi->dot ? 8 : 0);
         }
         if (mask != 0 && mask != 2 && mask != 13) mask = -1;
-        if (const char* e = std::getenv("NB2_ROWS_SPEC"))
-            if (e[0] == '0') mask = -1;
     }
 #define NB2_ROWS_MASKS(A, B, C)                                                  \
     if (mask == 0) NB2_RUN_ROWS_E(A, B, C, 0)                                    \
     else if (mask == 2) NB2_RUN_ROWS_E(A, B, C, 2)                               \
     else NB2_RUN_ROWS_E(A, B, C, 13)
-    const char* alt = std::getenv("NB2_PLAN9");
     if constexpr (PART == 0) {
         switch (logm) {
             case 1: NB2_RUN_ROWS(2, 1, 1) break;
@@ -325,16 +218,10 @@ int run_rows_part(nb2_plan* pl, const void* in, void* out, int conv, const nb2_p
             default: rc = NB2_ERR_UNSUPPORTED; break;
         }
     } else if constexpr (PART == 1) {
-        if (mask >= 0 && !(logm == 9 && alt)) {
+        if (mask >= 0) {
             if (logm == 8) { NB2_ROWS_MASKS(16, 1, 16) }
             else if (logm == 9) { NB2_ROWS_MASKS(32, 1, 16) }
             else { NB2_ROWS_MASKS(32, 1, 32) }
-        } else if (logm == 9 && alt && alt[0] == 'a') {
-            NB2_RUN_ROWS(16, 2, 16)
-        } else if (logm == 9 && alt && alt[0] == 'b') {
-            NB2_RUN_ROWS(8, 8, 8)
-        } else if (logm == 9 && alt && alt[0] == 'c') {
-            NB2_RUN_ROWS(16, 1, 32)
         } else {
             switch (logm) {
                 case 8: NB2_RUN_ROWS(16, 1, 16) break;
@@ -355,7 +242,7 @@ int run_rows_part(nb2_plan* pl, const void* in, void* out, int conv, const nb2_p
 #undef NB2_RUN_ROWS_E
 #undef NB2_RUN_ROWS
     if (rc) return rc;
-    if (want_dot && (!grp || grp->reduce)) {
+    if (want_dot) {
         rc = launch_final_reduce(pl->partials, grid, 1, epi->dot_out, st);
     }
     return rc;

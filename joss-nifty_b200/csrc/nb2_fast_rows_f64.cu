@@ -1,12 +1,8 @@
 #include "nb2_fast_impl.cuh"
 namespace nb2 {
-extern template int run_rows_part<double, 1>(nb2_plan*, const void*, void*, int, const nb2_pointop*, const nb2_pointop*, rt_stream,
-                               const RowGroup*);
-extern template int run_rows_part<double, 2>(nb2_plan*, const void*, void*, int, const nb2_pointop*, const nb2_pointop*, rt_stream,
-                               const RowGroup*);
-template int run_rows_part<double, 0>(nb2_plan*, const void*, void*, int, const nb2_pointop*, const nb2_pointop*, rt_stream,
-                               const RowGroup*);
-template int run_rows<double>(nb2_plan*, const void*, void*, int, const nb2_pointop*, const nb2_pointop*, rt_stream,
-                               const RowGroup*);
+extern template int run_rows_part<double, 1>(nb2_plan*, const void*, void*, int, const nb2_pointop*, const nb2_pointop*, rt_stream);
+extern template int run_rows_part<double, 2>(nb2_plan*, const void*, void*, int, const nb2_pointop*, const nb2_pointop*, rt_stream);
+template int run_rows_part<double, 0>(nb2_plan*, const void*, void*, int, const nb2_pointop*, const nb2_pointop*, rt_stream);
+template int run_rows<double>(nb2_plan*, const void*, void*, int, const nb2_pointop*, const nb2_pointop*, rt_stream);
 template int rows_pairs_per_cta<double>(const nb2_plan*);
 }

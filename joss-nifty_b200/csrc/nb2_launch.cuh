@@ -66,98 +66,27 @@ struct PhaseStep<K, PH, false> {
     __device__ __forceinline__ static void run(const typename K::Params&, char*, bool) {}
 };
 
+// `gate`: device-resident conjugate gradient (nb2_cg_* in nb2_capi.cu).  While the solver's state says
+// "stopped" (*gate != 0) every kernel of an iteration that was launched ahead returns at once, so the
+// host may enqueue iterations without waiting for the stopping decision of the previous one.
 template <class K>
-__global__ void __launch_bounds__(K::MAX_THREADS, K::MIN_BLOCKS) nb2_kernel(const typename K::Params p) {
+__global__ void __launch_bounds__(K::MAX_THREADS, K::MIN_BLOCKS) nb2_kernel(const typename K::Params p, const int* gate) {
     extern __shared__ __align__(16) char nb2_smem[];
+    if (gate != nullptr && *gate != 0) return;
     PhaseStep<K, 0>::run(p, nb2_smem, true);
 }
 
-// Persistent, software-pipelined variant: each CTA walks the tiles blockIdx.x, blockIdx.x + gridDim.x,
-// ... ; K::prefetch issues the asynchronous copies (cp.async) of a tile's input into one of
-// STAGES shared-memory stage buffers, STAGES-1 tiles ahead of the tile whose phases are running.
-template <class K, int PH, bool IN_RANGE = (PH < K::NPHASES)>
-struct PipeStep {
-    __device__ __forceinline__ static void run(const typename K::Params& p, long long tile, char* smem) {
-        if (K::enabled(PH)) {
-            if (PH != 0) __syncthreads();
-            K::template phase<PH>(p, tile, (int)threadIdx.x, (int)blockDim.x, smem);
-        }
-        PipeStep<K, PH + 1>::run(p, tile, smem);
-    }
-};
-template <class K, int PH>
-struct PipeStep<K, PH, false> {
-    __device__ __forceinline__ static void run(const typename K::Params&, long long, char*) {}
-};
-
-template <class K, int STAGES>
-__global__ void __launch_bounds__(K::MAX_THREADS, K::MIN_BLOCKS)
-    nb2_kernel_pipe(const typename K::Params p, long long ntiles, unsigned stage_bytes) {
-    extern __shared__ __align__(16) char nb2_smem[];
-    const int tid = (int)threadIdx.x, nt = (int)blockDim.x;
-    long long t = blockIdx.x;
-    NB2_UNROLL
-    for (int s = 0; s < STAGES - 1; ++s) {
-        const long long tt = t + (long long)s * gridDim.x;
-        if (tt < ntiles) K::prefetch(p, tt, tid, nt, nb2_smem + (size_t)s * stage_bytes);
-        cp_async_commit();
-    }
-    int st = 0;
-    for (; t < ntiles; t += gridDim.x) {
-        const long long tn = t + (long long)(STAGES - 1) * gridDim.x;
-        const int sn = st == 0 ? STAGES - 1 : st - 1;   // the stage the previous tile has just left
-        if (tn < ntiles) K::prefetch(p, tn, tid, nt, nb2_smem + (size_t)sn * stage_bytes);
-        cp_async_commit();
-        cp_async_wait<STAGES - 1>();
-        __syncthreads();
-        PipeStep<K, 0>::run(p, t, nb2_smem + (size_t)st * stage_bytes);
-        __syncthreads();
-        st = st + 1 == STAGES ? 0 : st + 1;
-    }
+// gate handed to every launch of the calling thread (nullptr: none)
+inline const int*& launch_gate() {
+    static thread_local const int* g = nullptr;
+    return g;
 }
-
-template <class K, int STAGES>
-inline int rt_launch_pipe_n(long long ntiles, long long grid, int nthreads, size_t stage_bytes, rt_stream stream,
-                            const typename K::Params& p) {
-    const size_t smem = stage_bytes * STAGES;
-    static thread_local size_t configured = 0;  // per kernel instantiation
-    if (smem > 48 * 1024 && smem > configured) {
-        NB2_CUDA_OK(cudaFuncSetAttribute(nb2_kernel_pipe<K, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
-    if (grid <= 0) {  // as many CTAs as can be resident at once
-        static thread_local int per_sm = 0, per_sm_threads = 0;
-        static thread_local size_t per_sm_smem = 0;
-        if (per_sm == 0 || per_sm_threads != nthreads || per_sm_smem != smem) {
-            NB2_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb2_kernel_pipe<K, STAGES>, nthreads, smem));
-            per_sm_threads = nthreads;
-            per_sm_smem = smem;
-            if (per_sm < 1) per_sm = 1;
-        }
-        int cap = per_sm;
-        if (const char* e = std::getenv("NB2_PIPE_CTAS")) cap = std::max(1, std::min(per_sm, std::atoi(e)));
-        grid = (long long)cap * rt_sm_count();
-    }
-    if (grid > ntiles) grid = ntiles;
-    nb2_kernel_pipe<K, STAGES><<<(unsigned)grid, nthreads, smem, stream>>>(p, ntiles, (unsigned)stage_bytes);
-    NB2_CUDA_OK(cudaGetLastError());
-    ++launch_counter();
-    return 0;
+inline int rt_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return dev;
 }
-template <class K>
-inline int rt_launch_pipe(long long ntiles, long long grid, int nthreads, size_t stage_bytes, int stages, rt_stream stream,
-                          const typename K::Params& p) {
-    if (ntiles <= 0) return 0;
-    if (stage_bytes % 16) {
-        last_error() = "stage size must be a multiple of 16 bytes";
-        return -1;
-    }
-    switch (stages) {
-        case 2: return rt_launch_pipe_n<K, 2>(ntiles, grid, nthreads, stage_bytes, stream, p);
-        case 3: return rt_launch_pipe_n<K, 3>(ntiles, grid, nthreads, stage_bytes, stream, p);
-        default: last_error() = "unsupported number of pipeline stages"; return -1;
-    }
-}
+constexpr int kMaxDevices = 64;
 
 template <class K>
 inline int rt_launch(long long grid, int nthreads, size_t smem, rt_stream stream, const typename K::Params& p) {
@@ -167,13 +96,14 @@ inline int rt_launch(long long grid, int nthreads, size_t smem, rt_stream stream
         return -1;
     }
     if (smem > 48 * 1024) {
-        static thread_local size_t configured = 0;  // per kernel instantiation
-        if (smem > configured) {
+        static size_t configured[kMaxDevices] = {0};  // per kernel instantiation and device
+        size_t& c = configured[rt_device() % kMaxDevices];
+        if (smem > c) {
             NB2_CUDA_OK(cudaFuncSetAttribute(nb2_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = smem;
+            c = smem;
         }
     }
-    nb2_kernel<K><<<(unsigned)grid, nthreads, smem, stream>>>(p);
+    nb2_kernel<K><<<(unsigned)grid, nthreads, smem, stream>>>(p, launch_gate());
     NB2_CUDA_OK(cudaGetLastError());
     ++launch_counter();
     return 0;
@@ -250,14 +180,25 @@ inline int rt_ipc_close(void* p) {
     return 0;
 }
 inline int rt_sm_count() {
-    int dev = 0, n = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    static int cached[kMaxDevices] = {0};
+    int& n = cached[rt_device() % kMaxDevices];
+    if (n == 0) {
+        int v = 148;
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, rt_device());
+        n = v;
+    }
     return n;
 }
 
 #else
 // ------------------------------------------------------------------ sequential emulator (tests only)
 typedef void* rt_stream;
+inline const int*& launch_gate() {
+    static thread_local const int* g = nullptr;
+    return g;
+}
+inline int rt_device() { return 0; }
+constexpr int kMaxDevices = 64;
 
 template <class K, int PH, bool IN_RANGE = (PH < K::NPHASES)>
 struct EmuStep {
@@ -274,27 +215,16 @@ struct EmuStep<K, PH, false> {
 
 template <class K>
 inline int rt_launch(long long grid, int nthreads, size_t smem, rt_stream, const typename K::Params& p) {
+    if (launch_gate() != nullptr && *launch_gate() != 0) {
+        ++launch_counter();
+        return 0;
+    }
     std::vector<char> buf(smem + 64);
     char* base = buf.data();
     base += (64 - (reinterpret_cast<uintptr_t>(base) & 63)) & 63;
     for (long long bid = 0; bid < grid; ++bid) {
         std::memset(base, 0xAB, smem);  // poison: catches reads of unwritten shared memory
         EmuStep<K, 0>::run(p, bid, nthreads, base);
-    }
-    ++launch_counter();
-    return 0;
-}
-// pipelined kernels: the emulator runs prefetch (plain copies) and then the phases, tile by tile
-template <class K>
-inline int rt_launch_pipe(long long ntiles, long long, int nthreads, size_t stage_bytes, int, rt_stream,
-                          const typename K::Params& p) {
-    std::vector<char> buf(stage_bytes + 64);
-    char* base = buf.data();
-    base += (64 - (reinterpret_cast<uintptr_t>(base) & 63)) & 63;
-    for (long long tile = 0; tile < ntiles; ++tile) {
-        std::memset(base, 0xAB, stage_bytes);
-        for (int tid = 0; tid < nthreads; ++tid) K::prefetch(p, tile, tid, nthreads, base);
-        EmuStep<K, 0>::run(p, tile, nthreads, base);
     }
     ++launch_counter();
     return 0;

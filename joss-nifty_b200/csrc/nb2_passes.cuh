@@ -118,15 +118,6 @@ struct StridedPass {
         const long long* out_coloff;
         long long in_ostride, out_ostride, col0, run_stride;
         int logrun;
-        // L2-blocked tail (hartley_fast): the launch covers a GROUP of planes -- local plane o is
-        // the natural plane  o < grp_lo_n ? grp_lo_a + o : grp_hi_a + (o - grp_lo_n)  of the input
-        // and plane o of the (small, L2-resident) output buffer.  keep_out: store with the default
-        // cache policy instead of evict-first so that the next kernel finds the tile in L2.
-        int grp_on, keep_out;
-        long long grp_lo_a, grp_lo_n, grp_hi_a;
-        // pipelined launch (nb2_kernel_pipe): the tile -- and, with pro_staged, the amplitude
-        // field tile behind it -- has been copied into the stage buffer by prefetch()
-        int staged, pro_staged;
     };
 
     static size_t smem_bytes(int logw) {
@@ -134,10 +125,9 @@ struct StridedPass {
     }
     NB2_HDC static bool enabled(int ph) { return ph == 0 || (ph == 1 && R2 > 1) || (ph == 2 && R3 > 1); }
 
-    NB2_HD static long long tile_base(const Params& p, long long bid, bool local = false) {
-        long long o = bid / p.tiles_per_outer;
+    NB2_HD static long long tile_base(const Params& p, long long bid) {
+        const long long o = bid / p.tiles_per_outer;
         const long long tile = bid - o * p.tiles_per_outer;
-        if (p.grp_on && !local) o = o < p.grp_lo_n ? p.grp_lo_a + o : p.grp_hi_a + (o - p.grp_lo_n);
         const long long tc = tile << p.logw;
         return o * N * p.inner + p.col0 + (tc >> p.logrun) * p.run_stride + (tc & ((1ll << p.logrun) - 1));
     }
@@ -146,32 +136,7 @@ struct StridedPass {
         const long long cc = p.out_coloff ? ld_ro(p.out_coloff + (tcol >> p.g.logM)) + (tcol & ((1ll << p.g.logM) - 1)) : tcol;
         return oo + cc;
     }
-    NB2_HD static void store_out(const Params& p, cplx<T>* dst, cplx<T> v) {
-        if (p.keep_out) stc_keep(dst, v);
-        else stc_stream(dst, v);
-    }
-
-    // asynchronous copy of tile `bid` into a stage buffer, in the padded slot layout phase 0 works in
-    NB2_HD static void prefetch(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
-        cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
-        constexpr int CH = 16 / sizeof(cplx<T>) > 0 ? 16 / sizeof(cplx<T>) : 1;   // elements per 16-byte copy
-        const int logcpr = p.logw - (CH == 2 ? 1 : 0);                              // log2(copies per row)
-        const long long base = tile_base(p, bid);
-        const long long tcol = (bid % p.tiles_per_outer) << p.logw;
-        const cplx<T>* src0 = p.in_rowoff ? p.in + (bid / p.tiles_per_outer) * p.in_ostride + tcol : p.in + base;
-        const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
-        const long long tile_elems = (long long)TPITCH << p.logw;
-        const int total = N << logcpr;
-        for (int i = tid; i < total; i += nthreads) {
-            const int row = i >> logcpr, cc = (i & ((1 << logcpr) - 1)) * CH;
-            const long long roff = p.in_rowoff ? ld_ro(p.in_rowoff + row) : (long long)row * p.inner;
-            cplx<T>* dst = smem + (slot_of<R2, R3>(row) << p.logw) + cc;
-            cp_async<16>(dst, src0 + roff + cc);
-            if (p.pro_staged)
-                cp_async<16>(dst + tile_elems, reinterpret_cast<const cplx<T>*>(p.pro.amp) +
-                                                   ((base + (long long)row * p.inner + cc) & itemmask));
-        }
-    }
+    NB2_HD static void store_out(const Params&, cplx<T>* dst, cplx<T> v) { stc_stream(dst, v); }
 
     template <int PH>
     NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
@@ -179,17 +144,13 @@ struct StridedPass {
         const int w = 1 << p.logw;
         const long long base = tile_base(p, bid);
         const long long tcol = (bid % p.tiles_per_outer) << p.logw;
-        const long long obase = p.out_rowoff ? out_origin(p, bid / p.tiles_per_outer, tcol)
-                                             : (p.grp_on ? tile_base(p, bid, true) : base);
+        const long long obase = p.out_rowoff ? out_origin(p, bid / p.tiles_per_outer, tcol) : base;
         if (PH == 0) {
             const int nb = MM << p.logw;
             for (int b = tid; b < nb; b += nthreads) {
                 const int c = b & (w - 1), r = b >> p.logw;
                 cplx<T> x[R1];
-                if (p.staged) {
-                    NB2_UNROLL
-                    for (int n1 = 0; n1 < R1; ++n1) x[n1] = smem[(slot_of<R2, R3>(r + n1 * MM) << p.logw) + c];
-                } else if (p.in_rowoff) {
+                if (p.in_rowoff) {
                     const cplx<T>* src = p.in + (bid / p.tiles_per_outer) * p.in_ostride + tcol + c;
                     const long long* ro = p.in_rowoff + r;
                     NB2_UNROLL
@@ -217,15 +178,7 @@ struct StridedPass {
                     // so that their latency overlaps instead of serialising per row
                     constexpr int PB = R1 >= 8 ? 8 : R1;
                     constexpr int NBATCH = R1 / PB;
-                    if (p.pro.amp_mode == 2 && p.pro_staged) {
-                        const cplx<T>* fs = smem + ((long long)TPITCH << p.logw);
-                        NB2_UNROLL
-                        for (int n1 = 0; n1 < R1; ++n1) {
-                            const cplx<T> f = fs[(slot_of<R2, R3>(r + n1 * MM) << p.logw) + c];
-                            x[n1].re *= f.re * p.pro.scale;
-                            x[n1].im *= f.im * p.pro.scale;
-                        }
-                    } else if (p.pro.amp_mode == 2) {
+                    if (p.pro.amp_mode == 2) {
                         const long long itemmask = (1ll << (p.g.logN0 + p.g.logN1 + p.g.logM)) - 1;
                         const FieldRows<T> fr(reinterpret_cast<const cplx<T>*>(p.pro.amp) + ((base + c) & itemmask), p.inner,
                                               N, p.pro.amp_sym && !(p.axis == 0 ? p.g.shift0 : p.g.shift1));
@@ -403,22 +356,11 @@ struct RowPass {
         int has_pro;
         PointOp<T> pro;
         PointOp<T> epi;
-        int staged;   // pipelined launch: prefetch() has copied the rows into the stage buffer
-        // L2-blocked tail: this launch covers the mirror pairs [bid0 * G, q_end) and reads its
-        // rows from a group buffer in which natural plane k0 is plane
-        //   k0 < grp_hi_a ? k0 - grp_lo_a : grp_lo_n + (k0 - grp_hi_a)
-        long long bid0, q_end;
-        // L2 prefetch distance in CTAs (0: off): CTA b asks for the rows -- input and streamed epilogue
-        // operands -- of CTA b + la, which becomes resident about when this one retires
-        long long la, bid_end;
-        int grp_on;
-        long long grp_lo_a, grp_lo_n, grp_hi_a;
     };
 
     // per-slot data computed once per tile (phase 0) and reused by the untangle phase
     struct SlotCache {
         long long row;  // linear row index over (batch, N0, N1)
-        long long in_row;  // row index in the input buffer (differs from `row` for group buffers)
         long long frow;    // row (inside one item) whose amplitude-field values this slot uses
         int f01;        // ksq contribution of (k0, k1)
         int flags;      // bit 0: valid, bit 1: duplicate of its partner (self-mirrored row)
@@ -441,7 +383,7 @@ struct RowPass {
         const long long q = (bid - item * p.ctas_per_item) * p.G + (s >> 1);
         const long long N0 = 1ll << p.g.logN0, N1 = 1ll << p.g.logN1;
         RowSlot rs;
-        rs.valid = q < rp.Q && q < p.q_end;
+        rs.valid = q < rp.Q;
         rs.dup = false;
         rs.k0 = rs.k1 = rs.row = 0;
         if (!rs.valid) return rs;
@@ -471,23 +413,6 @@ struct RowPass {
     static constexpr int KS1 = MM + R2 + (R2 > 1 ? 1 : 0);   // slot stride of k1 (consecutive k)
     NB2_HD static int slot_of_k(int k) {
         return (k & (R1 - 1)) * KS1 + ((k / R1) & (R2 - 1)) * (R3 + 1) + k / (R1 * R2);
-    }
-
-    // asynchronous copy of the 2G rows of tile `bid` into a stage buffer (padded slot layout)
-    NB2_HD static void prefetch(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
-        cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
-        const int total = 2 * p.G * M;
-        int prev_s = -1;
-        RowSlot rs{};
-        for (int i = tid; i < total; i += nthreads) {
-            const int s = i / M, L = i % M;
-            if (s != prev_s) {
-                rs = slot_info(p, bid, s);
-                prev_s = s;
-            }
-            if (!rs.valid) continue;
-            cp_async<(int)sizeof(cplx<T>)>(smem + s * PITCH + slot_of<R2, R3>(L), p.in + rs.row * M + L);
-        }
     }
 
     template <typename OP>
@@ -555,16 +480,12 @@ struct RowPass {
         cplx<T>* smem = reinterpret_cast<cplx<T>*>(smem_raw);
         double* red = reinterpret_cast<double*>(smem_raw + size_t(2 * p.G) * PITCH * sizeof(cplx<T>));
         const int nslots = 2 * p.G;
-        bid += p.bid0;
         if (PH == 0) {
             // row bookkeeping of the tile, once per slot
             for (int s = tid; s < nslots; s += nthreads) {
                 const RowSlot rs = slot_info(p, bid, s);
                 SlotCache sc;
                 sc.row = rs.row;
-                sc.in_row = !p.grp_on ? rs.row
-                                      : (((rs.k0 < p.grp_hi_a ? rs.k0 - p.grp_lo_a : p.grp_lo_n + (rs.k0 - p.grp_hi_a))
-                                          << p.g.logN1) + rs.k1);
                 sc.f01 = int(sq_mirror(rs.k0, p.g.logN0) + sq_mirror(rs.k1, p.g.logN1));
                 {
                     // NB2_AMP_SYMMETRIC: the field rows (+-k0, +-k1) are equal -- every one of them reads
@@ -579,19 +500,6 @@ struct RowPass {
                 }
                 sc.flags = (rs.valid ? 1 : 0) | (rs.dup ? 2 : 0);
                 slot_cache(p, smem_raw, nthreads)[s] = sc;
-                if (p.la > 0 && bid + p.la < p.bid_end) {
-                    const RowSlot rf = slot_info(p, bid + p.la, s);
-                    if (rf.valid && !rf.dup) {
-                        const unsigned rb = unsigned(M * sizeof(cplx<T>));
-                        prefetch_l2(p.in + rf.row * M, rb);
-                        if (p.epi.mul) prefetch_l2(p.epi.mul + rf.row * (2 * M), rb);
-                        if (p.epi.add) prefetch_l2(p.epi.add + rf.row * (2 * M), rb);
-                        if (p.epi.dot && p.epi.dot != p.epi.add) prefetch_l2(p.epi.dot + rf.row * (2 * M), rb);
-                        if (p.epi.bin_x) prefetch_l2(p.epi.bin_x + rf.row * (2 * M), rb);
-                        if (p.epi.amp_mode == 2 && !p.epi.amp_sym)
-                            prefetch_l2(p.epi.amp + (rf.row & ((1ll << (p.g.logN0 + p.g.logN1)) - 1)) * (2 * M), rb);
-                    }
-                }
             }
         } else if (PH == 1) {
             const int nb = nslots * MM;
@@ -601,19 +509,10 @@ struct RowPass {
                 const SlotCache sc = cache[s];
                 if (!(sc.flags & 1)) continue;
                 cplx<T> x[R1];
-                if (p.staged) {
-                    const cplx<T>* src = smem + s * PITCH;
+                {
+                    const cplx<T>* src = p.in + sc.row * M + r;
                     NB2_UNROLL
-                    for (int n1 = 0; n1 < R1; ++n1) x[n1] = src[slot_of<R2, R3>(r + n1 * MM)];
-                } else {
-                    const cplx<T>* src = p.in + sc.in_row * M + r;
-                    if (p.grp_on) {
-                        NB2_UNROLL
-                        for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_keep(src + n1 * MM);
-                    } else {
-                        NB2_UNROLL
-                        for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + n1 * MM);
-                    }
+                    for (int n1 = 0; n1 < R1; ++n1) x[n1] = ldc_stream(src + n1 * MM);
                 }
                 if (p.has_pro) {
                     const long long N0N1 = 1ll << (p.g.logN0 + p.g.logN1);

@@ -29,12 +29,8 @@ struct nb2_plan {
     void* twr = nullptr;  // row table (N2 entries)
     double* partials = nullptr;
     long long npartials = 0;
-    void* l2buf = nullptr;  // group buffers of the L2-blocked tail (one per auxiliary stream)
-    size_t l2buf_bytes = 0;
-    static constexpr int kMaxAux = 4;
-    nb2::rt_stream aux[kMaxAux] = {};
-    nb2::rt_event ev_fork = nullptr, ev_join[kMaxAux] = {};
-    int naux = 0;
+    // developer knobs, read from the environment once at plan creation (never on the dispatch path)
+    bool knob_tma = true, knob_tma_scatter = false, knob_tma_fx = true;
     // generic path
     void* roots[nb2::kMaxDim] = {nullptr};  // cplx<double>[n] per transformed axis
     void* work0 = nullptr;
@@ -55,18 +51,6 @@ struct RowRemap {
     // column subset of the natural side: ncols dense columns (0 = every column) in runs of `run`
     // contiguous columns (0 = one run) whose starts are `run_stride` apart, the first at col0
     long long col0 = 0, ncols = 0, run = 0, run_stride = 0;
-    // plane group of the L2-blocked tail (StridedPass::Params::grp_*): grp_n planes in the launch
-    int grp_on = 0, keep_out = 0;
-    long long grp_lo_a = 0, grp_lo_n = 0, grp_hi_a = 0, grp_n = 0;
-};
-
-// Row-pass launch restricted to the mirror pairs [q0, q_end) whose input rows live in a group
-// buffer (RowPass::Params::grp_*); q0 must be a multiple of the pairs-per-CTA count G.
-struct RowGroup {
-    long long q0 = 0, q_end = 0;
-    long long lo_a = 0, lo_n = 0, hi_a = 0;
-    int G = 0;              // pairs per CTA fixed by the caller for every group of the transform
-    bool reduce = false;    // run the final reduction of the dot partials after this launch
 };
 
 struct PlanDims { int r1, r2, r3; };
@@ -100,7 +84,7 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
                 const RowRemap* rm = nullptr);
 template <typename T>
 int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
-             rt_stream st, const RowGroup* grp = nullptr);
+             rt_stream st);
 template <typename T> int rows_pairs_per_cta(const nb2_plan* pl);
 int launch_final_reduce(const double* partials, long long nparts, int nv, double* out, rt_stream st);
 

@@ -299,8 +299,10 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, v
 template <class K>
 __global__ void __launch_bounds__(K::NTHREADS, K::MIN_BLOCKS)
     nb2_kernel_tma(const __grid_constant__ CUtensorMap map, const __grid_constant__ CUtensorMap mapf,
-                   const __grid_constant__ CUtensorMap mapft, const typename K::Params p, long long ntiles) {
+                   const __grid_constant__ CUtensorMap mapft, const typename K::Params p, long long ntiles,
+                   const int* gate) {
     extern __shared__ __align__(128) char nb2_smem[];
+    if (gate != nullptr && *gate != 0) return;   // device-resident CG: the solver has stopped (nb2_launch.cuh)
     char* P = nb2_smem;
     char* X = nb2_smem + K::P_BYTES;
     void* bar = nb2_smem + K::P_BYTES + K::X_BYTES;
@@ -387,6 +389,21 @@ inline nb2_encode_tiled_fn tma_encoder() {
 // 3-D tensor map over the scalars of a complex array: (2 * inner, N, outer), box (128 bytes, box_rows, 1)
 template <class K, typename T>
 inline int tma_make_map(CUtensorMap* map, const void* in, long long inner, long long outer, int box_rows) {
+    // the CG loop re-launches the same few (buffer, geometry) pairs every iteration: keep the encoded maps
+    struct Entry {
+        const void* in;
+        long long inner, outer;
+        int box_rows;
+        CUtensorMap map;
+    };
+    constexpr int kEntries = 8;
+    static thread_local Entry cache[kEntries] = {};
+    static thread_local int next = 0;
+    for (int i = 0; i < kEntries; ++i)
+        if (cache[i].in == in && cache[i].inner == inner && cache[i].outer == outer && cache[i].box_rows == box_rows) {
+            *map = cache[i].map;
+            return 0;
+        }
     nb2_encode_tiled_fn enc = tma_encoder();
     if (!enc) {
         last_error() = "cuTensorMapEncodeTiled is not available";
@@ -403,6 +420,8 @@ inline int tma_make_map(CUtensorMap* map, const void* in, long long inner, long 
         last_error() = "cuTensorMapEncodeTiled failed (code " + std::to_string((int)r) + ")";
         return -2;
     }
+    cache[next] = Entry{in, inner, outer, box_rows, *map};
+    next = (next + 1) % kEntries;
     return 0;
 }
 
@@ -417,19 +436,17 @@ inline int rt_launch_tma(long long ntiles, long long outer, rt_stream stream, co
     } else {
         mapf = mapft = map;
     }
-    static thread_local bool configured = false;
-    if (!configured) {
-        NB2_CUDA_OK(cudaFuncSetAttribute(nb2_kernel_tma<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K::SMEM));
-        configured = true;
-    }
-    static thread_local int per_sm = 0;
+    static int per_sm_dev[kMaxDevices] = {0};   // per kernel instantiation and device; 0 = not configured yet
+    int& per_sm = per_sm_dev[rt_device() % kMaxDevices];
     if (per_sm == 0) {
-        NB2_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb2_kernel_tma<K>, K::NTHREADS, K::SMEM));
-        if (per_sm < 1) per_sm = 1;
+        NB2_CUDA_OK(cudaFuncSetAttribute(nb2_kernel_tma<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K::SMEM));
+        int v = 0;
+        NB2_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, nb2_kernel_tma<K>, K::NTHREADS, K::SMEM));
+        per_sm = v < 1 ? 1 : v;
     }
     long long grid = (long long)per_sm * rt_sm_count();
     if (grid > ntiles) grid = ntiles;
-    nb2_kernel_tma<K><<<(unsigned)grid, K::NTHREADS, K::SMEM, stream>>>(map, mapf, mapft, p, ntiles);
+    nb2_kernel_tma<K><<<(unsigned)grid, K::NTHREADS, K::SMEM, stream>>>(map, mapf, mapft, p, ntiles, launch_gate());
     NB2_CUDA_OK(cudaGetLastError());
     ++launch_counter();
     ++tma_launch_counter();
@@ -443,6 +460,10 @@ inline bool tma_available() { return tma_encoder() != nullptr; }
 // barriers of a tile are kept per emulated thread.
 template <class K, typename T>
 inline int rt_launch_tma(long long ntiles, long long, rt_stream, const typename K::Params& p) {
+    if (launch_gate() != nullptr && *launch_gate() != 0) {
+        ++launch_counter();
+        return 0;
+    }
     std::vector<char> Pbuf(K::P_BYTES), Xbuf(K::X_BYTES);
     std::vector<typename K::Regs> regs(K::NTHREADS);
     for (long long tile = 0; tile < ntiles; ++tile) {

@@ -15,7 +15,7 @@ kernel for ``d = b d + r``.  The stopping logic is evaluated on the host in fp64
 three sums, line by line as in the reference, so iteration counts and status/info codes match.
 """
 
-import time
+import datetime
 from collections import namedtuple
 
 import numpy as np
@@ -69,7 +69,8 @@ def _apply_with_curv(A, d, q, pending=None, vec=None):
     """``q = A d`` and ``d.q``.  ``pending = (s, beta)``: the deferred direction update ``d <- s + beta d``
     of the previous iteration, done inside the first pass of ``A`` when it can carry it
     (``A.fused_direction_update``), else by the axpby kernel right here."""
-    if pending is not None and not getattr(A, "fused_direction_update", False):
+    fused = getattr(A, "fused_direction_update", False) and hasattr(A, "apply_with_curvature")
+    if pending is not None and not fused:
         vec.axpby(1.0, pending[0], pending[1], d)
         pending = None
     if hasattr(A, "apply_with_curvature"):
@@ -100,12 +101,18 @@ class QuadraticEnergy:
         self.position, self._A, self._b = position, A, b
         if _grad is not None:
             self.gradient = _grad
-            Ax = _grad if b is None else _grad + b
+            Ax = None
         else:
             Ax = A(position)
             self.gradient = Ax if b is None else Ax - b
         if _value is None:
-            _value = 0.5 * float(vdot_device(position, Ax).cpu())
+            # 0.5 x.(A x) - b.x with A x = grad + b (quadratic_energy.py:32-37); no N-sized temporary
+            if Ax is not None:
+                _value = 0.5 * float(vdot_device(position, Ax).cpu())
+            else:
+                _value = 0.5 * float(vdot_device(position, _grad).cpu())
+                if b is not None:
+                    _value += 0.5 * float(vdot_device(position, b).cpu())
             if b is not None:
                 _value -= float(vdot_device(b, position).cpu())
         self.value = _value
@@ -226,8 +233,9 @@ class ConjugateGradient:
         if previous_gamma == 0:
             return energy, CONVERGED
 
-        def mk_energy(value, gamma_rr):
-            return QuadraticEnergy(x, A, energy._b, _grad=r, _value=value, _gradnorm=float(np.sqrt(gamma_rr)))
+        def mk_energy(view):
+            # materialised on return only; x and r are buffers owned by this call
+            return QuadraticEnergy(x, A, energy._b, _grad=r, _value=view.value, _gradnorm=view.gradient_norm)
 
         ii = 0
         pending = None    # deferred direction update (s, beta): done with the next A d
@@ -249,19 +257,19 @@ class ConjugateGradient:
                 rr, xr, xb = vec.update(1, 0.0, d, q, b, x, r)
                 ii = 0
             value = 0.5 * (xr + xb) - xb                               # quadratic_energy.py:35-37
-            energy = mk_energy(value, rr)
+            view = _EnergyView(value, float(np.sqrt(rr)))              # what the controller looks at
             if preconditioner is None:
                 s, gamma = r, rr
             else:
                 s = preconditioner(r)
                 gamma = float(vdot_device(r, s).cpu())
             if np.isnan(gamma) or gamma < 0:                           # :110-115
-                return energy, ERROR
+                return mk_energy(view), ERROR
             if gamma == 0:
-                return energy, CONVERGED
-            status = controller.check(energy)                          # :120
+                return mk_energy(view), CONVERGED
+            status = controller.check(view)                            # :120
             if status != CONTINUE:
-                return energy, status
+                return mk_energy(view), status
             pending = (s, max(0.0, gamma / previous_gamma))            # :124, applied with the next A d
             previous_gamma = gamma
 
@@ -277,19 +285,44 @@ def _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord, tol, atol, comm=
     miniter = min(6, maxiter if maxiter is not None else maxiter_fallback) if miniter is None else miniter
     maxiter = max(min(200, maxiter_fallback), miniter) if maxiter is None else maxiter
     if absdelta is None and resnorm is None:
-        if comm is not None and norm_ord == 2:
-            jn = float(np.sqrt(_dot(j, j, comm)))
-        else:
-            jn = float(torch.linalg.vector_norm(j.reshape(-1).double(), ord=norm_ord).cpu())
-        resnorm = max(tol * jn, atol)
+        resnorm = max(tol * _norm(j, None, norm_ord, comm), atol)
     fi = np.finfo(np.float32 if j.dtype == torch.float32 else np.float64)
     return norm_ord, miniter, maxiter, resnorm, 6.0 * fi.eps, 6.0 * fi.tiny
 
 
-def _norm(r, rr, norm_ord):
+def _norm(r, rr, norm_ord, comm=None):
+    """``jft.norm(r, ord)`` (re/tree_math/vector_math.py:176-192); ``rr`` = r.r when already known.  On a
+    slab-decomposed vector every rank gets the GLOBAL norm (all ranks must take the same stopping decision)."""
     if norm_ord == 2:
-        return float(np.sqrt(rr))
-    return float(torch.linalg.vector_norm(r.reshape(-1).double(), ord=norm_ord).cpu())
+        return float(np.sqrt(rr if rr is not None else _dot(r, r, comm)))
+    if comm is None:
+        return float(torch.linalg.vector_norm(r.reshape(-1).double(), ord=norm_ord).cpu())
+    a = r.reshape(-1).double().abs()
+    if norm_ord == np.inf:
+        t = a.max().reshape(1)
+        comm.allreduce_max_(t)
+        return float(t.cpu())
+    if norm_ord == -np.inf:
+        t = (-a.min()).reshape(1)
+        comm.allreduce_max_(t)
+        return -float(t.cpu())
+    t = ((a != 0).sum().double() if norm_ord == 0 else (a ** norm_ord).sum()).reshape(1)
+    comm.allreduce_(t)
+    return float(t.cpu()) if norm_ord == 0 else float(t.cpu()) ** (1.0 / norm_ord)
+
+
+def _timed_out(time_threshold, comm=None):
+    """``datetime.now() > time_threshold`` (re/conjugate_gradient.py:176); a float is read as a
+    ``time.time()`` stamp.  Slab-decomposed solves take rank 0's decision (one broadcast)."""
+    if time_threshold is None:
+        return False
+    if isinstance(time_threshold, datetime.datetime):
+        out = datetime.datetime.now() > time_threshold
+    else:
+        out = datetime.datetime.now().timestamp() > float(time_threshold)
+    if comm is not None:
+        out = comm.broadcast_flag(out)
+    return out
 
 
 def _cg_setup(mat, j, x0):
@@ -358,14 +391,14 @@ def _cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5
             gamma, xr, xb = vec.update(1, 0.0, d, q, j, pos, r)
         else:                                                          # :169,174
             gamma, xr, xb = vec.update(0, alpha, d, q, j, pos, r)
-        if time_threshold is not None and time.time() > time_threshold:  # :176-178
+        if _timed_out(time_threshold, vec.comm):                       # :176-178
             info = i
             break
         if gamma >= 0.0 and gamma <= tiny:                             # :179-183
             info = 0
             break
         if resnorm is not None:                                        # :184-188
-            if _norm(r, gamma, norm_ord) < resnorm and i >= miniter:
+            if _norm(r, gamma, norm_ord, vec.comm) < resnorm and i >= miniter:
                 info = 0
                 break
         new_energy = 0.5 * (xr - xb)                                   # :191
@@ -425,7 +458,7 @@ def _static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, t
         if gamma >= 0.0 and gamma <= tiny and info != -1:              # :292-294
             info = 0
         if resnorm is not None:                                        # :295-301
-            if _norm(r, gamma, norm_ord) < resnorm and i >= miniter and info != -1:
+            if _norm(r, gamma, norm_ord, vec.comm) < resnorm and i >= miniter and info != -1:
                 info = 0
         energy = 0.5 * (xr - xb)                                       # :303
         energy_diff = previous_energy - energy

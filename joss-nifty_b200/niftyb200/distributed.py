@@ -63,6 +63,16 @@ class Comm:
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return t
 
+    def allreduce_max_(self, t):
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return t
+
+    def broadcast_flag(self, flag):
+        """Rank 0's boolean, on every rank (stopping decisions that depend on a local clock)."""
+        t = torch.tensor([1.0 if flag else 0.0], dtype=torch.float32, device=_device())
+        dist.broadcast(t, src=dist.get_global_rank(self.group, 0) if self.group is not None else 0, group=self.group)
+        return bool(t.item() != 0.0)
+
     def all_to_all(self, recv, send, async_op=False):
         """Returns the work handle when ``async_op`` (the caller ``wait()``s before reading)."""
         return dist.all_to_all_single(recv, send, group=self.group, async_op=async_op)

@@ -39,6 +39,12 @@ def host(t):
     return t.detach().cpu().numpy()
 
 
+def clear_plans():
+    """Developer knobs (NB2_TMA...) are read when a plan is created: drop the cached plans after changing one."""
+    from niftyb200 import transforms
+    transforms._plan_cache.clear()
+
+
 # ---------------------------------------------------------------- transforms
 def check_hartley_golden(golden):
     """ducc_dispatch.hartley/fftn/ifftn drop-ins == golden vectors made by the reference."""

@@ -73,31 +73,6 @@ def test_cg_failure_modes():
     pc.check_cg_failure_modes()
 
 
-@pytest.mark.parametrize("stages", ["2", "3"])
-def test_pipelined_passes(monkeypatch, stages):
-    # narrow tiles -> many tiles per pass -> the persistent, software-pipelined launch
-    # (prefetch into stage buffers + staged phase 0), incl. the prefetched amplitude field
-    monkeypatch.setenv("NB2_STRIDED_LOGW", "1")
-    monkeypatch.setenv("NB2_ROWS_G", "1")
-    monkeypatch.setenv("NB2_STAGES", stages)
-    monkeypatch.setenv("NB2_PIPE", "1")
-    pc.check_hartley_shapes([((64, 16), None), ((16, 64, 8), None), ((64, 2, 128), None)])
-    pc.check_metric((64, 64), 1 / 64)
-    pc.check_metric((16, 32, 16), (1 / 16, 1 / 32, 1 / 16), np.float32)
-
-
-@pytest.mark.parametrize("planes", ["2", "4", "6", "64"])
-def test_l2_blocked_tail(monkeypatch, planes):
-    # axis-1 pass + row pass run group by group (planes k0 and N0 - k0) through the group buffer
-    monkeypatch.setenv("NB2_L2_PLANES", planes)
-    pc.check_hartley_shapes([((4, 32, 8), None), ((8, 32, 16), None), ((16, 64, 4), None), ((32, 32, 32), None)])
-    pc.check_inplace_and_roundtrip((8, 32, 16))
-    pc.check_cf_vs_oracle((16, 32, 16), 1 / 16, np.float64, None)
-    pc.check_cf_vs_oracle((16, 32, 16), (1 / 16, 1 / 32, 1 / 16), np.float32, None)
-    pc.check_metric((16, 32, 16), (1 / 16, 1 / 32, 1 / 16))
-    pc.check_metric((8, 64, 8), (1 / 8, 1 / 64, 1 / 8), np.float32)
-
-
 def test_tma_strided_pass(emu, monkeypatch):
     # persistent TMA-fed strided pass (nb2_tma.cuh): 256..1024 rows, 128-byte tiles, both precisions,
     # with the fused amplitude prologues; NB2_TMA=0 must give the same answers through StridedPass
@@ -115,6 +90,7 @@ def test_tma_strided_pass(emu, monkeypatch):
     assert emu.nb2_tma_launch_count() > n0
     n0 = emu.nb2_tma_launch_count()
     monkeypatch.setenv("NB2_TMA", "0")
+    pc.clear_plans()
     pc.check_hartley_shapes(shapes[:2])
     assert emu.nb2_tma_launch_count() == n0
 
@@ -122,11 +98,13 @@ def test_tma_strided_pass(emu, monkeypatch):
 def test_strided_scatter(emu, monkeypatch):
     pc.check_strided_scatter(np.float32)            # default: StridedPass with the scatter tables
     monkeypatch.setenv("NB2_TMA_SCATTER", "1")
+    pc.clear_plans()
     n0 = emu.nb2_tma_launch_count()
     pc.check_strided_scatter(np.float32)
     pc.check_strided_scatter(np.float64)
     assert emu.nb2_tma_launch_count() > n0          # the 256/512-row cases go through the TMA kernel
     monkeypatch.setenv("NB2_TMA", "0")
+    pc.clear_plans()
     pc.check_strided_scatter(np.float32)
 
 
@@ -139,16 +117,14 @@ def test_fused_direction_update(shape, dist):
     pc.check_fused_direction_update(shape, dist, np.float32)
 
 
-def test_row_pass_compile_time_epilogues(monkeypatch):
+def test_row_pass_compile_time_epilogues():
     # rows of 512 / 1024 / 2048 scalars take the RowPass instantiations with compile-time epilogues
-    # (plain, * weight, * field + add + dot); NB2_ROWS_SPEC=0 must give the same answers generically
-    for spec in ("1", "0"):
-        monkeypatch.setenv("NB2_ROWS_SPEC", spec)
-        pc.check_hartley_shapes([((512,), None), ((4, 1024), None), ((2, 2, 2048), None)])
-        pc.check_metric((8, 512), (1 / 8, 1 / 512))
-        pc.check_metric((4, 4, 1024), (1 / 4, 1 / 4, 1 / 1024), np.float32)
-        pc.check_cf_vs_oracle((2, 2048), (1 / 2, 1 / 2048), np.float64, None)
-        pc.check_fused_direction_update((8, 512), (1 / 8, 1 / 512))
+    # (plain, * weight, * field + add + dot)
+    pc.check_hartley_shapes([((512,), None), ((4, 1024), None), ((2, 2, 2048), None)])
+    pc.check_metric((8, 512), (1 / 8, 1 / 512))
+    pc.check_metric((4, 4, 1024), (1 / 4, 1 / 4, 1 / 1024), np.float32)
+    pc.check_cf_vs_oracle((2, 2048), (1 / 2, 1 / 2048), np.float64, None)
+    pc.check_fused_direction_update((8, 512), (1 / 8, 1 / 512))
 
 
 def test_hartley_random_pow2_shapes():
