@@ -20,7 +20,13 @@ N_RESET = 20
 
 
 def _vdot(a, b):
-    return float(np.vdot(np.ravel(a), np.ravel(b)).real)
+    """``ducc_dispatch.vdot`` (``src/ducc_dispatch.py:81-86``): ``ducc0.misc.vdot`` accumulates in extended
+    precision whatever the input precision (the SciPy fallback warns about exactly that for fp32,
+    ``:53-58``), so fp32 operands are accumulated in fp64 here."""
+    a, b = np.ravel(a), np.ravel(b)
+    if a.dtype == np.float32 or b.dtype == np.float32:
+        a, b = a.astype(np.float64), b.astype(np.float64)
+    return float(np.vdot(a, b).real)
 
 
 # ------------------------------------------------------------------ numpy stack
@@ -109,11 +115,11 @@ class AbsDeltaEnergyController:
         return CONTINUE
 
 
-def conjugate_gradient_np(energy, controller, preconditioner=None, nreset=20, history=None):
+def conjugate_gradient_np(energy, controller, preconditioner=None, nreset=20, history=None, res_history=None):
     """``ConjugateGradient.__call__`` (``conjugate_gradient.py:48-126``).
 
     Returns ``(energy, status, n_iterations)``; ``history`` (a list) receives the
-    energy value after every step.
+    energy value after every step, ``res_history`` the gradient norm.
     """
     status = controller.start(energy)
     if status != CONTINUE:
@@ -147,6 +153,8 @@ def conjugate_gradient_np(energy, controller, preconditioner=None, nreset=20, hi
         gamma = _vdot(r, s)
         if history is not None:
             history.append(energy.value)
+        if res_history is not None:
+            res_history.append(energy.gradient_norm)
         if np.isnan(gamma) or gamma < 0:
             return energy, ERROR, nit
         if gamma == 0:
@@ -175,8 +183,9 @@ def _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord, tol, atol):
 
 
 def cg_re(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5, atol=0.0,
-          miniter=None, maxiter=None, _raise_nonposdef=True, history=None):
-    """``_cg`` (``re/conjugate_gradient.py:77-216``), Python-loop variant."""
+          miniter=None, maxiter=None, _raise_nonposdef=True, history=None, res_history=None):
+    """``_cg`` (``re/conjugate_gradient.py:77-216``), Python-loop variant.  ``history`` / ``res_history``
+    (lists) receive the energy / the residual norm after every step (test instrumentation)."""
     norm_ord, miniter, maxiter, resnorm, eps, tiny = _defaults(
         j, miniter, maxiter, absdelta, resnorm, norm_ord, tol, atol)
     if x0 is None:
@@ -216,6 +225,8 @@ def cg_re(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e
         else:
             r = r - q * alpha
         gamma = _vdot(r, r)
+        if res_history is not None:
+            res_history.append(float(np.linalg.norm(np.ravel(r), ord=norm_ord)))
         if gamma >= 0.0 and gamma <= tiny:
             info = 0
             break

@@ -84,8 +84,34 @@ def power_index_np(shape, distances):
     return PowerIndex(pindex, k_lengths, rho, uk)
 
 
+def fourier_mode_distributor_isotropic(shape, distances):
+    """Same result as :func:`fourier_mode_distributor` for grids with equal harmonic pixel sizes, from the
+    integer squared mode lengths ``ksq = sum_j min(k_j, N_j - k_j)^2`` (the device the reference's own numpy
+    stack uses in ``RGSpace.get_unique_k_lengths``, ``rg_space.py:130-141``) instead of a sort of N floats.
+    Only used above ``_ISOTROPIC_SHORTCUT_SIZE`` points, where the float sort takes minutes; equality with the
+    restated reference algorithm is asserted in tests/test_oracle_golden.py."""
+    shape = _as_tuple(shape)
+    hd = harmonic_distances(shape, distances)
+    ksq = None
+    for n in shape:
+        k = np.arange(n, dtype=np.int64)
+        k = np.minimum(k, n - k) ** 2
+        ksq = k if ksq is None else np.add.outer(ksq, k)
+    m_count_all = np.bincount(ksq.ravel())
+    uniq = np.nonzero(m_count_all)[0]
+    lut = np.zeros(m_count_all.size, dtype=np.int64)
+    lut[uniq] = np.arange(uniq.size)
+    return lut[ksq], np.sqrt(uniq.astype(np.float64)) * hd[0], m_count_all[uniq]
+
+
+_ISOTROPIC_SHORTCUT_SIZE = 1 << 24
+
+
 def fourier_mode_distributor(shape, distances):
     """``get_fourier_mode_distributor`` (``re/correlated_field.py:30-81``)."""
+    hd = harmonic_distances(shape, distances)
+    if np.prod(_as_tuple(shape)) > _ISOTROPIC_SHORTCUT_SIZE and len(hd) > 1 and np.all(hd == hd[0]):
+        return fourier_mode_distributor_isotropic(shape, distances)
     m_length = k_length_array(shape, distances)
     um = np.unique(m_length)
     tol = 1e-12 * um[-1]
@@ -102,10 +128,23 @@ Grid = namedtuple("Grid", "shape total_volume distances power_distributor mode_m
                           "mode_lengths relative_log_mode_lengths log_volume")
 
 
+_grid_cache = {}
+
+
 def make_grid(shape, distances):
-    """``_make_grid`` (``re/correlated_field.py:108-142``), fourier harmonic type."""
+    """``_make_grid`` (``re/correlated_field.py:108-142``), fourier harmonic type (memoised: the grid
+    depends on the shape and the distances only)."""
     shape = _as_tuple(shape)
-    distances = tuple(np.broadcast_to(distances, (len(shape),)).astype(np.float64))
+    distances = tuple(float(d) for d in np.broadcast_to(distances, (len(shape),)).astype(np.float64))
+    key = (shape, distances)
+    if key not in _grid_cache:
+        if len(_grid_cache) > 8:
+            _grid_cache.clear()
+        _grid_cache[key] = _make_grid(shape, distances)
+    return _grid_cache[key]
+
+
+def _make_grid(shape, distances):
     totvol = float(np.prod(np.array(shape) * np.array(distances)))
     idx, m_length, m_count = fourier_mode_distributor(shape, distances)
     um = m_length.copy()

@@ -76,19 +76,29 @@ def hartley_operator(x, axes, fct, convention=NON_CANONICAL):
 
 
 def direct_hartley_samples(a, idx_list, convention=NON_CANONICAL):
-    """O(N) direct evaluation of single output elements of the all-axes Hartley
-    transform (SURVEY.md section 8d "sub-sampled checks"): used at sizes where a full
-    CPU transform is too slow/large.  ``idx_list``: iterable of index tuples."""
-    a = np.asarray(a, dtype=np.float64)
-    out = []
-    grids = [np.arange(n, dtype=np.float64) for n in a.shape]
-    for idx in idx_list:
-        # separable phases, accumulated in extended fashion: cos(sum) -/+ sin(sum)
-        ph = [2 * np.pi * ((int(k) * g) % n) / n for k, g, n in zip(idx, grids, a.shape)]
-        e = [np.exp(-1j * p) for p in ph]
-        acc = a.astype(np.complex128)
-        for ax in range(a.ndim - 1, -1, -1):
-            acc = np.tensordot(acc, e[ax], axes=([ax], [0]))
-        f = complex(acc)
-        out.append(f.real + f.imag if convention == NON_CANONICAL else f.real - f.imag)
-    return np.array(out)
+    """O(N) direct evaluation of single output elements of the all-axes Hartley transform (SURVEY.md
+    section 8d "sub-sampled checks"), for sizes where a full CPU transform is too slow or too large.
+    ``idx_list``: iterable of index tuples.  The array is consumed slab by slab along its first axis
+    (any float dtype; at most 16 MB of it is held in fp64 at a time), all requested elements at once:
+    ``F[k] = sum_n0 e0[n0] (sum_rest a[n0, ...] e_rest[...])`` with fp64 phases ``exp(-2 pi i k n / N)``."""
+    a = np.asarray(a)
+    idx = [tuple(int(v) for v in i) for i in idx_list]
+    ns = len(idx)
+    shape = a.shape
+    ph = [np.exp(-2j * np.pi * ((np.array([i[ax] for i in idx])[:, None] * np.arange(n)[None, :]) % n) / n)
+          for ax, n in enumerate(shape)]                      # ph[ax][sample, n]
+    acc = np.zeros(ns, dtype=np.complex128)
+    if a.ndim == 1:
+        acc = ph[0] @ a.astype(np.float64)
+    else:
+        rest = int(np.prod(shape[1:]))
+        step = max(1, (2 << 20) // rest)
+        for lo in range(0, shape[0], step):
+            blk = a[lo:lo + step].astype(np.float64)           # (s, n1, ..., n_last)
+            t = np.tensordot(blk, ph[-1], axes=([blk.ndim - 1], [1]))      # (s, n1, ..., sample)
+            for ax in range(a.ndim - 2, 0, -1):
+                # multiply by the phase of axis `ax` (per sample) and sum that axis away
+                t = np.einsum("...ns,sn->...s", t, ph[ax])
+            acc += np.einsum("ns,sn->s", t, ph[0][:, lo:lo + step])
+    f = np.asarray(acc)
+    return f.real + f.imag if convention == NON_CANONICAL else f.real - f.imag

@@ -208,3 +208,28 @@ def test_cg_nonposdef():
     r = ocg.static_cg_re(mat, j)
     assert r.info == -1
     assert oracle is not None
+
+
+def test_isotropic_shortcut_equals_restated_algorithm():
+    """oracle.geometry uses an integer-ksq shortcut above 2^24 points (where the reference's float sort takes
+    minutes): same index, same mode lengths (to the last bits), same multiplicities as the restated
+    ``get_fourier_mode_distributor`` on every isotropic shape tried."""
+    from oracle import geometry as g
+    for shape, d in (((64, 64), 1 / 64), ((32, 32, 32), 1 / 32), ((16, 64), (1 / 16, 1 / 64)), ((128, 256), (1 / 128, 1 / 256)),
+                     ((8, 16, 32), (1 / 8, 1 / 16, 1 / 32)), ((12, 12), 0.3)):
+        idx, um, cnt = g.fourier_mode_distributor(shape, d)
+        idx2, um2, cnt2 = g.fourier_mode_distributor_isotropic(shape, d)
+        assert np.array_equal(idx, idx2) and np.array_equal(cnt, cnt2)
+        np.testing.assert_allclose(um2, um, rtol=4e-16, atol=0)
+
+
+def test_direct_hartley_samples_equal_the_full_transform():
+    from oracle import transforms as otr
+    rng = np.random.default_rng(0)
+    for shape in ((37,), (12, 9), (8, 6, 10), (4, 5, 6, 7)):
+        a = rng.normal(size=shape)
+        idx = [tuple(int(rng.integers(0, n)) for n in shape) for _ in range(5)]
+        for c in (otr.NON_CANONICAL, otr.CANONICAL):
+            ref = otr.hartley(a, None, c)
+            got = otr.direct_hartley_samples(a, idx, c)
+            assert np.max(np.abs(got - np.array([ref[i] for i in idx]))) <= 1e-12 * np.sqrt(a.size) * 10
