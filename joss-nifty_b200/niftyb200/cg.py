@@ -357,7 +357,9 @@ def cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5,
 
 
 def _cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5, atol=0.0, miniter=None,
-        maxiter=None, name=None, time_threshold=None, _raise_nonposdef=True, history=None):
+        maxiter=None, name=None, time_threshold=None, _raise_nonposdef=True, history=None, res_history=None):
+    """``_cg`` (re/conjugate_gradient.py:77-216).  ``history`` / ``res_history``: optional lists that receive
+    the energy / the residual norm after every iteration (instrumentation, not in the reference)."""
     norm_ord, miniter, maxiter, resnorm, eps, tiny = _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord,
                                                                tol, atol, getattr(mat, "comm", None))
     vec, pos, r, d, q, energy, nfev, previous_gamma = _cg_setup(mat, j, x0)
@@ -394,6 +396,8 @@ def _cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5
         if _timed_out(time_threshold, vec.comm):                       # :176-178
             info = i
             break
+        if res_history is not None:
+            res_history.append(_norm(r, gamma, norm_ord, vec.comm))
         if gamma >= 0.0 and gamma <= tiny:                             # :179-183
             info = 0
             break

@@ -14,7 +14,9 @@ for p in (ROOT, os.path.join(ROOT, "joss-nifty_b200"), os.path.join(ROOT, "tests
         sys.path.insert(0, p)
 
 
-def run(rank, world, port, backend, emu_path, shape, result):
+def run(rank, world, port, backend, emu_path, shape, result, mode="full", dtype="f64"):
+    """mode "full": forward, adjoint, metric, 5 back-to-back transforms and a CG solve against the oracle;
+    mode "large": the same without the CG solve (grids where the oracle CG would take minutes)."""
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     from niftyb200 import _lib
     if backend == "gloo":
@@ -25,48 +27,83 @@ def run(rank, world, port, backend, emu_path, shape, result):
     try:
         import niftyb200 as nb
         import parity_cases as pc
-        from oracle import cg as ocg
+        from oracle import cg as ocg, metric as om, transforms as otr
         cgm = sys.modules["niftyb200.cg"]
+        dt = np.float64 if dtype == "f64" else np.float32
+        tdt = torch.float64 if dtype == "f64" else torch.float32
+        if rank == 0:
+            otr.set_nthreads(max(1, (os.cpu_count() or 1) // 2))
         dist_ = tuple(1.0 / s for s in shape)      # isotropic harmonic pixels
-        cf, co = pc.make_pair(shape, dist_, torch.float64, kw=pc.GENTLE_KW)
+        cf, co = pc.make_pair(shape, dist_, tdt, kw=pc.GENTLE_KW)
         scf = nb.SlabCorrelatedField(cf)
         ht = scf.ht
         p = cf.init(5)
-        tab = scf.tables(p)
+        p["xi"] = p["xi"].astype(dt)
         amps_o, azm_o = co.normalized_amplitudes(p), co.azm(p)
+        tab = scf.streaming_tables(cf.tables_from_amplitudes(amps_o, float(azm_o)))
+
+        def f64(a):
+            return np.asarray(a, dtype=np.float64)
         # forward apply: X -> Y
         y = scf.apply_xi(ht.scatter_x(p["xi"]), tab)
-        err_f = pc.rel(ht.gather_y(y), co(p))
+        got = ht.gather_y(y)
+        err_f = pc.rel(got, co.apply(amps_o, azm_o, f64(p["xi"]))) if rank == 0 else 0.0
         # adjoint: Y -> X
         rng = np.random.default_rng(9)
-        yb = rng.normal(size=shape)
+        yb = rng.normal(size=shape).astype(dt)
         xb = scf.adjoint_xi(ht.scatter_y(yb), tab)
-        err_a = pc.rel(ht.gather_x(xb), co.adjoint(amps_o, azm_o, yb)[0])
-        # metric + CG
-        from oracle import metric as om
-        w = np.exp(0.3 * rng.normal(size=shape))
+        got = ht.gather_x(xb)
+        err_a = pc.rel(got, co.adjoint(amps_o, azm_o, f64(yb))[0]) if rank == 0 else 0.0
+        # metric
+        w = np.exp(0.3 * rng.normal(size=shape)).astype(dt)
         M = nb.CFMetric(scf, tab, ht.scatter_y(w))
-        Mo = om.cf_metric_xi(co, amps_o, azm_o, w)
-        x0 = rng.normal(size=shape)
-        j = om.linear_sample_rhs(co, amps_o, azm_o, w, rng.normal(size=shape), x0)
+        Mo = om.cf_metric_xi(co, amps_o, azm_o, f64(w))
+        Mo.parts = (co, amps_o, azm_o, f64(w))
+        x0 = rng.normal(size=shape).astype(dt)
         q, curv = M.apply_with_curvature(ht.scatter_x(x0))
-        err_m = pc.rel(ht.gather_x(q), Mo(x0))
-        err_c = abs(float(curv.cpu()) - np.vdot(x0, Mo(x0))) / abs(np.vdot(x0, Mo(x0)))
-        kw = dict(absdelta=1e-5 * j.size, maxiter=60)
-        r = cgm._cg(M, ht.scatter_x(j), ht.scatter_x(x0), **kw)
-        ro = ocg.cg_re(Mo, j, x0, **kw)
-        err_x = pc.rel(ht.gather_x(r.x), ro.x)
-        window = [ro.nit] + [ocg.cg_re(Mo, pc.perturb(j, sd), x0, **kw).nit for sd in (1, 2, 3, 4)]
+        got = ht.gather_x(q)
+        err_m = err_c = 0.0
         if rank == 0:
-            result.update(window=window, err_f=err_f, err_a=err_a, err_m=err_m, err_c=err_c, nit=(r.nit, ro.nit), info=(r.info, ro.info),
-                          nfev=(r.nfev, ro.nfev), err_x=err_x)
+            ref = Mo(f64(x0))
+            err_m = pc.rel(got, ref)
+            err_c = abs(float(curv.cpu()) - np.vdot(f64(x0), ref)) / abs(np.vdot(f64(x0), ref))
+        # double-buffer rule of the peer exchange: five back-to-back transforms, no host synchronisation
+        # in between, compared after the last
+        t = ht.scatter_x(x0)
+        ys = [torch.empty(scf.position_shape, dtype=tdt, device=t.device) for _ in range(2)]
+        xs = [torch.empty(scf.latent_shape, dtype=tdt, device=t.device) for _ in range(2)]
+        y1 = scf.apply_xi(t, tab, out=ys[0], offset=0.0)
+        x2 = scf.adjoint_xi(y1, tab, out=xs[0])
+        y3 = scf.apply_xi(x2, tab, out=ys[1], offset=0.0)
+        x4 = scf.adjoint_xi(y3, tab, out=xs[1])
+        y5 = scf.apply_xi(x4, tab, out=ys[0], offset=0.0)
+        got = ht.gather_y(y5)
+        err_s = 0.0
+        if rank == 0:
+            r = f64(x0)
+            for k in range(5):
+                r = co.apply(amps_o, azm_o, r, offset=0.0) if k % 2 == 0 else co.adjoint(amps_o, azm_o, r)[0]
+            err_s = pc.rel(got, r)
+        out = dict(err_f=err_f, err_a=err_a, err_m=err_m, err_c=err_c, err_s=err_s, dtype=dtype, world=world,
+                   p2p=ht.peer is not None)
+        if mode == "full":
+            j = om.linear_sample_rhs(co, amps_o, azm_o, f64(w), rng.normal(size=shape), f64(x0)).astype(dt)
+            kw = dict(absdelta=1e-5 * j.size, maxiter=60)
+            r = cgm._cg(M, ht.scatter_x(j), ht.scatter_x(x0), **kw)
+            got = ht.gather_x(r.x)
+            if rank == 0:
+                ro = ocg.cg_re(Mo, f64(j), f64(x0), **kw)
+                out.update(window=pc.count_window(lambda m: ocg.cg_re(m, f64(j), f64(x0), **kw), Mo),
+                           nit=(r.nit, ro.nit), info=(r.info, ro.info), nfev=(r.nfev, ro.nfev), err_x=pc.rel(got, ro.x))
+        if rank == 0:
+            result.update(out)
     finally:
         dist.destroy_process_group()
 
 
-def launch(world, backend, emu_path, shape, port=29533):
+def launch(world, backend, emu_path, shape, port=29533, mode="full", dtype="f64"):
     import torch.multiprocessing as mp
     mgr = mp.Manager()
     result = mgr.dict()
-    mp.spawn(run, args=(world, port, backend, emu_path, shape, result), nprocs=world, join=True)
+    mp.spawn(run, args=(world, port, backend, emu_path, shape, result, mode, dtype), nprocs=world, join=True)
     return dict(result)

@@ -6,16 +6,19 @@ import dist_worker
 
 
 def check(res, strict=True):
-    assert res["err_f"] <= 1e-12 and res["err_a"] <= 1e-12 and res["err_m"] <= 1e-12, res
-    assert res["err_c"] <= 1e-12, res
+    tol = 1e-12 if res["dtype"] == "f64" else 1e-5
+    for k in ("err_f", "err_a", "err_m", "err_c", "err_s"):
+        assert res[k] <= tol, (k, res)
+    if "nit" not in res:
+        return
     if strict:
         assert res["nit"][0] == res["nit"][1] and res["nfev"][0] == res["nfev"][1], res
     else:   # the reference CG's own sensitivity window (parity_cases._same_counts)
-        assert (min(res["window"]) - 1 <= res["nit"][0] <= max(res["window"]) + 1
-                or abs(res["nit"][0] - res["nit"][1]) <= max(2, 0.3 * res["nit"][1])), res
+        assert min(res["window"]) - 1 <= res["nit"][0] <= max(res["window"]) + 1, \
+            f"count {res['nit'][0]} outside the reference's own window {sorted(set(res['window']))} +-1"
     assert res["info"][0] == res["info"][1], res
     if res["nit"][0] == res["nit"][1]:
-        assert res["err_x"] <= (1e-8 if strict else 1e-3), res
+        assert res["err_x"] <= (1e-8 if strict else 2e-2), res
 
 
 def test_slab_two_ranks_gloo():
@@ -55,3 +58,8 @@ def test_symmetric_split_is_a_partition():
             for l in range(n):
                 lm = (n - l - s.shift(r)) % n
                 assert (N - own[l]) % N == own[lm]        # local mirror rule == global index negation
+
+
+def test_slab_two_ranks_gloo_fp32():
+    res = dist_worker.launch(2, "gloo", conftest.build_emulator(), (16, 16, 32), port=29547, mode="large", dtype="f32")
+    check(res)

@@ -69,6 +69,20 @@ def test_cg_parity(shape, dist):
     pc.check_cg_parity(shape, dist)
 
 
+def test_cg_count_identical():
+    # stopping rules with separated thresholds: identical counts, both precisions, both likelihoods
+    n = pc.check_cg_strict((32, 32), (1 / 32, 1 / 32), np.float64, "gaussian", min_checks=2)
+    n += pc.check_cg_strict((32, 32), (1 / 32, 1 / 32), np.float32, "gaussian", min_checks=0)
+    n += pc.check_cg_strict((64, 64), (1 / 64, 1 / 64), np.float64, "poisson", min_checks=6)
+    n += pc.check_cg_strict((16, 16, 16), (1 / 16,) * 3, np.float32, "poisson", min_checks=4)
+    assert n >= 16
+
+
+def test_metric_poissonian():
+    pc.check_metric((32, 32), (1 / 32, 1 / 32), np.float64, "poisson")
+    pc.check_metric((8, 8, 16), (1 / 8, 1 / 8, 1 / 16), np.float32, "poisson")
+
+
 def test_cg_failure_modes():
     pc.check_cg_failure_modes()
 

@@ -1,5 +1,7 @@
-"""N>1 GPU twin of test_distributed_cpu.py: NCCL all-to-all + CUDA passes on 2 (and 4) GPUs of
-one box.  Skipped on boxes with a single GPU."""
+"""N>1 GPU twin of test_distributed_cpu.py on the GPUs of one box: the DEFAULT exchange of the slab path
+(peer-memory stores through CUDA IPC, `nb2_strided_pass_scatter`) and NCCL for the scalars, against the
+single-process oracle -- forward, adjoint, metric, curvature, five back-to-back transforms (double-buffer
+rule) and a CG solve.  Skipped on boxes with fewer GPUs than ranks."""
 
 import pytest
 import torch
@@ -10,9 +12,33 @@ from test_distributed_cpu import check
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("world,shape", [(2, (64, 64, 64)), (4, (64, 128, 32)), (8, (128, 128, 64))])
-def test_slab_nccl(world, shape):
+@pytest.mark.parametrize("world,shape", [(2, (64, 64, 64)), (4, (64, 128, 32)), (8, (128, 128, 64)), (4, (256, 256, 128)),
+                                         (8, (256, 256, 256))])
+def test_slab_peer_exchange(world, shape):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     res = dist_worker.launch(world, "nccl", None, shape, port=29550 + world)
+    assert res["p2p"] and res["world"] == world
+    check(res, strict=False)
+
+
+@pytest.mark.parametrize("world,shape,dtype", [(8, (512, 512, 512), "f32"), (4, (512, 512, 512), "f32"), (2, (256, 256, 256), "f32"),
+                                               (8, (512, 512, 512), "f64")])
+def test_slab_peer_exchange_large(world, shape, dtype):
+    """BASELINE-sized grid: forward / adjoint / metric / back-to-back transforms against the full oracle."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    res = dist_worker.launch(world, "nccl", None, shape, port=29560 + world, mode="large", dtype=dtype)
+    assert res["p2p"] and res["world"] == world
+    check(res)
+
+
+def test_slab_nccl_all_to_all(monkeypatch):
+    """The alternative data plane (NIFTYB200_SLAB_P2P=0: NCCL all_to_all_single per column chunk)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    monkeypatch.setenv("NIFTYB200_SLAB_P2P", "0")
+    world = min(4, torch.cuda.device_count())
+    res = dist_worker.launch(world, "nccl", None, (64, 128, 64), port=29571)
+    assert not res["p2p"]
     check(res, strict=False)
