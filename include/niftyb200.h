@@ -196,6 +196,9 @@ int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, c
  * synchronous. */
 int nb2_hartley_host(nb2_plan* plan, const void* in_host, void* out_host, int convention, double scale);
 int nb2_c2c_host(nb2_plan* plan, const void* in_host, void* out_host, int forward, double scale);
+/* sum_i a[i]*b[i] of two HOST arrays of n real scalars into *out_host (fp64 accumulation on the device):
+ * the numpy drop-in form of ducc_dispatch.vdot (src/ducc_dispatch.py:81-86).  Synchronous. */
+int nb2_vdot_host(int dtype, int64_t n, const void* a_host, const void* b_host, double* out_host);
 
 #ifdef __cplusplus
 }

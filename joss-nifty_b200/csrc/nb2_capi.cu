@@ -738,4 +738,23 @@ int nb2_c2c_host(nb2_plan* pl, const void* in_host, void* out_host, int forward,
     return rc;
 }
 
+int nb2_vdot_host(int dtype, int64_t n, const void* a_host, const void* b_host, double* out_host) {
+    if (n < 0 || !out_host || (n > 0 && (!a_host || !b_host)) || (dtype != NB2_F32 && dtype != NB2_F64)) {
+        last_error() = "nb2_vdot_host: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    const size_t bytes = (size_t)n * (dtype == NB2_F32 ? 4 : 8);
+    void *a = nullptr, *b = nullptr;
+    double* out = nullptr;
+    int rc = rt_malloc(&a, bytes) || rt_malloc(&b, bytes) || rt_malloc((void**)&out, sizeof(double)) ? NB2_ERR_CUDA : 0;
+    if (!rc) rc = rt_h2d(a, a_host, bytes, nullptr);
+    if (!rc) rc = rt_h2d(b, b_host, bytes, nullptr);
+    if (!rc) rc = nb2_vdot(dtype, n, a, b, out, nullptr);
+    if (!rc) rc = rt_d2h(out_host, out, sizeof(double), nullptr);
+    rt_free(a);
+    rt_free(b);
+    rt_free(out);
+    return rc;
+}
+
 }  // extern "C"

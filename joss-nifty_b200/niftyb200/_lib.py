@@ -78,6 +78,7 @@ class Library:
                                   c_void_p, c_void_p, c_void_p]),
         "nb2_hartley_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double]),
         "nb2_c2c_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double]),
+        "nb2_vdot_host": (c_int, [c_int, c_int64, c_void_p, c_void_p, c_void_p]),
     }
 
     def __init__(self, path, device_type):
