@@ -257,6 +257,15 @@ class SlabHartley:
                                                     in_ostride=self.ostride1, col0=c * mc, ncols=mc))
         return self.plan_x.run_pass(2, out, out, convention, epi=epi)
 
+    def close(self):
+        """Unmap the peers' receive buffers and free this rank's (collective: every rank calls it, after a
+        barrier, so that no peer is still storing into a buffer that goes away)."""
+        if self.peer is not None:
+            torch.cuda.synchronize()
+            dist.barrier(group=self.comm.group)
+            self.peer.close()
+            self.peer = None
+
     # ---- host-side helpers: natural global array <-> local parts ----------------------------
     def scatter_x(self, a):
         return torch.as_tensor(np.ascontiguousarray(np.asarray(a)[self.s0.owned(self.comm.rank)])).to(_device())
@@ -304,6 +313,10 @@ class SlabCorrelatedField:
         self.ht = SlabHartley(cf.shape, cf.dtype, self.comm)
         self.shape = cf.shape
         self.latent_shape, self.position_shape = self.ht.shape_x, self.ht.shape_y
+
+    def close(self):
+        """Release the peer-memory mappings of the exchange (collective)."""
+        self.ht.close()
 
     def tables(self, p):
         return self.streaming_tables(self.cf.tables(p))

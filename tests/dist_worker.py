@@ -93,7 +93,8 @@ def run(rank, world, port, backend, emu_path, shape, result, mode="full", dtype=
             got = ht.gather_x(r.x)
             if rank == 0:
                 ro = ocg.cg_re(Mo, f64(j), f64(x0), **kw)
-                out.update(window=pc.count_window(lambda m: ocg.cg_re(m, f64(j), f64(x0), **kw), Mo),
+                dE, g, nE, nG = pc.oracle_histories(Mo, f64(j), f64(x0), kw["maxiter"], dt)
+                out.update(window=sorted(pc.acceptable_stops(dE, nE, kw["absdelta"], 6, kw["maxiter"])),
                            nit=(r.nit, ro.nit), info=(r.info, ro.info), nfev=(r.nfev, ro.nfev), err_x=pc.rel(got, ro.x))
         if rank == 0:
             result.update(out)

@@ -278,11 +278,17 @@ def check_baseline_size(shape, dt):
         p = cf.init(3)
         p["xi"] = p["xi"].astype(dt)
         xi64 = p["xi"].astype(np.float64)
-        tab = cf.tables(p)
         amps_o, azm_o = co.normalized_amplitudes(p), co.azm(p)
+        own = cf.tables(p)                     # our O(n_bins) amplitude chain (torch; parallel scan)
+        out = {"amplitude chain": max(rel(host(a), b) for a, b in zip(own.amps, amps_o))}
+        # the hot path's inputs are the amplitude tables: the applies are compared on the SAME tables (the
+        # chain's own rounding, 3e-13 at 141k bins, would otherwise enter the metric twice); the full model
+        # with our own chain is the "forward (full model)" entry
+        tab = cf.tables_from_amplitudes(amps_o, float(azm_o))
         x = dev(p["xi"])
         plan = get_plan(shape, None, tdt)
-        out = {}
+        out["forward (full model)"] = rel(host(cf.apply_xi(x, own)), co(p))
+        del own
         for conv in CONVS:
             got = host(plan.hartley(x, convention=conv))
             out["hartley " + conv] = rel(got, otr.hartley(xi64, None, conv))
@@ -322,9 +328,14 @@ def check_baseline_size(shape, dt):
 #    from the tested values and NOISE_MARGIN times the reference's own rounding sensitivity away from them).
 #    For these rules nit / info / nfev must be IDENTICAL.
 #  * demo-style thresholds (`check_cg_parity`): identical counts, or -- recorded in the assertion message --
-#    a count inside the window (+-1) spanned by the oracle itself when it is run in a second arithmetic
-#    (`other_arithmetic`: another summation order; `noisy_metric`: rounding-sized transform noise; six seeds).
+#    a stopping iteration that is CONSISTENT with the oracle's own history and its measured per-iteration
+#    rounding sensitivity (`acceptable_stops`): the reference could not have stopped earlier and may stop
+#    there when each tested value is moved by at most ENVELOPE times the deviation that the oracle shows
+#    when it is run in a second arithmetic (`other_arithmetic`: another summation order; `noisy_metric`:
+#    rounding-sized transform noise).  Outside the bursts that sensitivity is ~1e-12 of the value, so the
+#    criterion forces equality there; it is only loose where the reference itself is undetermined.
 NOISE_MARGIN = 50.0
+ENVELOPE = 3.0
 WINDOW_SEEDS = (1, 2, 3, 4, 5, 6)
 
 # Size of the rounding noise injected into the oracle to measure its sensitivity (relative L2, white, per
@@ -462,16 +473,37 @@ def check_cg_strict(shape, dist, dt=np.float64, likelihood="gaussian", nmax=40, 
     return checked
 
 
-def _same_counts(r, ro, kw, strict, rerun):
-    """Identical (nit, info, nfev); otherwise (demo-style thresholds that fall inside a near-breakdown
-    burst, see above) the count must lie inside the window (+-1) spanned by the oracle in a second
-    arithmetic (`rerun(mat, kw)`), which the assertion message records.  `strict`: no window."""
+def acceptable_stops(vals, noise, t, miniter, maxiter):
+    """Stopping iterations of the rule "first i >= miniter with vals[i] < t, else maxiter" that are consistent
+    with the oracle history `vals` when every value may move by ENVELOPE * `noise` (iterations 1-based):
+    from the first iteration whose lower envelope is below `t` up to the first whose upper envelope is."""
+    acc = set()
+    lo, hi = vals - ENVELOPE * noise, vals + ENVELOPE * noise
+    for i in range(max(miniter, 1), min(maxiter, len(vals)) + 1):
+        if lo[i - 1] < t:
+            acc.add(i)
+        if hi[i - 1] < t:
+            return acc
+    acc.add(maxiter)
+    return acc
+
+
+def _same_counts(r, ro, kw, strict, hist, j):
+    """Identical (nit, info, nfev); otherwise (demo-style thresholds that fall inside a near-breakdown burst,
+    see above) a stopping iteration consistent with the oracle's history and sensitivity (`acceptable_stops`),
+    which the assertion message records.  `strict`: identical, no exception."""
     if (r.nit, r.info, r.nfev) == (ro.nit, ro.info, ro.nfev):
         return
     assert not strict, (kw, tuple(r[1:]), tuple(ro[1:]))
-    nits = count_window(lambda m: rerun(m, kw), rerun.Mo)
-    assert min(nits) - 1 <= r.nit <= max(nits) + 1 and r.info == ro.info, \
-        f"count {r.nit} outside the reference's own window {sorted(set(nits))} +-1 for {kw}"
+    dE, g, nE, nG = hist
+    maxiter = kw.get("maxiter", 200)
+    miniter = kw.get("miniter", min(6, maxiter))
+    if kw.get("absdelta") is not None:
+        acc = acceptable_stops(dE, nE, kw["absdelta"], miniter, maxiter)
+    else:
+        acc = acceptable_stops(g, nG, kw.get("resnorm", 1e-5 * float(np.linalg.norm(j))), miniter, maxiter)
+    assert r.nit in acc and r.info in (0, r.nit), \
+        f"count {r.nit} (reference {ro.nit}) is not a stopping iteration consistent with the reference: {sorted(acc)} for {kw}"
 
 
 def check_cg_parity(shape, dist, strict=True):
@@ -486,18 +518,13 @@ def check_cg_parity(shape, dist, strict=True):
     jt, xt = dev(j), dev(x0)
     n = j.size
 
-    def rerun_cg(m, k):
-        return ocg.cg_re(m, j, x0, **k)
-
-    def rerun_static(m, k):
-        return ocg.static_cg_re(m, j, x0, **k)
-    rerun_cg.Mo = rerun_static.Mo = Mo
+    hist = None if strict else oracle_histories(Mo, j, x0, 200)
     for kw in (dict(absdelta=1e-5 * n, maxiter=100), dict(resnorm=1e-4 * np.linalg.norm(j), maxiter=100),
                dict(absdelta=1e-12, maxiter=27), dict()):
         h1, h2 = [], []
         r = cgm._cg(M, jt, xt, history=h1, **kw)
         ro = ocg.cg_re(Mo, j, x0, history=h2, **kw)
-        _same_counts(r, ro, kw, strict, rerun_cg)
+        _same_counts(r, ro, kw, strict, hist, j)
         m = min(len(h1), len(h2))
         np.testing.assert_allclose(h1[:m], h2[:m], rtol=htol)
         np.testing.assert_allclose(h1[:min(m, 5)], h2[:min(m, 5)], rtol=1e-12)     # before the first burst
@@ -505,7 +532,7 @@ def check_cg_parity(shape, dist, strict=True):
             assert rel(host(r.x), ro.x) <= xtol
         s = cgm._static_cg(M, jt, xt, **kw)
         so = ocg.static_cg_re(Mo, j, x0, **kw)
-        _same_counts(s, so, kw, strict, rerun_static)
+        _same_counts(s, so, kw, strict, hist, j)
         if s.nit == so.nit:
             assert rel(host(s.x), so.x) <= xtol
     # x0 = None branch
@@ -515,22 +542,21 @@ def check_cg_parity(shape, dist, strict=True):
     if r.nit == ro.nit:
         assert rel(host(r.x), ro.x) <= xtol
     # numpy-stack interface
-    for mk in (lambda m: m.AbsDeltaEnergyController(1e-6 * n, iteration_limit=100),
-               lambda m: m.GradientNormController(tol_rel_gradnorm=1e-4, iteration_limit=100),
-               lambda m: m.AbsDeltaEnergyController(0., iteration_limit=23)):
+    g0 = float(np.linalg.norm(Mo(x0) - j))          # gradient norm at the start (tol_rel_gradnorm reference)
+    for mk, rule in ((lambda m: m.AbsDeltaEnergyController(1e-6 * n, iteration_limit=100), ("dE", 1e-6 * n, 100)),
+                     (lambda m: m.GradientNormController(tol_rel_gradnorm=1e-4, iteration_limit=100), ("g", 1e-4 * g0, 100)),
+                     (lambda m: m.AbsDeltaEnergyController(0., iteration_limit=23), ("dE", 0.0, 23))):
         solver = nb.ConjugateGradient(mk(nb))
         e, status = solver(nb.QuadraticEnergy(xt, M, jt))
         eo, so, nito = ocg.conjugate_gradient_np(ocg.QuadraticEnergy(x0, Mo, j), mk(ocg))
         assert status == so
         if solver.nit != nito:
             assert not strict, (solver.nit, nito)
-            nits = [nito]
-            with other_arithmetic():
-                for sd in WINDOW_SEEDS:
-                    nits.append(ocg.conjugate_gradient_np(
-                        ocg.QuadraticEnergy(x0, noisy_metric(Mo, np.float64, sd), j), mk(ocg))[2])
-            assert min(nits) - 1 <= solver.nit <= max(nits) + 1, \
-                f"count {solver.nit} outside the reference's own window {sorted(set(nits))} +-1"
+            dE, g, nE, nG = hist
+            vals, noise = (dE, nE) if rule[0] == "dE" else (g, nG)
+            acc = acceptable_stops(vals, noise, rule[1], 1, rule[2])
+            assert solver.nit in acc, \
+                f"count {solver.nit} (reference {nito}) is not consistent with the reference: {sorted(acc)} for {rule}"
         else:
             assert rel(host(e.position), eo.position) <= xtol
             assert abs(e.value - eo.value) <= (1e-10 if strict else htol) * abs(eo.value)

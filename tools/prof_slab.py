@@ -17,7 +17,8 @@ tdt = torch.float32 if (len(sys.argv) < 3 or sys.argv[2] == "f32") else torch.fl
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-cf, tab, M, j, x0 = bench.setup_slab_problem(nb, torch, (n, n, n), tdt, seed=42 + rank)
+cf, tab, M, j, x0 = bench.setup_problem(nb, torch, [((n, n, n), bench.CF_KW)], bench.OFFSET, "gaussian", tdt, seed=42 + rank,
+                                        slab=True)
 ht = cf.ht
 cgm = sys.modules["niftyb200.cg"]
 loop = cgm.CGLoop(M, j, x0)
