@@ -181,6 +181,23 @@ int nb2_c2c(nb2_plan* plan, const void* in, void* out, int forward, double scale
  * (src/ducc_dispatch.py:81-86).  *out_dev is a device double. */
 int nb2_vdot(int dtype, int64_t n, const void* a, const void* b, double* out_dev, void* stream);
 
+/* nb2_vdot WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same result contract as nb2_vdot (fp64 accumulation, deterministic; the
+ * summation order differs from nb2_vdot's, so the two agree to rounding, not bit for bit).  The per-CTA
+ * partial sums live in a file-scope `static __device__` array of NB2_VDOT_NOALLOC_MAX_PARTIALS doubles
+ * (512 KiB, held by every GPU that loads the library until exit); one CTA reduces
+ * NB2_VDOT_NOALLOC_CHUNK elements, hence n <= NB2_VDOT_NOALLOC_MAX_N (= 2^30 scalars, one 1024^3 field);
+ * larger n is rejected with NB2_ERR_ARG and a message.  The call makes no cudaMalloc / cudaFree / allocating
+ * library call (the first call on a device resolves the array's address with cudaGetSymbolAddress).
+ * Every call on a device shares the one array: it keeps the previous call's partials (every slot that is
+ * read is overwritten first, nothing needs to start at zero), and two calls that overlap on the GPU
+ * (different streams, or threads) RACE -- serialise them. */
+#define NB2_VDOT_NOALLOC_CHUNK 16384
+#define NB2_VDOT_NOALLOC_MAX_PARTIALS 65536
+#define NB2_VDOT_NOALLOC_MAX_N ((int64_t)NB2_VDOT_NOALLOC_CHUNK * NB2_VDOT_NOALLOC_MAX_PARTIALS)
+int nb2_vdot_noalloc(int dtype, int64_t n, const void* a, const void* b, double* out_dev, void* stream);
+
 /* y = a*x + b*y.  The vector updates of ConjugateGradient (src/minimization/
  * conjugate_gradient.py:101,124) and re `_cg` (src/re/conjugate_gradient.py:169,205). */
 int nb2_axpby(int dtype, int64_t n, double a, const void* x, double b, void* y, void* stream);

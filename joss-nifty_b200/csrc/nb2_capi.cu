@@ -662,6 +662,71 @@ int nb2_vdot(int dtype, int64_t n, const void* a, const void* b, double* out_dev
     return rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
 }
 
+// ---- nb2_vdot_noalloc: the dot-product reduction with its scratch in a static device array (see the header)
+#if !defined(NB2_EMU)
+static __device__ __align__(256) double nb2_noalloc_partials[NB2_VDOT_NOALLOC_MAX_PARTIALS];
+#else
+alignas(256) static double nb2_noalloc_partials[NB2_VDOT_NOALLOC_MAX_PARTIALS];
+#endif
+
+// Device address of the array on the CURRENT device.  In host code `nb2_noalloc_partials` is only a
+// stand-in for the symbol, not a device address: the address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+static int noalloc_scratch(double** out) {
+#if !defined(NB2_EMU)
+    static double* addr[kMaxDevices] = {nullptr};
+    static std::mutex m;
+    const int dev = rt_device();
+    if (dev < 0 || dev >= kMaxDevices) {
+        last_error() = "nb2_vdot_noalloc: device ordinal out of range";
+        return NB2_ERR_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(m);
+    if (!addr[dev]) {
+        double* p = nullptr;
+        const cudaError_t err = cudaGetSymbolAddress((void**)&p, nb2_noalloc_partials);
+        if (err != cudaSuccess || !p) {
+            last_error() = std::string("nb2_vdot_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(err);
+            return NB2_ERR_CUDA;
+        }
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+#else
+    *out = nb2_noalloc_partials;
+#endif
+    return NB2_OK;
+}
+
+int nb2_vdot_noalloc(int dtype, int64_t n, const void* a, const void* b, double* out_dev, void* stream) {
+    if (n < 0 || !out_dev || (n > 0 && (!a || !b)) || (dtype != NB2_F32 && dtype != NB2_F64)) {
+        last_error() = "nb2_vdot_noalloc: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (n > NB2_VDOT_NOALLOC_MAX_N) {
+        last_error() = "nb2_vdot_noalloc: n = " + std::to_string((long long)n) + " exceeds the maximum of " +
+                       std::to_string((long long)NB2_VDOT_NOALLOC_MAX_N) +
+                       " scalars that the static scratch array covers (use nb2_vdot, or split the vectors)";
+        return NB2_ERR_ARG;
+    }
+    double* partials = nullptr;
+    if (int rc = noalloc_scratch(&partials)) return rc;
+    rt_stream st = (rt_stream)stream;
+    // one CTA per chunk of NB2_VDOT_NOALLOC_CHUNK elements: the number of partials follows n
+    const long long grid = std::max<long long>(1, (n + NB2_VDOT_NOALLOC_CHUNK - 1) / NB2_VDOT_NOALLOC_CHUNK);
+    int rc;
+    if (dtype == NB2_F32) {
+        Dot<float>::Params p{(const float*)a, (const float*)b, n, partials, grid};
+        rc = rt_launch<Dot<float>>(grid, kVecThreads, Dot<float>::smem_bytes(kVecThreads), st, p);
+    } else {
+        Dot<double>::Params p{(const double*)a, (const double*)b, n, partials, grid};
+        rc = rt_launch<Dot<double>>(grid, kVecThreads, Dot<double>::smem_bytes(kVecThreads), st, p);
+    }
+    if (rc) return rc;
+    FinalReduce::Params fp{partials, grid, 1, out_dev};
+    return rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
+}
+
 int nb2_axpby(int dtype, int64_t n, double a, const void* x, double b, void* y, void* stream) {
     if (n < 0 || (n > 0 && (!x || !y))) {
         last_error() = "nb2_axpby: invalid argument";

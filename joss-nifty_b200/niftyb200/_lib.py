@@ -73,6 +73,7 @@ class Library:
         "nb2_tma_launch_count": (c_int64, []),
         "nb2_c2c": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double, c_void_p]),
         "nb2_vdot": (c_int, [c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
+        "nb2_vdot_noalloc": (c_int, [c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
         "nb2_axpby": (c_int, [c_int, c_int64, c_double, c_void_p, c_double, c_void_p, c_void_p]),
         "nb2_cg_update": (c_int, [c_int, c_int64, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p]),
