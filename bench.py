@@ -303,11 +303,12 @@ def setup_problem(nb, torch, subs, offset, lik, tdt, seed=42, slab=False):
     return cf, tab, M, j, x0
 
 
-def verify_slab(nb, torch, dist, rank, world):
+def verify_slab(nb, torch, dist, rank, world, shape=(256, 256, 256)):
     """Pre-timing parity check of a multi-GPU run, OUTSIDE the timed region: a 256^3 fp64 metric apply
     through the same SlabCorrelatedField / PeerExchange code path the timed loop uses, gathered and compared
     on rank 0 with the CPU oracle (the checker: oracle.metric.cf_metric_xi).  Returns the rel-L2 error."""
-    shape = (256, 256, 256)
+    from niftyb200.transforms import device as nb_device
+    dev = nb_device()
     cf0 = make_field(nb, [(shape, CF_KW)], OFFSET, torch.float64)
     cf = nb.SlabCorrelatedField(cf0)
     rng = np.random.default_rng(43)
@@ -315,7 +316,7 @@ def verify_slab(nb, torch, dist, rank, world):
     rng = np.random.default_rng(7)
     w = np.exp(0.3 * rng.standard_normal(shape))
     t = rng.standard_normal(shape)
-    err = torch.zeros(1, dtype=torch.float64, device="cuda")
+    err = torch.zeros(1, dtype=torch.float64, device=dev)
     if rank == 0:
         from oracle import correlated_field as ocf, metric as om, transforms as otr
         otr.set_nthreads(max(1, (os.cpu_count() or 2) // 2))
@@ -341,7 +342,8 @@ def verify_slab(nb, torch, dist, rank, world):
     dist.broadcast(err, src=0)
     cf.close()
     del M, tab, cf, cf0
-    torch.cuda.empty_cache()
+    if dev.type == "cuda":
+        torch.cuda.empty_cache()
     return float(err.item())
 
 

@@ -262,7 +262,8 @@ class SlabHartley:
         barrier, so that no peer is still storing into a buffer that goes away)."""
         if self.peer is not None:
             torch.cuda.synchronize()
-            dist.barrier(group=self.comm.group)
+            self.comm.allreduce_(self.peer.flag)        # barrier on the communicator the exchange uses
+            torch.cuda.synchronize()
             self.peer.close()
             self.peer = None
 

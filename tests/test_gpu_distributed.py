@@ -12,8 +12,7 @@ from test_distributed_cpu import check
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("world,shape", [(2, (64, 64, 64)), (4, (64, 128, 32)), (8, (128, 128, 64)), (4, (256, 256, 128)),
-                                         (8, (256, 256, 256))])
+@pytest.mark.parametrize("world,shape", [(2, (64, 64, 64)), (4, (64, 128, 32)), (8, (128, 128, 64)), (8, (256, 256, 128))])
 def test_slab_peer_exchange(world, shape):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
@@ -22,8 +21,7 @@ def test_slab_peer_exchange(world, shape):
     check(res, strict=False)
 
 
-@pytest.mark.parametrize("world,shape,dtype", [(8, (512, 512, 512), "f32"), (4, (512, 512, 512), "f32"), (2, (256, 256, 256), "f32"),
-                                               (8, (512, 512, 512), "f64")])
+@pytest.mark.parametrize("world,shape,dtype", [(8, (512, 512, 512), "f32"), (4, (256, 256, 256), "f32"), (8, (256, 256, 256), "f64")])
 def test_slab_peer_exchange_large(world, shape, dtype):
     """BASELINE-sized grid: forward / adjoint / metric / back-to-back transforms against the full oracle."""
     if torch.cuda.device_count() < world:
