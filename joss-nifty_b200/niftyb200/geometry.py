@@ -37,12 +37,15 @@ class RGGrid:
             self._build_isotropic()
         else:
             self._build_general()
-        um = self.mode_lengths
-        rel = um.clone()
-        rel[1:] = torch.log(rel[1:])
-        rel[1:] -= rel[1].clone()
+        # O(n_bins) set-up tables, evaluated ONCE per grid on the host in NumPy like the reference does
+        # (re/correlated_field.py:127-132): log_volume is a difference of nearly equal logarithms, which turns
+        # a one-ulp difference of a device `log` into a 1e-9 relative change of the Wiener-process steps
+        um = self.mode_lengths.cpu().numpy().copy()
+        um[1:] = np.log(um[1:])
+        um[1:] -= um[1]
+        rel = torch.from_numpy(um).to(self.device)
         self.relative_log_mode_lengths = rel          # re/correlated_field.py:127-131
-        self.log_volume = rel[2:] - rel[1:-1]         # :132
+        self.log_volume = torch.from_numpy(um[2:] - um[1:-1]).to(self.device)         # :132
 
     # -- isotropic: everything from integer ksq, no N-sized array -------------------
     def _axis_sq(self, n):
@@ -73,8 +76,62 @@ class RGGrid:
         self.ksq_size = int(sum((n // 2) ** 2 for n in self.shape)) + 1
         self.unique_ksq = sq                                   # sorted int64
         self.mode_multiplicity = mult.round().to(torch.int64)  # points per bin
-        self.mode_lengths = torch.sqrt(sq.to(torch.float64)) * self.hdist[0]
         self.nbins = int(sq.numel())
+        self.mode_lengths = self._reference_mode_lengths(sq)
+
+    def _reference_mode_lengths(self, unique_ksq):
+        """Mode length of every bin with the reference's rounding: the reference evaluates
+        ``sqrt(sum_j (min(k_j, N_j - k_j) * h_j)^2)`` in fp64 for every grid point and keeps, per bin, the
+        largest of the (one-ulp apart) values (``rg_space.py:105-116``; ``re/correlated_field.py:55-72``:
+        ``unique`` + the 1e-12 tolerance filter keep the last member of each cluster).  Same here, over the
+        half grid ``0 .. N_j/2`` (the mirrored index takes no other values), slab by slab, with a scatter-max
+        into the ksq table -- no N-sized array."""
+        d = len(self.shape)
+        h = self.hdist
+        if d == 1:
+            return torch.arange(self.shape[0] // 2 + 1, dtype=torch.float64, device=self.device) * h[0]
+        if self.device.type != "cuda":
+            return torch.from_numpy(self._reference_mode_lengths_host(unique_ksq.cpu().numpy())).to(self.device)
+        # CUDA: fp64 sqrt / multiply / add are IEEE-exact there (torch's vectorised CPU sqrt is not)
+        ax = [torch.arange(n // 2 + 1, dtype=torch.int64, device=self.device) for n in self.shape]
+        sq = []
+        for a, hh in zip(ax, h):
+            v = a.to(torch.float64) * hh
+            sq.append(v * v)                                                      # (k * h)^2 per axis
+        table = torch.zeros(self.ksq_size, dtype=torch.float64, device=self.device)
+        rest = int(np.prod([a.numel() for a in ax[1:]]))
+        step = max(1, (1 << 22) // rest)
+        for lo in range(0, ax[0].numel(), step):
+            k0 = ax[0][lo:lo + step]
+            acc_f, acc_i = sq[0][lo:lo + step], k0 * k0
+            for a, f in zip(ax[1:], sq[1:]):                                      # ((f0 + f1) + f2): add.outer order
+                acc_f = acc_f[..., None] + f
+                acc_i = acc_i[..., None] + a * a
+            table.scatter_reduce_(0, acc_i.reshape(-1), torch.sqrt(acc_f).reshape(-1), "amax", include_self=True)
+        return table[unique_ksq]
+
+    def _reference_mode_lengths_host(self, unique_ksq):
+        """NumPy twin of :meth:`_reference_mode_lengths` (CPU tensors: the emulator tests)."""
+        ax = [np.arange(n // 2 + 1, dtype=np.int64) for n in self.shape]
+        sq = []
+        for a, hh in zip(ax, self.hdist):
+            v = a.astype(np.float64) * hh
+            sq.append(v * v)
+        table = np.zeros(self.ksq_size, dtype=np.float64)
+        rest = int(np.prod([a.size for a in ax[1:]]))
+        step = max(1, (1 << 22) // rest)
+        for lo in range(0, ax[0].size, step):
+            k0 = ax[0][lo:lo + step]
+            acc_f, acc_i = sq[0][lo:lo + step], k0 * k0
+            for a, f in zip(ax[1:], sq[1:]):
+                acc_f = np.add.outer(acc_f, f)
+                acc_i = np.add.outer(acc_i, a * a)
+            idx, val = acc_i.ravel(), np.sqrt(acc_f).ravel()
+            order = np.argsort(idx, kind="stable")
+            idx, val = idx[order], val[order]
+            first = np.flatnonzero(np.r_[True, idx[1:] != idx[:-1]])
+            np.maximum.at(table, idx[first], np.maximum.reduceat(val, first))
+        return table[unique_ksq]
 
     def ksq_table(self, amp, dtype):
         """Dense table T[ksq] = amp[bin(ksq)] for the kernels' amp_mode 1."""

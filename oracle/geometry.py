@@ -101,7 +101,22 @@ def fourier_mode_distributor_isotropic(shape, distances):
     uniq = np.nonzero(m_count_all)[0]
     lut = np.zeros(m_count_all.size, dtype=np.int64)
     lut[uniq] = np.arange(uniq.size)
-    return lut[ksq], np.sqrt(uniq.astype(np.float64)) * hd[0], m_count_all[uniq]
+    # mode length of a bin with the reference's rounding: the largest of the fp64 values
+    # sqrt(((k0 h)^2 + (k1 h)^2) + ...) over the bin's points (``unique`` + the tolerance filter of
+    # ``:69-72`` keep the last member of every cluster of nearly equal values); plane by plane
+    um = np.zeros(uniq.size, dtype=np.float64)
+    f = []
+    for n, h in zip(shape, hd):
+        v = np.arange(n, dtype=np.float64)
+        v = np.minimum(v, n - v) * h
+        f.append(v * v)
+    idx = lut[ksq]
+    for i0 in range(shape[0] // 2 + 1):              # planes i0 and n0 - i0 hold the same values
+        acc = f[0][i0]
+        for fj in f[1:]:
+            acc = np.add.outer(acc, fj)
+        np.maximum.at(um, idx[i0].ravel(), np.sqrt(acc).ravel())
+    return idx, um, m_count_all[uniq]
 
 
 _ISOTROPIC_SHORTCUT_SIZE = 1 << 24
