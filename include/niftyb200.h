@@ -83,6 +83,9 @@ typedef struct nb2_pointop {
     const void* pre_add;
     double pre_scale;
     void* pre_out;
+    /* Device-resident conjugate gradient: if not NULL, pre_scale is read from this DEVICE double when the
+     * kernel runs (beta = state[NB2_CG_BETA], see nb2_cg_decide) instead of the host value above. */
+    const double* pre_scale_dev;
 } nb2_pointop;
 
 int nb2_version(void);
@@ -208,6 +211,43 @@ int nb2_axpby(int dtype, int64_t n, double a, const void* x, double b, void* y, 
  *  src/re/conjugate_gradient.py:169-191) */
 int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, const void* q, const void* b,
                   void* x, void* r, double* sums_dev, void* stream);
+
+/* ---- Device-resident conjugate gradient (static_cg, src/re/conjugate_gradient.py:219-389: the reference keeps
+ * the whole loop on the device inside lax.while_loop, :382).  The scalars of the recurrence live in a DEVICE
+ * array `state` of NB2_CG_STATE_SIZE doubles (integers stored as doubles); the kernels of an iteration read
+ * alpha / beta from it and write their reductions into it, and nb2_cg_decide evaluates the reference's
+ * stopping tests on the device (cg_single_step, :266-313).  While `*gate != 0` ("stopped") every kernel this
+ * library launches on the calling thread returns at once (nb2_set_launch_gate), so the host may enqueue
+ * iterations ahead of the decision and poll state[NB2_CG_INFO] only now and then. */
+#define NB2_CG_GAMMA 0        /* r.r of the last completed iteration (:291) */
+#define NB2_CG_ENERGY 1       /* vdot((r - j)/2, pos) (:303) */
+#define NB2_CG_CURV 2         /* d.q of the running iteration: the metric apply's dot_out (:271) */
+#define NB2_CG_ALPHA 3        /* gamma / curv (:274), written by stage 0 */
+#define NB2_CG_BETA 4         /* max(0, gamma_new / gamma_old) (:315), written by stage 1 */
+#define NB2_CG_SUMS 5         /* 5,6,7: r.r, x.r, x.b of nb2_cg_update_dev */
+#define NB2_CG_ITER 8         /* completed iterations i */
+#define NB2_CG_INFO 9         /* -2 running, -1 error, 0 converged, i > 0 iteration limit (:276-313) */
+#define NB2_CG_MINITER 10
+#define NB2_CG_MAXITER 11
+#define NB2_CG_RESNORM 12     /* threshold on sqrt(r.r) (norm_ord 2); < 0: criterion off */
+#define NB2_CG_ABSDELTA 13    /* threshold on the energy decrease; NaN: criterion off */
+#define NB2_CG_EPS 14         /* 6 * finfo.eps  (:259) */
+#define NB2_CG_TINY 15        /* 6 * finfo.tiny (:260) */
+#define NB2_CG_STATE_SIZE 16
+/* stage 0 (after the metric apply): info = -1 if curv == 0; alpha = gamma / curv; info = -1 if alpha < 0.
+ * stage 1 (after nb2_cg_update_dev [and the all-reduce of the sums]): the tests of :292-313 in the reference's
+ * order, beta, iteration count; *gate = (info >= -1).  One thread; asynchronous on `stream`. */
+int nb2_cg_decide(double* state, int* gate, int stage, void* stream);
+/* Every later launch of this library on the calling host thread checks `*gate` on the device first and
+ * returns at once if it is non-zero.  NULL switches the check off.  The pointer must stay valid. */
+int nb2_set_launch_gate(const int* gate);
+/* nb2_cg_update with alpha = state[NB2_CG_ALPHA] read on the device; the sums go to state[NB2_CG_SUMS..]. */
+int nb2_cg_update_dev(int dtype, int64_t n, int mode, double* state, const void* d, const void* q, const void* b,
+                      void* x, void* r, void* stream);
+/* y = (a * *a_dev) x + (b * *b_dev) y with the device factors optional (NULL = 1): `pos -= alpha d` of a reset
+ * step (:277, a = -1, a_dev = &state[NB2_CG_ALPHA]) and the unfused `d = r + beta d` (:315). */
+int nb2_axpby_dev(int dtype, int64_t n, double a, const double* a_dev, const void* x, double b, const double* b_dev,
+                  void* y, void* stream);
 
 /* Host-buffer convenience wrappers (numpy drop-in path): copy in, transform, copy out,
  * synchronous. */

@@ -727,26 +727,32 @@ int nb2_vdot_noalloc(int dtype, int64_t n, const void* a, const void* b, double*
     return rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
 }
 
-int nb2_axpby(int dtype, int64_t n, double a, const void* x, double b, void* y, void* stream) {
+int nb2_axpby_dev(int dtype, int64_t n, double a, const double* a_dev, const void* x, double b, const double* b_dev,
+                  void* y, void* stream) {
     if (n < 0 || (n > 0 && (!x || !y))) {
         last_error() = "nb2_axpby: invalid argument";
         return NB2_ERR_ARG;
     }
-    if (ensure_ctx()) return NB2_ERR_CUDA;
     rt_stream st = (rt_stream)stream;
     const long long grid = vec_grid(n);
     if (dtype == NB2_F32) {
-        Axpby<float>::Params p{(const float*)x, (float*)y, (float)a, (float)b, n, grid};
+        Axpby<float>::Params p{(const float*)x, (float*)y, (float)a, (float)b, n, grid, a_dev, b_dev};
         return rt_launch<Axpby<float>>(grid, kVecThreads, 0, st, p);
     } else if (dtype == NB2_F64) {
-        Axpby<double>::Params p{(const double*)x, (double*)y, a, b, n, grid};
+        Axpby<double>::Params p{(const double*)x, (double*)y, a, b, n, grid, a_dev, b_dev};
         return rt_launch<Axpby<double>>(grid, kVecThreads, 0, st, p);
     }
+    last_error() = "nb2_axpby: invalid dtype";
     return NB2_ERR_ARG;
 }
 
-int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, const void* q, const void* b,
-                  void* x, void* r, double* sums_dev, void* stream) {
+int nb2_axpby(int dtype, int64_t n, double a, const void* x, double b, void* y, void* stream) {
+    return nb2_axpby_dev(dtype, n, a, nullptr, x, b, nullptr, y, stream);
+}
+
+// x -= alpha d, r -= alpha q (mode 0) / r = q - b (mode 1), then the three sums into sums_dev
+static int cg_update_impl(int dtype, int64_t n, int mode, double alpha, const double* alpha_dev, const void* d,
+                          const void* q, const void* b, void* x, void* r, double* sums_dev, void* stream) {
     if (n < 0 || !sums_dev || (mode != 0 && mode != 1) || !x || !r || !q || !b || (mode == 0 && !d)) {
         last_error() = "nb2_cg_update: invalid argument";
         return NB2_ERR_ARG;
@@ -757,18 +763,47 @@ int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, c
     int rc;
     if (dtype == NB2_F32) {
         CgUpdate<float>::Params p{(float*)x, (float*)r, (const float*)d, (const float*)q, (const float*)b,
-                                  (float)alpha, mode, n, ctx().partials, grid};
+                                  (float)alpha, mode, n, ctx().partials, grid, alpha_dev};
         rc = rt_launch<CgUpdate<float>>(grid, kVecThreads, CgUpdate<float>::smem_bytes(kVecThreads), st, p);
     } else if (dtype == NB2_F64) {
         CgUpdate<double>::Params p{(double*)x, (double*)r, (const double*)d, (const double*)q, (const double*)b,
-                                   alpha, mode, n, ctx().partials, grid};
+                                   alpha, mode, n, ctx().partials, grid, alpha_dev};
         rc = rt_launch<CgUpdate<double>>(grid, kVecThreads, CgUpdate<double>::smem_bytes(kVecThreads), st, p);
     } else {
+        last_error() = "nb2_cg_update: invalid dtype";
         return NB2_ERR_ARG;
     }
     if (rc) return rc;
     FinalReduce::Params fp{ctx().partials, grid, 3, sums_dev};
     return rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
+}
+
+int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, const void* q, const void* b,
+                  void* x, void* r, double* sums_dev, void* stream) {
+    return cg_update_impl(dtype, n, mode, alpha, nullptr, d, q, b, x, r, sums_dev, stream);
+}
+
+int nb2_cg_update_dev(int dtype, int64_t n, int mode, double* state, const void* d, const void* q, const void* b,
+                      void* x, void* r, void* stream) {
+    if (!state) {
+        last_error() = "nb2_cg_update_dev: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    return cg_update_impl(dtype, n, mode, 0.0, state + NB2_CG_ALPHA, d, q, b, x, r, state + NB2_CG_SUMS, stream);
+}
+
+int nb2_cg_decide(double* state, int* gate, int stage, void* stream) {
+    if (!state || !gate || (stage != 0 && stage != 1)) {
+        last_error() = "nb2_cg_decide: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    CgDecide::Params p{state, gate, stage};
+    return rt_launch<CgDecide>(1, 32, 0, (rt_stream)stream, p);
+}
+
+int nb2_set_launch_gate(const int* gate) {
+    launch_gate() = gate;
+    return NB2_OK;
 }
 
 int nb2_hartley_host(nb2_plan* pl, const void* in_host, void* out_host, int conv, double scale) {

@@ -165,11 +165,12 @@ struct StridedPass {
                     const long long e0 = base + c + (long long)r * p.inner;
                     const cplx<T>* rs = reinterpret_cast<const cplx<T>*>(p.pro.pre_add) + e0;
                     cplx<T>* dd = p.pro.pre_out ? reinterpret_cast<cplx<T>*>(p.pro.pre_out) + e0 : nullptr;
+                    const T beta = pre_scale_of(p.pro);
                     NB2_UNROLL
                     for (int n1 = 0; n1 < R1; ++n1) {
                         const cplx<T> rr = ldc_stream(rs + (long long)n1 * MM * p.inner);
-                        x[n1].re = rr.re + p.pro.pre_scale * x[n1].re;
-                        x[n1].im = rr.im + p.pro.pre_scale * x[n1].im;
+                        x[n1].re = rr.re + beta * x[n1].re;
+                        x[n1].im = rr.im + beta * x[n1].im;
                         if (dd) stc_stream(dd + (long long)n1 * MM * p.inner, x[n1]);
                     }
                 }

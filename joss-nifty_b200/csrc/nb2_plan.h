@@ -75,6 +75,7 @@ PointOp<T> to_pointop(const nb2_pointop* o, double* partials) {
     r.pre_add = o ? (const T*)o->pre_add : nullptr;
     r.pre_scale = o ? (T)o->pre_scale : T(0);
     r.pre_out = o ? (T*)o->pre_out : nullptr;
+    r.pre_scale_dev = o ? o->pre_scale_dev : nullptr;
     return r;
 }
 

@@ -38,7 +38,12 @@ struct PointOp {
     const T* pre_add;
     T pre_scale;
     T* pre_out;
+    const double* pre_scale_dev;   // device-resident CG: beta read on the device when not NULL
 };
+
+template <typename T> NB2_HD T pre_scale_of(const PointOp<T>& op) {
+    return op.pre_scale_dev ? T(*op.pre_scale_dev) : op.pre_scale;
+}
 
 NB2_HD void atomic_add_f64(double* p, double v) {
 #if defined(__CUDA_ARCH__)

@@ -130,6 +130,7 @@ struct StridedTma {
             cplx<T>* dd = p.pro.pre_out ? reinterpret_cast<cplx<T>*>(p.pro.pre_out) + e0 : nullptr;
             const cplx<T>* F = reinterpret_cast<const cplx<T>*>(Fraw);
             cplx<T> rr[2][PB];
+            const T beta = pre_scale_of(p.pro);
             NB2_UNROLL
             for (int i = 0; i < PB; ++i) rr[0][i] = R.f0[i];
             NB2_UNROLL
@@ -142,8 +143,8 @@ struct StridedTma {
                 for (int i = 0; i < PB; ++i) {
                     const int n1 = g * PB + i, row = r + n1 * MM;
                     cplx<T> v = P[(row << LOGW) + c];
-                    v.re = rr[g & 1][i].re + p.pro.pre_scale * v.re;
-                    v.im = rr[g & 1][i].im + p.pro.pre_scale * v.im;
+                    v.re = rr[g & 1][i].re + beta * v.re;
+                    v.im = rr[g & 1][i].im + beta * v.im;
                     if (dd) stc_stream(dd + n1 * rstride, v);
                     if (p.fx) {
                         const cplx<T> f = F[((row <= N - row ? row : N - row) << LOGW) + c];

@@ -15,6 +15,7 @@
 // src/utilities.py:331-390).
 #pragma once
 
+#include "../../include/niftyb200.h"
 #include "nb2_common.cuh"
 #include "nb2_pointwise.cuh"
 
@@ -82,6 +83,7 @@ struct CgUpdate {
         long long n;
         double* partials;  // 3 per CTA
         long long nctas;
+        const double* alpha_dev;   // device-resident CG: alpha read on the device when not NULL
     };
     static size_t smem_bytes(int nthreads) { return size_t(3) * nthreads * sizeof(double); }
     NB2_HDC static bool enabled(int) { return true; }
@@ -91,6 +93,7 @@ struct CgUpdate {
         double* red = reinterpret_cast<double*>(smem_raw);
         if (PH == 0) {
             double s0 = 0, s1 = 0, s2 = 0;
+            const T alpha = p.alpha_dev ? T(*p.alpha_dev) : p.alpha;
             const long long stride = p.nctas * nthreads;
             const long long n4 = all_aligned16(p.x, p.r, p.d, p.q, p.b) ? p.n / 4 : 0;
             for (long long v = bid * nthreads + tid; v < n4; v += stride) {
@@ -102,8 +105,8 @@ struct CgUpdate {
                     const vec4<T> dv = ld4_stream(p.d + i), qv = ld4_stream(p.q + i);
                     NB2_UNROLL
                     for (int e = 0; e < 4; ++e) {
-                        xv.v[e] -= p.alpha * dv.v[e];
-                        rv.v[e] -= p.alpha * qv.v[e];
+                        xv.v[e] -= alpha * dv.v[e];
+                        rv.v[e] -= alpha * qv.v[e];
                     }
                     st4_stream(p.x + i, xv);
                 } else {
@@ -126,8 +129,8 @@ struct CgUpdate {
             for (long long i = 4 * n4 + bid * nthreads + tid; i < p.n; i += stride) {
                 T xv, rv;
                 if (p.mode == 0) {
-                    xv = ld_stream(p.x + i) - p.alpha * ld_stream(p.d + i);
-                    rv = ld_stream(p.r + i) - p.alpha * ld_stream(p.q + i);
+                    xv = ld_stream(p.x + i) - alpha * ld_stream(p.d + i);
+                    rv = ld_stream(p.r + i) - alpha * ld_stream(p.q + i);
                     st_stream(p.x + i, xv);
                 } else {
                     xv = ld_stream(p.x + i);
@@ -163,11 +166,16 @@ struct Axpby {
         T a, b;
         long long n;
         long long nctas;
+        const double* a_dev;   // optional device factors (device-resident CG): a *= *a_dev, b *= *b_dev
+        const double* b_dev;
     };
     static size_t smem_bytes(int) { return 0; }
     NB2_HDC static bool enabled(int) { return true; }
     template <int PH>
-    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+    NB2_HD static void phase(const Params& q, long long bid, int tid, int nthreads, char*) {
+        Params p = q;
+        if (q.a_dev) p.a = T(double(q.a) * *q.a_dev);
+        if (q.b_dev) p.b = T(double(q.b) * *q.b_dev);
         const long long stride = p.nctas * nthreads;
         const long long n4 = all_aligned16(p.x, p.y) ? p.n / 4 : 0;
         for (long long v = bid * nthreads + tid; v < n4; v += stride) {
@@ -267,6 +275,61 @@ struct FinalReduce {
                 for (int v = 0; v < p.nv; ++v) p.out[v] = tmp[v];
 #endif
         }
+    }
+};
+
+// ---------------------------------------------------------------- device-resident CG: the scalar logic of one step
+// cg_single_step of the reference (src/re/conjugate_gradient.py:266-313), evaluated by one thread on the
+// scalars in `state` (layout: NB2_CG_* of include/niftyb200.h).  Comparisons involving NaN are false, as
+// with jnp.where.
+struct CgDecide {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 32;
+    static constexpr int MIN_BLOCKS = 1;
+    struct Params {
+        double* state;
+        int* gate;
+        int stage;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int, char*) {
+        if (bid != 0 || tid != 0) return;
+        double* s = p.state;
+        double info = s[NB2_CG_INFO];
+        if (p.stage == 0) {
+            const double curv = s[NB2_CG_CURV];
+            if (curv == 0.0) info = -1;                                   // :272-273
+            const double alpha = s[NB2_CG_GAMMA] / curv;                  // :274
+            if (alpha < 0.0) info = -1;                                   // :275-276
+            s[NB2_CG_ALPHA] = alpha;
+            s[NB2_CG_INFO] = info;
+            return;
+        }
+        const double i = s[NB2_CG_ITER] + 1.0;                            // :269
+        const double previous_gamma = s[NB2_CG_GAMMA], previous_energy = s[NB2_CG_ENERGY];
+        const double gamma = s[NB2_CG_SUMS], xr = s[NB2_CG_SUMS + 1], xb = s[NB2_CG_SUMS + 2];
+        const double miniter = s[NB2_CG_MINITER], maxiter = s[NB2_CG_MAXITER];
+        if (gamma >= 0.0 && gamma <= s[NB2_CG_TINY] && info != -1) info = 0;            // :292-294
+        if (s[NB2_CG_RESNORM] >= 0.0) {                                                  // :295-299 (norm_ord 2)
+            if (sqrt(gamma) < s[NB2_CG_RESNORM] && i >= miniter && info != -1) info = 0;
+        }
+        const double energy = 0.5 * (xr - xb);                                           // :303
+        const double energy_diff = previous_energy - energy;
+        if (energy_diff < -s[NB2_CG_EPS] * fabs(energy)) info = -1;                      // :305-307
+        const double absdelta = s[NB2_CG_ABSDELTA];
+        if (absdelta == absdelta) {                                                      // :308-312
+            if (energy_diff < absdelta && i >= miniter && info != -1) info = 0;
+        }
+        if (i >= maxiter && info != -1) info = i;                                        // :313
+        const double ratio = gamma / previous_gamma;
+        s[NB2_CG_BETA] = ratio > 0.0 ? ratio : (ratio != ratio ? ratio : 0.0);           // jnp.maximum(0, .) :315
+        s[NB2_CG_GAMMA] = gamma;
+        s[NB2_CG_ENERGY] = energy;
+        s[NB2_CG_ITER] = i;
+        s[NB2_CG_INFO] = info;
+        *p.gate = info >= -1.0 ? 1 : 0;                                                  // continue_condition :263-264
     }
 };
 

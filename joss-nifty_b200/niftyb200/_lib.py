@@ -12,6 +12,9 @@ import os
 from ctypes import POINTER, c_char_p, c_double, c_int, c_int32, c_int64, c_void_p
 
 F32, F64 = 0, 1
+# layout of the device-resident CG state (NB2_CG_* of include/niftyb200.h)
+CG_GAMMA, CG_ENERGY, CG_CURV, CG_ALPHA, CG_BETA, CG_SUMS, CG_ITER, CG_INFO = 0, 1, 2, 3, 4, 5, 8, 9
+CG_MINITER, CG_MAXITER, CG_RESNORM, CG_ABSDELTA, CG_EPS, CG_TINY, CG_STATE_SIZE = 10, 11, 12, 13, 14, 15, 16
 NONCANONICAL, CANONICAL = 0, 1
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -36,6 +39,7 @@ class PointOp(ctypes.Structure):
         ("pre_add", c_void_p),
         ("pre_scale", c_double),
         ("pre_out", c_void_p),
+        ("pre_scale_dev", c_void_p),
     ]
 
 
@@ -77,6 +81,11 @@ class Library:
         "nb2_axpby": (c_int, [c_int, c_int64, c_double, c_void_p, c_double, c_void_p, c_void_p]),
         "nb2_cg_update": (c_int, [c_int, c_int64, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p]),
+        "nb2_cg_decide": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+        "nb2_set_launch_gate": (c_int, [c_void_p]),
+        "nb2_cg_update_dev": (c_int, [c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_void_p]),
+        "nb2_axpby_dev": (c_int, [c_int, c_int64, c_double, c_void_p, c_void_p, c_double, c_void_p, c_void_p, c_void_p]),
         "nb2_hartley_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double]),
         "nb2_c2c_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_double]),
         "nb2_vdot_host": (c_int, [c_int, c_int64, c_void_p, c_void_p, c_void_p]),

@@ -433,12 +433,23 @@ def static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, to
 
 
 def _static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, tol=1e-5, atol=0.0, miniter=None,
-               maxiter=None, name=None, history=None, **kwargs):
+               maxiter=None, name=None, history=None, device_resident=None, poll=4, **kwargs):
     """``_static_cg`` (re/conjugate_gradient.py:219-389): the body of ``cg_single_step``
     (``:266-338``) with the same ``info`` bookkeeping (-2 running, -1 error, 0 converged,
-    i > 0 iteration limit); the while-loop runs on the host, the state stays on the device."""
+    i > 0 iteration limit).
+
+    Device-resident by default, like the reference's ``lax.while_loop`` (:382): scalars, stopping tests and
+    alpha / beta stay on the device (:class:`_DeviceCG`), the host polls ``info`` every ``poll`` iterations.
+    The host-driven loop below (one read-back of 4 scalars per iteration) is used when per-iteration values
+    are wanted on the host (``history``, ``name`` = logging, as the reference's host callback :317-327), for
+    ``norm_ord != 2`` and for operators without ``apply_with_curvature``."""
     norm_ord, miniter, maxiter, resnorm, eps, tiny = _defaults(j, miniter, maxiter, absdelta, resnorm, norm_ord,
                                                                tol, atol, getattr(mat, "comm", None))
+    if device_resident is None:
+        device_resident = (history is None and name is None and norm_ord == 2
+                           and hasattr(mat, "apply_with_curvature") and getattr(mat, "device_resident_cg", False))
+    if device_resident:
+        return _DeviceCG(mat, j, x0, miniter, maxiter, resnorm, absdelta, eps, tiny, poll=poll).run()
     vec, pos, r, d, q, energy, nfev, gamma = _cg_setup(mat, j, x0)
     info, i = (0 if gamma == 0.0 else -2), 0
     pending = None    # deferred direction update (r, beta): done with the next mat(d)
@@ -481,19 +492,157 @@ def _static_cg(mat, j, x0=None, *, absdelta=None, resnorm=None, norm_ord=None, t
     return CGResults(pos, i, nfev, info, info == 0)
 
 
+# ---------------------------------------------------------------- device-resident static_cg
+class _DeviceCG:
+    """The reference's ``lax.while_loop`` CG (re/conjugate_gradient.py:219-389) with the loop state on the
+    device: the scalars of the recurrence live in a device array (``nb2_cg_decide``), alpha / beta are read
+    from it by the update kernels and the fused first pass, and the stopping tests run in a one-thread kernel.
+    The host only enqueues iterations and polls ``info`` every ``poll`` iterations; iterations enqueued
+    past the stopping decision are no-ops (launch gate).  On a single GPU the regular iteration is captured
+    once as a CUDA graph and replayed."""
+
+    def __init__(self, mat, j, x0, miniter, maxiter, resnorm, absdelta, eps, tiny, poll=4, use_graph=None):
+        self.mat, self.j = mat, j
+        self.lib = lib = _lib.get()
+        self.comm = getattr(mat, "comm", None)
+        self.vec, self.pos, self.r, self.d, self.q, energy, self.nfev0, gamma = _cg_setup(mat, j, x0)
+        self.code, self.n = self.vec.code, self.vec.n
+        dev = j.device
+        st = np.zeros(_lib.CG_STATE_SIZE)
+        st[_lib.CG_GAMMA], st[_lib.CG_ENERGY] = gamma, energy
+        st[_lib.CG_INFO] = 0 if gamma == 0.0 else -2                   # :363-366
+        st[_lib.CG_MINITER], st[_lib.CG_MAXITER] = miniter, maxiter
+        st[_lib.CG_RESNORM] = -1.0 if resnorm is None else resnorm
+        st[_lib.CG_ABSDELTA] = np.nan if absdelta is None else absdelta
+        st[_lib.CG_EPS], st[_lib.CG_TINY] = eps, tiny
+        self.state = torch.from_numpy(st).to(dev)
+        self.gate = torch.zeros(1, dtype=torch.int32, device=dev)
+        if gamma == 0.0:
+            self.gate.fill_(1)
+        self.curv = self.state[_lib.CG_CURV:_lib.CG_CURV + 1]
+        self.beta = self.state[_lib.CG_BETA:_lib.CG_BETA + 1]
+        self.alpha = self.state[_lib.CG_ALPHA:_lib.CG_ALPHA + 1]
+        self.sums = self.state[_lib.CG_SUMS:_lib.CG_SUMS + 3]
+        self.fused = getattr(mat, "fused_direction_update", False)
+        self.poll = max(1, int(poll))
+        if use_graph is None:
+            use_graph = dev.type == "cuda" and self.comm is None
+        self.use_graph, self.graph = use_graph, None
+        self.miniter, self.maxiter = int(miniter), int(maxiter)
+        self.i = 0                       # iterations enqueued so far
+        self.graph_kernels = 0           # kernels inside the captured iteration
+        self.replayed_kernels = 0        # kernels launched through graph replays (not seen by nb2_launch_count)
+
+    def _decide(self, stage):
+        lib = self.lib
+        lib.check(lib.nb2_cg_decide(_ptr(lib, self.state), _ptr(lib, self.gate), stage, _stream(self.state)),
+                  "nb2_cg_decide")
+
+    def _iteration(self, i):
+        """Enqueue iteration ``i`` (1-based); nothing is read back."""
+        lib, mat, j = self.lib, self.mat, self.j
+        pending = i > 1                                   # d <- r + beta d of the previous iteration (:315)
+        if pending and not self.fused:
+            lib.check(lib.nb2_axpby_dev(self.code, self.n, 1.0, None, _ptr(lib, self.r), 1.0, _ptr(lib, self.beta),
+                                        _ptr(lib, self.d), _stream(self.d)), "nb2_axpby_dev")
+        pre = (self.r, self.beta) if (pending and self.fused) else None
+        if pre is not None:
+            mat.apply_with_curvature(self.d, out=self.q, pre=pre, curv_out=self.curv)     # :270-271
+        else:
+            mat.apply_with_curvature(self.d, out=self.q, curv_out=self.curv)
+        self._decide(0)                                   # alpha = gamma / curv (:272-276)
+        if i % N_RESET == 0:                              # :277-290 exact residual
+            lib.check(lib.nb2_axpby_dev(self.code, self.n, -1.0, _ptr(lib, self.alpha), _ptr(lib, self.d), 1.0, None,
+                                        _ptr(lib, self.pos), _stream(self.pos)), "nb2_axpby_dev")
+            _apply(mat, self.pos, self.q)
+            mode = 1
+        else:
+            mode = 0
+        lib.check(lib.nb2_cg_update_dev(self.code, self.n, mode, _ptr(lib, self.state), _ptr(lib, self.d),
+                                        _ptr(lib, self.q), _ptr(lib, j), _ptr(lib, self.pos), _ptr(lib, self.r),
+                                        _stream(self.pos)), "nb2_cg_update_dev")
+        if self.comm is not None:
+            self.comm.allreduce_(self.sums)
+        self._decide(1)                                   # :291-315 + continue_condition
+
+    def _regular(self, i):
+        """Iterations with the pending update and no reset are identical launches: replay a graph."""
+        if not self.use_graph:
+            return self._iteration(i)
+        if self.graph is None:
+            n0 = self.lib.nb2_launch_count()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._iteration(i)
+            self.graph, self.graph_kernels = g, int(self.lib.nb2_launch_count() - n0)
+        self.graph.replay()
+        self.replayed_kernels += self.graph_kernels
+
+    def enqueue(self, n):
+        """Enqueue the next ``n`` iterations without reading anything back."""
+        for _ in range(n):
+            self.i += 1
+            if self.i > 1 and self.i % N_RESET != 0:
+                self._regular(self.i)
+            else:
+                self._iteration(self.i)
+
+    def run(self):
+        lib = self.lib
+        info = int(self.state[_lib.CG_INFO].item())
+        lib.check(lib.nb2_set_launch_gate(_ptr(lib, self.gate)), "nb2_set_launch_gate")
+        try:
+            while info < -1 and self.i < self.maxiter:
+                self.enqueue(1)
+                # nothing but an error can stop the loop before miniter: poll from there on
+                if self.i >= min(self.miniter, self.maxiter) and (self.i % self.poll == 0 or self.i == self.maxiter):
+                    info = int(self.state[_lib.CG_INFO].item())
+        finally:
+            lib.nb2_set_launch_gate(None)
+        st = self.state.cpu().numpy()
+        nit, info = int(st[_lib.CG_ITER]), int(st[_lib.CG_INFO])
+        nfev = self.nfev0 + nit + nit // N_RESET
+        return CGResults(self.pos, nit, nfev, info, info == 0)
+
+
 class CGLoop:
     """The CG recurrence with the stopping tests taken out: ``run(n)`` executes exactly ``n``
-    iterations with the same primitives as :func:`_cg` (metric apply with fused curvature,
+    iterations with the same primitives as the solvers (metric apply with fused curvature,
     fused update + sums, direction update; exact residual every ``N_RESET`` iterations).
-    Used by ``bench.py`` / profiling, where a fixed amount of work has to be timed."""
+    Used by ``bench.py`` / profiling, where a fixed amount of work has to be timed.
 
-    def __init__(self, mat, j, x0=None):
+    ``device_resident`` (default when the operator allows it): the loop of :func:`static_cg` -- scalars on the
+    device, nothing read back, the regular iteration replayed as a CUDA graph on a single GPU; ``run`` only
+    enqueues.  Otherwise the host-driven loop of :func:`cg` (4 scalars read back per iteration)."""
+
+    def __init__(self, mat, j, x0=None, device_resident=None):
         self.mat, self.j = mat, j
+        if device_resident is None:
+            device_resident = hasattr(mat, "apply_with_curvature") and getattr(mat, "device_resident_cg", False)
+        self.dev = None
+        if device_resident:
+            # every criterion off: only an error (non-positive curvature, energy increase) could stop it
+            self.dev = _DeviceCG(mat, j, x0, 2 ** 40, 2 ** 40, None, None, 0.0, 0.0)
+            self.dev.state[_lib.CG_EPS] = float("inf")
+            self.vec, self.pos, self.r, self.d, self.q = self.dev.vec, self.dev.pos, self.dev.r, self.dev.d, self.dev.q
+            return
         (self.vec, self.pos, self.r, self.d, self.q, self.energy, self.nfev, self.gamma) = _cg_setup(mat, j, x0)
         self.i = 0
         self.pending = None    # deferred direction update (r, beta), applied with the next metric apply
 
+    @property
+    def replayed_kernels(self):
+        return self.dev.replayed_kernels if self.dev is not None else 0
+
     def run(self, n):
+        if self.dev is not None:
+            lib = self.dev.lib
+            lib.check(lib.nb2_set_launch_gate(_ptr(lib, self.dev.gate)), "nb2_set_launch_gate")
+            try:
+                self.dev.enqueue(n)
+            finally:
+                lib.nb2_set_launch_gate(None)
+            return self
         mat, vec, j = self.mat, self.vec, self.j
         for _ in range(n):
             self.i += 1

@@ -286,7 +286,11 @@ class CorrelatedField:
         if pre is not None:
             if not self.fuses_direction_update:
                 raise ValueError("this field's transform cannot carry the fused direction update")
-            pro.pre_add, pro.pre_scale, pro.pre_out = pre[0], float(pre[1]), xi
+            pro.pre_add, pro.pre_out = pre[0], xi
+            if isinstance(pre[1], torch.Tensor):       # beta lives on the device (device-resident CG)
+                pro.pre_scale_dev = pre[1]
+            else:
+                pro.pre_scale = float(pre[1])
         if self.single:
             return self.plans[0].hartley(xi, out=out, convention=convention, pro=pro,
                                          epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))

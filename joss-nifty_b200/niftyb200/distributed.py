@@ -352,7 +352,11 @@ class SlabCorrelatedField:
         out = torch.empty(self.position_shape, dtype=self.dtype, device=self.device) if out is None else out
         pro = PointOp(2, tab.amp, 1.0)
         if pre is not None:
-            pro.pre_add, pro.pre_scale, pro.pre_out = pre[0], float(pre[1]), xi
+            pro.pre_add, pro.pre_out = pre[0], xi
+            if isinstance(pre[1], torch.Tensor):       # beta lives on the device (device-resident CG)
+                pro.pre_scale_dev = pre[1]
+            else:
+                pro.pre_scale = float(pre[1])
         return self.ht.x_to_y(xi, out, convention, pro=pro,
                               epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))
 

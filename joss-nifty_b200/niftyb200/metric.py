@@ -51,6 +51,9 @@ class CFMetric:
         self._curv = torch.zeros((), dtype=torch.float64, device=cf.device)
         self.shape, self.dtype, self.device = self.latent_shape, cf.dtype, cf.device
         self.napply = 0
+        # apply_with_curvature(curv_out=..., pre=(r, device beta)) makes no host read-back: static_cg may keep
+        # its whole loop on the device
+        self.device_resident_cg = True
         # the CG loops hand their pending direction update d <- r + beta d to apply_with_curvature(pre=...)
         # (NIFTYB200_FUSED_AXPBY=0: keep the separate axpby kernel -- A/B measurements)
         self.fused_direction_update = (bool(getattr(cf, "fuses_direction_update", False))
@@ -67,15 +70,16 @@ class CFMetric:
         u = self.forward_weighted(t, self._u)
         return self.cf.adjoint_xi(u, self.tab, out=out, convention=self.convention, add=t)
 
-    def apply_with_curvature(self, t, out=None, pre=None):
+    def apply_with_curvature(self, t, out=None, pre=None, curv_out=None):
         """Returns ``(M t, t.(M t))``; the dot product is fused into the last store.  The
-        curvature is a 0-d fp64 device tensor.  ``pre = (r, beta)``: ``t <- r + beta t`` in place first
-        (fused into the first pass; only when :attr:`fused_direction_update`)."""
+        curvature is a 0-d fp64 device tensor (``curv_out``: where to put it, e.g. a slot of the
+        device-resident CG state).  ``pre = (r, beta)``: ``t <- r + beta t`` in place first (fused into the
+        first pass; only when :attr:`fused_direction_update`); ``beta`` may be a 1-element fp64 device tensor."""
         self.napply += 1
+        curv = self._curv if curv_out is None else curv_out
         u = self.forward_weighted(t, self._u, pre)
-        q = self.cf.adjoint_xi(u, self.tab, out=out, convention=self.convention, add=t, dot=t,
-                               dot_out=self._curv)
-        return q, self._curv
+        q = self.cf.adjoint_xi(u, self.tab, out=out, convention=self.convention, add=t, dot=t, dot_out=curv)
+        return q, curv
 
     def sample_rhs(self, white_data, white_prior, out=None):
         """``j = J^T sqrt(w) eta + x0`` of ``draw_linear_residual`` (src/re/evi.py:114-125)."""

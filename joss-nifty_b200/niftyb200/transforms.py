@@ -81,7 +81,7 @@ class PointOp:
 
     def __init__(self, amp_mode=0, amp=None, scale=1.0, mul=None, add=None, add_scalar=0.0,
                  dot=None, dot_out=None, bin_x=None, bin_out=None, amp_sym=False, pre_add=None, pre_scale=0.0,
-                 pre_out=None):
+                 pre_out=None, pre_scale_dev=None):
         self.amp_mode, self.amp, self.scale = int(amp_mode), amp, float(scale)
         self.amp_sym = bool(amp_sym)      # NB2_AMP_SYMMETRIC: amp_mode-2 field with field[k] == field[-k]
         self.mul, self.add, self.add_scalar = mul, add, float(add_scalar)
@@ -89,6 +89,7 @@ class PointOp:
         self.bin_x, self.bin_out = bin_x, bin_out
         # prologue only: in' = pre_add + pre_scale * in (stored to pre_out), the fused CG direction update
         self.pre_add, self.pre_scale, self.pre_out = pre_add, float(pre_scale), pre_out
+        self.pre_scale_dev = pre_scale_dev     # 1-element fp64 device tensor: pre_scale read on the device
 
     def to_c(self, lib):
         c = _lib.PointOp()
@@ -106,6 +107,7 @@ class PointOp:
         c.pre_add = _ptr(lib, self.pre_add, "pre_add")
         c.pre_scale = self.pre_scale
         c.pre_out = _ptr(lib, self.pre_out, "pre_out")
+        c.pre_scale_dev = _ptr(lib, self.pre_scale_dev, "pre_scale_dev")
         return c
 
 

@@ -90,6 +90,13 @@ def run(rank, world, port, backend, emu_path, shape, result, mode="full", dtype=
             j = om.linear_sample_rhs(co, amps_o, azm_o, f64(w), rng.normal(size=shape), f64(x0)).astype(dt)
             kw = dict(absdelta=1e-5 * j.size, maxiter=60)
             r = cgm._cg(M, ht.scatter_x(j), ht.scatter_x(x0), **kw)
+            # device-resident static_cg on the slab-decomposed vectors (sums all-reduced on the stream) against
+            # its host-driven twin: identical counts on every rank
+            sd = cgm._static_cg(M, ht.scatter_x(j), ht.scatter_x(x0), **kw)
+            sh = cgm._static_cg(M, ht.scatter_x(j), ht.scatter_x(x0), device_resident=False, **kw)
+            assert tuple(sd[1:]) == tuple(sh[1:]), (rank, tuple(sd[1:]), tuple(sh[1:]))
+            out.update(static=(sd.nit, sd.info, sd.nfev), err_static=float(torch.linalg.vector_norm(sd.x - sh.x)
+                                                                         / torch.linalg.vector_norm(sh.x)))
             got = ht.gather_x(r.x)
             if rank == 0:
                 ro = ocg.cg_re(Mo, f64(j), f64(x0), **kw)

@@ -562,6 +562,42 @@ def check_cg_parity(shape, dist, strict=True):
             assert abs(e.value - eo.value) <= (1e-10 if strict else htol) * abs(eo.value)
 
 
+def check_static_cg_device_resident(shape, dist, dt=np.float64, likelihood="gaussian"):
+    """The device-resident ``static_cg`` (scalars, stopping tests, alpha / beta on the device; iterations enqueued
+    ahead of the decision and gated) against the host-driven loop of the same kernels: identical nit / info /
+    nfev and the same solution, for every stopping rule, across the exact-residual step at iteration 20, for
+    several polling intervals, with x0 = None, and for the failure codes."""
+    M, Mo, j, x0 = metric_pair(shape, dist, dt, kw=GENTLE_KW, likelihood=likelihood)
+    jt, xt = dev(j), dev(x0)
+    n = j.size
+    tol = 1e-12 if dt == np.float64 else 1e-5
+    for kw in (dict(absdelta=1e-5 * n, maxiter=100), dict(resnorm=1e-4 * float(np.linalg.norm(j)), maxiter=100),
+               dict(absdelta=1e-12, maxiter=27), dict(), dict(absdelta=0.0, miniter=3, maxiter=41)):
+        h = cgm._static_cg(M, jt, xt, device_resident=False, **kw)
+        for poll in (1, 4, 7):
+            s = cgm._static_cg(M, jt, xt, poll=poll, **kw)
+            assert tuple(s[1:]) == tuple(h[1:]), (shape, dt, kw, poll, tuple(s[1:]), tuple(h[1:]))
+            assert rel(host(s.x), host(h.x)) <= tol, (shape, dt, kw, poll)
+    s, h = cgm._static_cg(M, jt, None, absdelta=1e-7 * n), cgm._static_cg(M, jt, None, absdelta=1e-7 * n, device_resident=False)
+    assert tuple(s[1:]) == tuple(h[1:]) and rel(host(s.x), host(h.x)) <= tol
+    # the public entry point takes the device-resident path by itself for a CFMetric
+    x, info = nb.static_cg(M, jt, xt, absdelta=1e-5 * n, maxiter=100)
+    assert info == 0 and rel(host(x), host(cgm._static_cg(M, jt, xt, absdelta=1e-5 * n, maxiter=100, device_resident=False).x)) <= tol
+
+    class Neg:          # not positive definite: info = -1 after the first step (:272-276), on the device
+        device_resident_cg = True
+
+        def apply_with_curvature(self, t, out=None, pre=None, curv_out=None):
+            out.copy_(-t)
+            curv_out.copy_(-(t.double() * t.double()).sum().reshape(1))
+            return out, curv_out
+
+        def __call__(self, t, out=None):
+            return -t
+    r = cgm._static_cg(Neg(), jt, None)
+    assert (r.info, r.nit) == (-1, 1)
+
+
 def check_cg_failure_modes():
     """Non-positive-definite operator: same error behaviour as the reference
     (re/conjugate_gradient.py:151-167,276-279; conjugate_gradient.py:86-96)."""

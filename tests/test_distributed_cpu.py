@@ -11,6 +11,7 @@ def check(res, strict=True):
         assert res[k] <= tol, (k, res)
     if "nit" not in res:
         return
+    assert res["err_static"] <= tol, res           # device-resident static_cg == host-driven static_cg
     if strict:
         assert res["nit"][0] == res["nit"][1] and res["nfev"][0] == res["nfev"][1], res
     else:   # a stopping iteration consistent with the reference's own sensitivity (parity_cases.acceptable_stops)

@@ -105,6 +105,12 @@ def test_metric_poissonian(shape):
     pc.check_metric(shape, dist, np.float32, "poisson")
 
 
+@pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((128, 128), 1 / 128), ((64, 64, 64), 1 / 64), ((256, 8, 256), (1 / 256, 1 / 8, 1 / 256))])
+def test_static_cg_device_resident(shape, dist):
+    pc.check_static_cg_device_resident(shape, dist)
+    pc.check_static_cg_device_resident(shape, dist, np.float32, "poisson" if len(shape) == 2 else "gaussian")
+
+
 def test_cg_failure_modes():
     pc.check_cg_failure_modes()
 
