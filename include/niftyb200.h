@@ -104,6 +104,9 @@ int nb2_plan_is_fast(const nb2_plan* plan);
  * space x frequency field: HarmonicTransformOperator(..., space=0),
  * src/library/correlated_fields.py:790-793): strided passes + one mirror-combine pass. */
 int nb2_plan_kind(const nb2_plan* plan);
+/* 1 if nb2_c2c runs on the fast path: trailing 1..3 power-of-two axes with rows of 2..8192 complex numbers
+ * (the strided passes + the contiguous-axis c2c kernel); 0: the generic O(n^2)-per-axis path */
+int nb2_plan_is_c2c_fast(const nb2_plan* plan);
 /* Mirror rule of the contiguous (row) pass for slab-decomposed grids: the Hartley partner of
  * row (k0,k1) is ((N0-k0-shift0) mod N0, (N1-k1-shift1) mod N1).  0 = index negation (a full
  * axis, default); 1 = pure reflection (the mirror-symmetric local part of a distributed axis,

@@ -4,6 +4,7 @@
 // same file builds the sequential thread emulator used by the CPU-only index tests.
 #include <mutex>
 
+#include "nb2_c2c.cuh"
 #include "nb2_generic.cuh"
 #include "nb2_plan.h"
 #include "nb2_passes.cuh"
@@ -274,9 +275,48 @@ int hartley_generic(nb2_plan* pl, const void* in, void* out, int conv, const nb2
     return rc;
 }
 
+// c2c over trailing power-of-two axes: the strided passes as they are (complex FFTs over rows of complex
+// columns) + the contiguous-axis kernel of nb2_c2c.cuh.  Backward: conj(fft(conj(x))) -- one conjugation
+// sweep in front when a strided pass comes first, the last conjugation and the scale on the last store.
+template <typename T>
+int c2c_fast(nb2_plan* pl, const void* in, void* out, int forward, double scale, rt_stream st) {
+    int rc;
+    const Geom& g = pl->gc;
+    if (!pl->ctwr) {
+        if (g.logN0 && (rc = upload_table<T>(&pl->ctw0, 1ll << g.logN0, 1ll << g.logN0))) return rc;
+        if (g.logN1 && (rc = upload_table<T>(&pl->ctw1, 1ll << g.logN1, 1ll << g.logN1))) return rc;
+        if ((rc = upload_table<T>(&pl->ctwr, 1ll << g.logM, 1ll << g.logM))) return rc;
+    }
+    nb2_plan view = *pl;          // the strided passes read geometry and tables from the plan: complex-row view
+    view.g = g;
+    view.tw0 = pl->ctw0;
+    view.tw1 = pl->ctw1;
+    view.fast = true;
+    const bool strided = g.logN0 > 0 || g.logN1 > 0;
+    const void* cur = in;
+    const long long total = g.batch << (g.logN0 + g.logN1 + g.logM);
+    if (!forward && strided) {
+        const long long grid = vec_grid(total);
+        typename CplxConjScale<T>::Params cp{(const cplx<T>*)in, (cplx<T>*)out, T(1), 1, total, grid};
+        if ((rc = rt_launch<CplxConjScale<T>>(grid, kVecThreads, 0, st, cp))) return rc;
+        cur = out;
+    }
+    if (g.logN0 > 0) {
+        if ((rc = run_strided<T>(&view, 0, cur, out, nullptr, st))) return rc;
+        cur = out;
+    }
+    if (g.logN1 > 0) {
+        if ((rc = run_strided<T>(&view, 1, cur, out, nullptr, st))) return rc;
+        cur = out;
+    }
+    return run_rows_c2c<T>(cur, out, pl->ctwr, g.logM, total >> g.logM, (!forward && !strided) ? 1 : 0, forward ? 0 : 1,
+                           scale, st);
+}
+
 template <typename T>
 int c2c_impl(nb2_plan* pl, const void* in, void* out, int forward, double scale, rt_stream st) {
     int rc;
+    if (pl->cfast) return c2c_fast<T>(pl, in, out, forward, scale, st);
     if ((rc = ensure_work<T>(pl))) return rc;
     if ((rc = rt_d2d(pl->work0, in, pl->total * sizeof(cplx<T>), st))) return rc;
     cplx<T>* res = nullptr;
@@ -392,6 +432,29 @@ int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* ax
         if (fast && size_t(2 * pitch_of(pl->g.logM)) * es + 2048 > kSmemLimit) fast = false;
     }
     pl->fast = fast;
+    // ---- complex-to-complex fast path: trailing 1..3 power-of-two axes, rows of 2..8192 complex numbers
+    {
+        bool cf = pl->naxes >= 1 && pl->naxes <= 3;
+        for (int i = 0; cf && i < pl->naxes; ++i)
+            if (pl->axes[i] != ndim - pl->naxes + i || !is_pow2(pl->shape[pl->axes[i]])) cf = false;
+        if (cf) {
+            long long n[3] = {1, 1, 1};
+            for (int i = 0; i < pl->naxes; ++i) n[3 - pl->naxes + i] = pl->shape[pl->axes[i]];
+            Geom& gc = pl->gc;
+            gc.logN0 = ilog2(n[0]);
+            gc.logN1 = ilog2(n[1]);
+            gc.logM = ilog2(n[2]);
+            gc.batch = 1;
+            gc.shift0 = gc.shift1 = 0;
+            for (int i = 0; i < ndim - pl->naxes; ++i) gc.batch *= pl->shape[i];
+            const size_t es = dtype == NB2_F32 ? sizeof(cplx<float>) : sizeof(cplx<double>);
+            if (gc.logM < 1 || gc.logM > 13 || gc.logN0 > 13 || gc.logN1 > 13) cf = false;
+            if (cf && gc.logN0 && size_t(pitch_of(gc.logN0)) * es > kSmemLimit) cf = false;
+            if (cf && gc.logN1 && size_t(pitch_of(gc.logN1)) * es > kSmemLimit) cf = false;
+            if (cf && size_t(pitch_of(gc.logM)) * es > kSmemLimit) cf = false;
+        }
+        pl->cfast = cf;
+    }
     // ---- leading 1..2 contiguous axes with an even power-of-two-pairs inner batch
     if (!fast && pl->naxes >= 1 && pl->naxes <= 2 && pl->axes[pl->naxes - 1] < ndim - 1 &&
         (pl->naxes == 1 || pl->axes[1] == pl->axes[0] + 1)) {
@@ -456,6 +519,9 @@ int nb2_plan_destroy(nb2_plan* pl) {
     rt_free(pl->tw0);
     rt_free(pl->tw1);
     rt_free(pl->twr);
+    rt_free(pl->ctw0);
+    rt_free(pl->ctw1);
+    rt_free(pl->ctwr);
     rt_free(pl->partials);
     rt_free(pl->work0);
     rt_free(pl->work1);
@@ -475,6 +541,7 @@ int nb2_plan_set_mirror(nb2_plan* pl, int shift0, int shift1) {
 }
 
 int nb2_plan_is_fast(const nb2_plan* pl) { return pl && pl->fast ? 1 : 0; }
+int nb2_plan_is_c2c_fast(const nb2_plan* pl) { return pl && pl->cfast ? 1 : 0; }
 int nb2_plan_kind(const nb2_plan* pl) { return !pl ? -1 : (pl->fast ? 1 : (pl->inner ? 2 : 0)); }
 
 int64_t nb2_plan_ksq_size(const nb2_plan* pl) {

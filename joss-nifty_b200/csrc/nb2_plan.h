@@ -27,6 +27,13 @@ struct nb2_plan {
     void* tw0 = nullptr;  // strided axis-0 table (N0 entries)
     void* tw1 = nullptr;  // strided axis-1 table (N1 entries)
     void* twr = nullptr;  // row table (N2 entries)
+    // complex-to-complex fast path over the trailing axes (nb2_c2c): geometry with M = N2 complex numbers per
+    // row and its own twiddle tables (created at the first nb2_c2c call)
+    bool cfast = false;
+    nb2::Geom gc{};
+    void* ctw0 = nullptr;
+    void* ctw1 = nullptr;
+    void* ctwr = nullptr;
     double* partials = nullptr;
     long long npartials = 0;
     // developer knobs, read from the environment once at plan creation (never on the dispatch path)
@@ -88,5 +95,8 @@ int run_rows(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointo
              rt_stream st);
 template <typename T> int rows_pairs_per_cta(const nb2_plan* pl);
 int launch_final_reduce(const double* partials, long long nparts, int nv, double* out, rt_stream st);
+template <typename T>
+int run_rows_c2c(const void* in, void* out, const void* tw, int logl, long long nrows, int conj_in, int conj_out,
+                 double scale, rt_stream st);
 
 }  // namespace nb2

@@ -16,6 +16,6 @@ from .metric import CFMetric  # noqa: F401
 from .cg import (ConjugateGradient, QuadraticEnergy, GradientNormController,  # noqa: F401
                  AbsDeltaEnergyController, cg, static_cg, CGResults)
 from .distributed import SlabCorrelatedField, SlabHartley, SymmetricSplit  # noqa: F401
-from .operators import HartleyOperator, HarmonicTransformOperator, RGSpace  # noqa: F401
+from .operators import FFTOperator, HartleyOperator, HarmonicTransformOperator, RGSpace  # noqa: F401
 
 __version__ = "0.1.0"

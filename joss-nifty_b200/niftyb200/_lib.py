@@ -58,6 +58,7 @@ class Library:
         "nb2_plan_destroy": (c_int, [c_void_p]),
         "nb2_plan_is_fast": (c_int, [c_void_p]),
         "nb2_plan_kind": (c_int, [c_void_p]),
+        "nb2_plan_is_c2c_fast": (c_int, [c_void_p]),
         "nb2_plan_set_mirror": (c_int, [c_void_p, c_int, c_int]),
         "nb2_plan_ksq_size": (c_int64, [c_void_p]),
         "nb2_hartley": (c_int, [c_void_p, c_void_p, c_void_p, c_int, POINTER(PointOp), POINTER(PointOp), c_void_p]),

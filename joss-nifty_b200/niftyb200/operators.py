@@ -1,6 +1,6 @@
-"""HartleyOperator / HarmonicTransformOperator on the GPU backend.
+"""FFTOperator / HartleyOperator / HarmonicTransformOperator on the GPU backend.
 
-Mirror of ``/root/reference/src/operators/harmonic_operators.py:126-217,326-380`` for regular
+Mirror of ``/root/reference/src/operators/harmonic_operators.py:34-123,126-217,326-380`` for regular
 grids: same modes (TIMES, ADJOINT_TIMES, INVERSE_TIMES, ADJOINT_INVERSE_TIMES), same volume
 factors (``:213-217``: domain ``scalar_dvol`` for TIMES|ADJOINT_TIMES, target ``scalar_dvol``
 for the inverse modes), complex input transformed part by part (``:202-206``).  Fields are
@@ -11,7 +11,7 @@ plain arrays (numpy in -> numpy out, torch device tensors in -> device tensors o
 import numpy as np
 import torch
 
-from .transforms import PointOp, get_plan, device as _device
+from .transforms import PointOp, _CPLX_OF, _TORCH_CPLX, _TORCH_REAL, get_plan, device as _device
 
 
 class RGSpace:
@@ -106,6 +106,41 @@ class HartleyOperator:
         return self.apply(x, self.ADJOINT_INVERSE_TIMES)
 
     __call__ = times
+
+
+class FFTOperator(HartleyOperator):
+    """``FFTOperator`` (``harmonic_operators.py:34-123``): full complex FFT between a position-space and a
+    harmonic RGSpace; the result is always complex (``:52-56``).  A field on a position space is transformed
+    with ``fftn`` (factor 1), a field on a harmonic space with ``ifftn`` times the number of cells (``:108-114``);
+    the volume factor is the domain's ``scalar_dvol`` for TIMES | ADJOINT_TIMES and the target's for the
+    inverse modes (``:119-122``).  All four modes (``_all_ops``, ``:60``)."""
+
+    def __init__(self, domain, target=None, full_shape=None, axes=None):
+        if not isinstance(domain, RGSpace):
+            raise TypeError("FFTOperator only works on RGSpaces")
+        super().__init__(domain, target, full_shape, axes)
+
+    def apply(self, x, mode):
+        if mode not in (1, 2, 4, 8):
+            raise ValueError("invalid operator mode specified")
+        host = not isinstance(x, torch.Tensor)
+        t = torch.as_tensor(np.ascontiguousarray(x)) if host else x
+        if tuple(t.shape) != self.full_shape:
+            raise ValueError("The operator's and field's domains don't match.")
+        if not t.is_complex():
+            t = t.to(torch.complex64 if t.dtype == torch.float32 else torch.complex128)
+        t = t.to(_device()).contiguous()
+        # the space the INPUT lives on: the domain for TIMES / ADJOINT_INVERSE_TIMES, else the target
+        src = self.domain if mode & (self.TIMES | self.ADJOINT_INVERSE_TIMES) else self.target
+        ncells = int(np.prod(src.shape))
+        fct = self._fct(mode)
+        plan = get_plan(t.shape, self.axes, t.dtype)
+        if src.harmonic:          # harmonic -> position: ifftn * ncells == unnormalised backward transform
+            y = plan.c2c(t, forward=False, scale=fct)
+        else:
+            y = plan.c2c(t, forward=True, scale=fct)
+        del ncells
+        return y.cpu().numpy() if host else y
 
 
 class HarmonicTransformOperator(HartleyOperator):

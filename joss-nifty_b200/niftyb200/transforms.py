@@ -133,6 +133,7 @@ class Plan:
         self.is_fast = bool(self.lib.nb2_plan_is_fast(h))
         self.kind = int(self.lib.nb2_plan_kind(h))   # 0 generic, 1 fast (trailing axes), 2 fast (inner batch)
         self.ksq_size = int(self.lib.nb2_plan_ksq_size(h))
+        self.is_c2c_fast = bool(self.lib.nb2_plan_is_c2c_fast(h))   # fftn / ifftn on the strided + row c2c passes
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None

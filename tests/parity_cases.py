@@ -85,6 +85,33 @@ def check_hartley_shapes(shapes, dtypes=(np.float64, np.float32), seed=42):
                 assert rel(got, ref) <= TOL[dt], (shape, axes, dt, c, rel(got, ref))
 
 
+def check_c2c_shapes(shapes, dtypes=(np.complex128, np.complex64), seed=17, expect_fast=None):
+    """``fftn`` / ``ifftn`` drop-ins (ducc_dispatch.py:66-72) against the oracle (scipy pocketfft): complex and
+    real input, forward unnormalised, backward scaled 1/N over the transformed axes."""
+    rng = np.random.default_rng(seed)
+    for shape, axes in shapes:
+        z128 = rng.normal(size=shape) + 1j * rng.normal(size=shape)
+        for dt in dtypes:
+            z = z128.astype(dt)
+            tol = 1e-12 if dt == np.complex128 else 1e-5
+            if expect_fast is not None:
+                launches0 = nb._lib.get().nb2_launch_count()
+            f, b = nb.fftn(z, axes), nb.ifftn(z, axes)
+            if expect_fast is not None:
+                # fast path: <= 4 launches per transform (conj sweep + 2 strided + rows); the O(n^2) path
+                # runs one NaiveDft launch per axis plus two copies -- and is told apart by the plan flag
+                from niftyb200.transforms import _norm_axes
+                rdt = torch.float32 if dt == np.complex64 else torch.float64
+                assert bool(get_plan(z.shape, _norm_axes(z.ndim, axes), rdt).is_c2c_fast) == expect_fast, (shape, axes)
+            assert f.dtype == dt and f.shape == z.shape
+            assert rel(f, otr.fftn(z.astype(np.complex128), axes)) <= tol, (shape, axes, dt, "fftn")
+            assert rel(b, otr.ifftn(z.astype(np.complex128), axes)) <= tol, (shape, axes, dt, "ifftn")
+        # real input: complex result (harmonic_operators.py:110-117 passes real fields too)
+        x = rng.normal(size=shape)
+        assert rel(nb.fftn(x, axes), otr.fftn(x, axes)) <= 1e-12
+        assert rel(nb.ifftn(x.astype(np.float32), axes), otr.ifftn(x.astype(np.float32).astype(np.float64), axes)) <= 1e-5
+
+
 def check_inplace_and_roundtrip(shape, dt=np.float64):
     """in-place execution == out-of-place; H(H(x)) = N x (test_fft_operator.py:38-60)."""
     rng = np.random.default_rng(7)
@@ -111,6 +138,20 @@ def check_operator_golden(golden):
         assert rel(op.inverse_times(y), g[f"o{n}_inverse"]) <= 1e-12
         assert rel(op.adjoint_times(x), g[f"o{n}_adjoint"]) <= 1e-12
         assert rel(op.times(g[f"o{n}_cin"]), g[f"o{n}_ctimes"]) <= 1e-12
+        # FFTOperator (harmonic_operators.py:106-123): times on the position space, inverse_times from the target
+        fop = nb.FFTOperator(nb.RGSpace(x.shape, tuple(dist)))
+        z = g[f"o{n}_cin"]
+        assert rel(fop.times(z), g[f"o{n}_fft_times"]) <= 1e-12
+        assert rel(fop.inverse_times(z), g[f"o{n}_fft_inverse"]) <= 1e-12
+        assert rel(fop.inverse_times(fop.times(z)), z) <= 1e-12                 # test_fft_operator.py:38-60
+        assert np.iscomplexobj(fop.times(x)) and rel(fop.times(x), fop.times(x.astype(np.complex128))) <= 1e-13
+        # adjointness <A a, b> == <a, A^T b> (extra.py:156-167), also of the operator on the harmonic partner
+        for o2 in (fop, nb.FFTOperator(fop.target)):
+            rng = np.random.default_rng(n)
+            a, b = (rng.normal(size=x.shape) + 1j * rng.normal(size=x.shape) for _ in range(2))
+            lhs, rhs = np.vdot(b, o2.times(a)), np.vdot(o2.adjoint_times(b), a)
+            assert abs(lhs - rhs) <= 1e-12 * abs(lhs)
+            assert rel(o2.adjoint_inverse_times(o2.adjoint_times(b)), b) <= 1e-12
 
 
 def check_vdot():

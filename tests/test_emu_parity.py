@@ -28,6 +28,18 @@ def test_hartley_long_axes():
     pc.check_hartley_shapes([((16384,), None), ((4096, 4), None)], dtypes=(np.float32,))
 
 
+def test_c2c_fast_path():
+    # every radix plan of the contiguous-axis c2c kernel (rows of 2 .. 8192), strided passes of all three kinds,
+    # batch axes, axis subsets
+    pc.check_c2c_shapes([((2,), None), ((4,), None), ((8,), None), ((16,), None), ((32,), None), ((64,), None), ((128,), None),
+                         ((256,), None), ((512,), None), ((1024,), None), ((2048,), None), ((4096,), None), ((8192,), None),
+                         ((16, 32), None), ((8, 4, 16), None), ((3, 16, 8), (1, 2)), ((5, 64), (1,)), ((2, 3, 8, 8, 4), (2, 3, 4)),
+                         ((256, 8), None), ((4, 256, 16), None), ((2048, 4), None)], expect_fast=True)
+    pc.check_c2c_shapes([((32, 32), None), ((16, 16, 16), None), ((64, 2), None)], dtypes=(np.complex64,), expect_fast=True)
+    # not on the fast path: non-power-of-two, leading axes, 16384-point rows
+    pc.check_c2c_shapes([((10,), None), ((12, 9), None), ((8, 4), (0,)), ((6, 16), None)], expect_fast=False)
+
+
 def test_hartley_generic_shapes():
     pc.check_hartley_shapes([((10,), None), ((12, 9), None), ((15, 27), None), ((7, 1, 5), None), ((1,), None),
                              ((6, 16, 8), (1,)), ((8, 4, 16), (0, 2)), ((16, 2), None), ((8, 6), None)])

@@ -37,6 +37,18 @@ def test_hartley_long_axes():
                              ((64, 8192), None), ((16384,), None), ((2048, 2048), None)])
 
 
+def test_c2c_fast_path():
+    # fftn / ifftn on the strided passes + the contiguous-axis c2c kernel: every radix plan, TMA-fed strided
+    # passes (256..1024 rows), three-step plans, batch axes, axis subsets
+    pc.check_c2c_shapes([((2,), None), ((4,), None), ((8,), None), ((16,), None), ((32,), None), ((64,), None), ((128,), None),
+                         ((256,), None), ((512,), None), ((1024,), None), ((2048,), None), ((4096,), None), ((8192,), None),
+                         ((16, 32), None), ((8, 4, 16), None), ((3, 16, 8), (1, 2)), ((5, 64), (1,)), ((2, 3, 8, 8, 4), (2, 3, 4)),
+                         ((1024, 1024), None), ((64, 4096), None), ((4096, 64), None), ((512, 8, 1024), None),
+                         ((8, 1024, 64), None), ((128, 128, 128), None)], expect_fast=True)
+    pc.check_c2c_shapes([((256, 256, 256), None), ((2048, 2048), None)], dtypes=(np.complex64,), expect_fast=True)
+    pc.check_c2c_shapes([((10,), None), ((12, 9), None), ((8, 4), (0,)), ((6, 16), None)], expect_fast=False)
+
+
 def test_hartley_generic_shapes():
     pc.check_hartley_shapes([((10,), None), ((12, 9), None), ((15, 27), None), ((7, 1, 5), None), ((1,), None),
                              ((6, 16, 8), (1,)), ((8, 4, 16), (0, 2)), ((16, 2), None), ((8, 6), None),
