@@ -215,6 +215,26 @@ int nb2_axpby(int dtype, int64_t n, double a, const void* x, double b, void* y, 
 int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, const void* q, const void* b,
                   void* x, void* r, double* sums_dev, void* stream);
 
+/* ---- The O(n_bins) amplitude (power-spectrum) chain of the correlated field on the device, and its VJP
+ * (SURVEY.md 8f N1).  Replaces non_parametric_amplitude.correlate (src/re/correlated_field.py:277-304) with the
+ * integrated Wiener process (src/re/gauss_markov.py:105-121) and amp.at[1:].mul(1/azm) (:605-611); numpy twin
+ * _Amplitude (src/library/correlated_fields.py:276-385).  All arrays are DEVICE fp64 arrays:
+ *   rel (nb) relative_log_mode_lengths, dt (nb-2) log_volume, mult (nb) mode multiplicity, xi (nb-2, 2) the
+ *   white excitations of the Wiener process (NULL / flx < 0: no flexibility; asp < 0: no asperity);
+ *   flu, slope, flx, asp, azm are the prior-transformed scalars; power_kind 1 = "power", 0 = "amplitude".
+ * forward: amp (nb) = normalised amplitude (amp[0] = totvol); optionally also scattered into a table
+ *   (table[table_idx[k]] = amp[k], float if table_f32 else double: the ksq table of amp_mode 1);
+ *   scratch (2 nb + 2 doubles) keeps what the VJP needs.
+ * vjp: given ampbar (nb, cotangent of amp; entry 0 ignored) -> xibar (nb-2, 2) and
+ *   scalars_bar[5] = cotangents of (flu, slope, flx, asp, azm) through the chain.  Consumes the scratch. */
+int nb2_amplitude_forward(int64_t nb, const double* rel, const double* dt, const double* mult, double totvol,
+                          const double* xi, double flu, double slope, double flx, double asp, double azm, int power_kind,
+                          double* scratch, double* amp, void* table, const int64_t* table_idx, int table_f32, void* stream);
+int nb2_amplitude_vjp(int64_t nb, const double* rel, const double* dt, const double* mult, double totvol,
+                      const double* xi, double flu, double slope, double flx, double asp, double azm, int power_kind,
+                      double* scratch, const double* amp, const double* ampbar, double* xibar, double* scalars_bar,
+                      void* stream);
+
 /* ---- Device-resident conjugate gradient (static_cg, src/re/conjugate_gradient.py:219-389: the reference keeps
  * the whole loop on the device inside lax.while_loop, :382).  The scalars of the recurrence live in a DEVICE
  * array `state` of NB2_CG_STATE_SIZE doubles (integers stored as doubles); the kernels of an iteration read

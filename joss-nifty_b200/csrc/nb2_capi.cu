@@ -4,6 +4,7 @@
 // same file builds the sequential thread emulator used by the CPU-only index tests.
 #include <mutex>
 
+#include "nb2_amplitude.cuh"
 #include "nb2_c2c.cuh"
 #include "nb2_generic.cuh"
 #include "nb2_plan.h"
@@ -866,6 +867,32 @@ int nb2_cg_decide(double* state, int* gate, int stage, void* stream) {
     }
     CgDecide::Params p{state, gate, stage};
     return rt_launch<CgDecide>(1, 32, 0, (rt_stream)stream, p);
+}
+
+int nb2_amplitude_forward(int64_t nb, const double* rel, const double* dt, const double* mult, double totvol,
+                          const double* xi, double flu, double slope, double flx, double asp, double azm, int power_kind,
+                          double* scratch, double* amp, void* table, const int64_t* table_idx, int table_f32, void* stream) {
+    if (nb < 1 || !rel || !mult || !scratch || !amp || (nb > 2 && !dt) || (table && !table_idx) || !(azm > 0.0)) {
+        last_error() = "nb2_amplitude_forward: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    AmplitudeForward::Params p{{nb, rel, dt, mult, totvol}, {flu, slope, flx, asp, azm, power_kind}, xi,
+                               scratch, scratch + nb, scratch + 2 * nb, amp, table, (const long long*)table_idx, table_f32};
+    return rt_launch<AmplitudeForward>(1, kAmpThreads, AmplitudeForward::smem_bytes(kAmpThreads), (rt_stream)stream, p);
+}
+
+int nb2_amplitude_vjp(int64_t nb, const double* rel, const double* dt, const double* mult, double totvol,
+                      const double* xi, double flu, double slope, double flx, double asp, double azm, int power_kind,
+                      double* scratch, const double* amp, const double* ampbar, double* xibar, double* scalars_bar,
+                      void* stream) {
+    if (nb < 1 || !rel || !mult || !scratch || !amp || !ampbar || !scalars_bar || (nb > 2 && !dt) ||
+        (flx >= 0.0 && nb > 2 && xi && !xibar)) {
+        last_error() = "nb2_amplitude_vjp: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    AmplitudeVjp::Params p{{nb, rel, dt, mult, totvol}, {flu, slope, flx, asp, azm, power_kind}, xi, amp,
+                           scratch + 2 * nb, ampbar, scratch + nb, scratch, xibar, scalars_bar};
+    return rt_launch<AmplitudeVjp>(1, kAmpThreads, AmplitudeVjp::smem_bytes(kAmpThreads), (rt_stream)stream, p);
 }
 
 int nb2_set_launch_gate(const int* gate) {

@@ -37,13 +37,34 @@ def lognormal_moments(mean, std):
     return math.log(mean) - 0.5 * logstd ** 2, logstd
 
 
+class _ScalarPrior:
+    """Standard-normal excitation -> parameter (re/num/stats_distributions.py:41-88), callable on torch
+    tensors like the plain lambdas, plus value and derivative as host floats for the scalar leaves (the
+    amplitude-chain kernels take the transformed scalars by value)."""
+
+    def __init__(self, kind, a, b):
+        self.kind, self.a, self.b = kind, float(a), float(b)      # normal: a + b xi; lognormal: exp(a + b xi)
+
+    def __call__(self, xi):
+        if self.kind == "normal":
+            return self.a + self.b * xi
+        return torch.exp(self.a + self.b * xi) if isinstance(xi, torch.Tensor) else math.exp(self.a + self.b * xi)
+
+    def value(self, xi):
+        return float(self(float(xi)))
+
+    def grad(self, xi):
+        """d value / d xi"""
+        return self.b if self.kind == "normal" else self.b * self.value(xi)
+
+
 def normal_prior(mean, std):
-    return lambda xi: mean + std * xi
+    return _ScalarPrior("normal", mean, std)
 
 
 def lognormal_prior(mean, std):
     lm, ls = lognormal_moments(mean, std)
-    return lambda xi: torch.exp(lm + ls * xi)
+    return _ScalarPrior("lognormal", lm, ls)
 
 
 def _prior(spec, kind):
@@ -88,6 +109,91 @@ class _Fluctuations:
             for k in ("scale", "cutoff", "loglogslope"):
                 d[pf + k] = ()
         return d
+
+    @property
+    def on_kernel(self):
+        """The chain runs in the CUDA kernels of csrc/nb2_amplitude.cuh: non-parametric spectrum with the
+        standard (mean, std) priors.  Matern spectra and user-supplied prior callables use the torch ops below."""
+        if self.kind != "nonparametric":
+            return False
+        keys = ["fluctuations", "loglogavgslope"]
+        if self.priors["flexibility"] is not None and self.grid.log_volume.numel() > 0:
+            keys.append("flexibility")
+            if self.priors["asperity"] is not None:
+                keys.append("asperity")
+        return all(isinstance(self.priors[k], _ScalarPrior) for k in keys)
+
+    def _chain_inputs(self, p, azm):
+        g, pr, pf = self.grid, self.priors, self.prefix
+        lat = {k: float(np.asarray(p[pf + k])) for k in ("fluctuations", "loglogavgslope")}
+        flex = pr["flexibility"] is not None and g.log_volume.numel() > 0
+        asp = flex and pr["asperity"] is not None
+        if flex:
+            lat["flexibility"] = float(np.asarray(p[pf + "flexibility"]))
+        if asp:
+            lat["asperity"] = float(np.asarray(p[pf + "asperity"]))
+        xi = None
+        if flex:
+            v = p[pf + "spectrum"]
+            xi = (v if isinstance(v, torch.Tensor) else torch.as_tensor(np.asarray(v))).to(device=g.device, dtype=torch.float64)
+            xi = xi.contiguous()
+        sc = dict(flu=pr["fluctuations"].value(lat["fluctuations"]), slope=pr["loglogavgslope"].value(lat["loglogavgslope"]),
+                  flx=pr["flexibility"].value(lat["flexibility"]) if flex else -1.0,
+                  asp=pr["asperity"].value(lat["asperity"]) if asp else -1.0, azm=float(azm))
+        return lat, xi, sc
+
+    def _geom_args(self):
+        g = self.grid
+        if not hasattr(g, "_mult_f64"):
+            g._mult_f64 = g.mode_multiplicity.to(torch.float64).contiguous()
+        return g.relative_log_mode_lengths.contiguous(), g.log_volume.contiguous(), g._mult_f64
+
+    def amplitude_kernel(self, p, azm, table=None, table_idx=None):
+        """NORMALISED amplitude per power bin (amp[0] = totvol, amp[1:] / azm; re/correlated_field.py:277-304,
+        605-611) by the device kernel; returns (amp, context for :meth:`vjp_kernel`)."""
+        lib = _lib.get()
+        g = self.grid
+        rel, dt, mult = self._geom_args()
+        lat, xi, sc = self._chain_inputs(p, azm)
+        nbins = int(rel.numel())
+        scratch = torch.empty(2 * nbins + 2, dtype=torch.float64, device=g.device)
+        amp = torch.empty(nbins, dtype=torch.float64, device=g.device)
+        kind = 1 if self.np_kind == "power" else 0
+        from .transforms import _ptr, _stream
+        rc = lib.nb2_amplitude_forward(nbins, _ptr(lib, rel), _ptr(lib, dt) if nbins > 2 else None, _ptr(lib, mult),
+                                       float(g.total_volume), _ptr(lib, xi), sc["flu"], sc["slope"], sc["flx"], sc["asp"],
+                                       sc["azm"], kind, _ptr(lib, scratch), _ptr(lib, amp),
+                                       _ptr(lib, table), _ptr(lib, table_idx),
+                                       1 if (table is not None and table.dtype == torch.float32) else 0, _stream(amp))
+        lib.check(rc, "nb2_amplitude_forward")
+        return amp, dict(lat=lat, xi=xi, sc=sc, scratch=scratch, amp=amp, kind=kind)
+
+    def vjp_kernel(self, ctx, ampbar):
+        """Cotangents of this sub-space's latents for the cotangent ``ampbar`` of its normalised amplitudes:
+        ``({leaf: cotangent}, azmbar through the chain)``."""
+        lib = _lib.get()
+        g, pr, pf = self.grid, self.priors, self.prefix
+        rel, dt, mult = self._geom_args()
+        nbins = int(rel.numel())
+        xi, sc, lat = ctx["xi"], ctx["sc"], ctx["lat"]
+        xibar = torch.zeros_like(xi) if xi is not None else None
+        sbar = torch.zeros(5, dtype=torch.float64, device=g.device)
+        from .transforms import _ptr, _stream
+        ab = ampbar.to(device=g.device, dtype=torch.float64).contiguous()
+        rc = lib.nb2_amplitude_vjp(nbins, _ptr(lib, rel), _ptr(lib, dt) if nbins > 2 else None, _ptr(lib, mult),
+                                   float(g.total_volume), _ptr(lib, xi), sc["flu"], sc["slope"], sc["flx"], sc["asp"],
+                                   sc["azm"], ctx["kind"], _ptr(lib, ctx["scratch"]), _ptr(lib, ctx["amp"]), _ptr(lib, ab),
+                                   _ptr(lib, xibar), _ptr(lib, sbar), _stream(ab))
+        lib.check(rc, "nb2_amplitude_vjp")
+        sb = sbar.cpu().numpy()
+        out = {pf + "fluctuations": sb[0] * pr["fluctuations"].grad(lat["fluctuations"]),
+               pf + "loglogavgslope": sb[1] * pr["loglogavgslope"].grad(lat["loglogavgslope"])}
+        if "flexibility" in lat:
+            out[pf + "flexibility"] = sb[2] * pr["flexibility"].grad(lat["flexibility"])
+            out[pf + "spectrum"] = xibar
+        if "asperity" in lat:
+            out[pf + "asperity"] = sb[3] * pr["asperity"].grad(lat["asperity"])
+        return out, float(sb[4])
 
     def amplitude(self, p):
         """Un-normalised amplitude per power bin (fp64 device tensor)."""
@@ -232,18 +338,60 @@ class CorrelatedField:
 
     def normalized_amplitudes(self, p):
         """``get_normalized_amplitudes`` (``:598-611``): ``amp.at[1:].mul(1/azm)``, fp64, device."""
-        pd = {k: self._as_dev(v) for k, v in p.items() if not k.endswith("xi")}
-        azm = self._azm(pd[self.prefix + "zeromode"])
-        out = []
+        amps, azm, _ = self._amplitudes(p)
+        return amps, azm
+
+    def _amplitudes(self, p):
+        """(normalised amplitudes, azm, per-sub-space chain context or None).  Sub-spaces with a non-parametric
+        spectrum and standard priors run the chain in ONE kernel (csrc/nb2_amplitude.cuh, SURVEY.md 8f N1);
+        Matern spectra / user prior callables use torch ops."""
+        zl = p[self.prefix + "zeromode"]
+        if isinstance(self._azm, _ScalarPrior):
+            azm = self._azm.value(float(np.asarray(zl.cpu() if isinstance(zl, torch.Tensor) else zl)))
+        else:
+            azm = self._azm(self._as_dev(zl))
+        out, ctxs, pd = [], [], None
         for f in self.fl:
+            if f.on_kernel and isinstance(azm, float):
+                a, ctx = f.amplitude_kernel(p, azm)
+                out.append(a)
+                ctxs.append(ctx)
+                continue
+            if pd is None:
+                pd = {k: self._as_dev(v) for k, v in p.items() if not k.endswith("xi")}
             a = f.amplitude(pd)
             out.append(torch.cat((a[:1], a[1:] / azm)))
-        return out, azm
+            ctxs.append(None)
+        return out, azm, ctxs
 
     def tables(self, p):
         """Device tables for the expansion point ``p`` (cold path, once per nonlinear step)."""
-        amps, azm = self.normalized_amplitudes(p)
-        return self.tables_from_amplitudes(amps, float(azm))
+        amps, azm, ctxs = self._amplitudes(p)
+        tab = self.tables_from_amplitudes(amps, float(azm))
+        tab.chain = ctxs          # what vjp_latent needs to continue through the amplitude chain
+        return tab
+
+    def vjp_latent(self, ybar, p, convention=None, tab=None):
+        """Cotangent of EVERY latent leaf of the model for the position-space cotangent ``ybar`` -- the
+        Jacobian adjoint the reference gets from ``jax.vjp`` / ``Linearization.jac.adjoint_times``
+        (re/likelihood.py:299,573-583; golden ``adj_*`` vectors): the hot tail's VJP (one transform with the
+        binned reduction, :meth:`vjp`), then the amplitude chain's VJP kernel per sub-space and the priors'
+        derivatives.  Returns ``{leaf: cotangent}`` (device tensors for ``xi`` / ``spectrum``, floats for the
+        scalar leaves) and the cotangent of ``offset_mean`` under the key ``"offset_mean"``."""
+        tab = self.tables(p) if tab is None else tab
+        if getattr(tab, "chain", None) is None or any(c is None for c in tab.chain) or not isinstance(self._azm, _ScalarPrior):
+            raise NotImplementedError("vjp_latent: non-parametric spectra with standard (mean, std) priors")
+        xi = self._as_dev(p[self.prefix + "xi"], self.dtype).contiguous()
+        yb = self._as_dev(ybar, self.dtype).contiguous()
+        xibar, ampbars, azmbar, offbar = self.vjp(yb, tab, xi, convention=convention)
+        out = {self.prefix + "xi": xibar, "offset_mean": offbar}
+        for f, ctx, ab in zip(self.fl, tab.chain, ampbars):
+            leaves, azm_chain = f.vjp_kernel(ctx, ab)
+            out.update(leaves)
+            azmbar += azm_chain
+        zl = float(np.asarray(p[self.prefix + "zeromode"]))
+        out[self.prefix + "zeromode"] = azmbar * self._azm.grad(zl)
+        return out
 
     def tables_from_amplitudes(self, amps, azm):
         amps = [self._as_dev(a) for a in amps]

@@ -205,6 +205,63 @@ def check_cf_golden(golden, names):
             assert rel(host(xb), g[f"{tag}_adj_xi"]) <= 1e-10, tag
 
 
+def check_cf_latent_vjp_golden(golden, names):
+    """Jacobian adjoint to EVERY latent leaf (xi, zeromode, fluctuations, loglogavgslope, flexibility, asperity,
+    spectrum; per sub-space for product spaces) == the reference's ``lin.jac.adjoint_times`` golden vectors
+    (make_golden.py: ``adj_<leaf>``): hot-tail VJP + the amplitude chain's VJP kernel + the priors."""
+    from test_oracle_golden import CF_CASES, golden_pos, build_oracle_cf
+    g = golden["correlated_field"]
+    for name in names:
+        subs, off_mean, off_std = CF_CASES[name]
+        mk = nb.CorrelatedFieldMaker("")
+        mk.set_amplitude_total_offset(off_mean, off_std)
+        for i, (shape, dist, kw) in enumerate(subs):
+            mk.add_fluctuations(shape, dist, **kw, prefix="" if len(subs) == 1 else f"ax{i}", non_parametric_kind="power")
+        cf, co = mk.finalize(), build_oracle_cf(name)
+        assert all(f.on_kernel for f in cf.fl)
+        for conv in CONVS:
+            tag = f"{name}_{conv}"
+            p = golden_pos(g, tag, co)
+            amps, azm = cf.normalized_amplitudes(p)                 # the chain kernel
+            for a, b in zip(amps, co.normalized_amplitudes(p)):
+                assert rel(host(a), b) <= 1e-13, tag
+            adj = cf.vjp_latent(g[f"{tag}_ybar"], p, convention=conv)
+            assert set(adj) == set(cf.domain) | {"offset_mean"}
+            for k in cf.domain:
+                ref = g[f"{tag}_adj_{k}"]
+                got = adj[k]
+                got = host(got) if isinstance(got, torch.Tensor) else np.asarray(got)
+                got = got.T if k.endswith("spectrum") else got           # numpy stack stores (2, nb - 2)
+                # the zero-mode cotangent is a difference of two cancelling terms: 1e-9 instead of 1e-10
+                assert rel(got, ref) <= (1e-9 if k.endswith("zeromode") else 1e-10), (tag, k, rel(got, ref))
+
+
+def check_cf_latent_vjp_directional(shape, dist, kind="power", seed=5):
+    """<ybar, d cf(p)[t]> == <vjp_latent(ybar), t> with the directional derivative by central differences of the
+    ORACLE model (fp64), for a random direction t over all latent leaves -- at bin counts beyond the golden
+    cases (the segmented scans of the chain kernels with many elements per thread)."""
+    cf, co = make_pair(shape, dist, torch.float64, kind=kind)
+    rng = np.random.default_rng(seed)
+    p = cf.init(seed)
+    t = {k: rng.standard_normal(np.shape(v)) for k, v in p.items()}
+    ybar = rng.standard_normal(shape)
+    adj = cf.vjp_latent(ybar, p)
+    lhs = 0.0
+    for k in cf.domain:
+        a = adj[k]
+        a = host(a) if isinstance(a, torch.Tensor) else np.asarray(a)
+        lhs += float(np.vdot(a, t[k]))
+    eps = 1e-6
+    yp = co({k: p[k] + eps * t[k] for k in p})
+    ym = co({k: p[k] - eps * t[k] for k in p})
+    rhs = float(np.vdot(ybar, (yp - ym) / (2 * eps)))
+    assert abs(lhs - rhs) <= 2e-7 * max(abs(lhs), abs(rhs)), (shape, kind, lhs, rhs)
+    # and the kernel amplitudes against the oracle chain
+    amps, _ = cf.normalized_amplitudes(p)
+    for a, b in zip(amps, co.normalized_amplitudes(p)):
+        assert rel(host(a), b) <= 1e-13
+
+
 def check_cf_vs_oracle(shape, dist, dt=np.float64, expect_mode=None, seed=3):
     tdt = torch.float64 if dt == np.float64 else torch.float32
     cf, co = make_pair(shape, dist, tdt)

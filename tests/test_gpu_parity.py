@@ -73,6 +73,15 @@ def test_cf_golden(golden):
     pc.check_cf_golden(golden, ["cf1d", "cf2d", "cf2d_odd", "cf3d", "cfprod"])
 
 
+def test_cf_latent_vjp_golden(golden):
+    pc.check_cf_latent_vjp_golden(golden, ["cf1d", "cf2d", "cf2d_odd", "cf3d", "cfprod"])
+
+
+@pytest.mark.parametrize("shape,dist,kind", [((64, 64), 1 / 64, "power"), ((16, 16, 16), 1 / 16, "amplitude"), ((2048,), 0.01, "power"), ((512, 512), 1 / 512, "power"), ((64, 64, 64), 1 / 64, "amplitude")])
+def test_cf_latent_vjp_directional(shape, dist, kind):
+    pc.check_cf_latent_vjp_directional(shape, dist, kind)
+
+
 @pytest.mark.parametrize("shape,dist,mode", [((64,), 0.3, 1), ((32, 32), 1 / 32, 1), ((16, 16, 16), 1 / 16, 1),
                                              ((8, 4, 16), 1 / 16, 2), ((5, 6), (0.3, 0.5), 2),
                                              ((128, 128), 1 / 128, 1), ((512, 512), 1 / 512, 1),
