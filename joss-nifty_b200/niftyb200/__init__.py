@@ -12,7 +12,7 @@ from .transforms import Plan, hartley, fftn, ifftn, vdot, hartley_device  # noqa
 from .ducc_dispatch import set_nthreads, nthreads, install  # noqa: F401
 from .geometry import RGGrid  # noqa: F401
 from .correlated_field import CorrelatedFieldMaker, CorrelatedField, SimpleCorrelatedField  # noqa: F401
-from .metric import CFMetric  # noqa: F401
+from .metric import CFMetric, SampledCFMetric  # noqa: F401
 from .cg import (ConjugateGradient, QuadraticEnergy, GradientNormController,  # noqa: F401
                  AbsDeltaEnergyController, cg, static_cg, CGResults)
 from .distributed import SlabCorrelatedField, SlabHartley, SymmetricSplit  # noqa: F401

@@ -85,3 +85,82 @@ class CFMetric:
         """``j = J^T sqrt(w) eta + x0`` of ``draw_linear_residual`` (src/re/evi.py:114-125)."""
         h = torch.sqrt(self.w) * white_data
         return self.cf.adjoint_xi(h, self.tab, out=out, convention=self.convention, add=white_prior)
+
+
+class SampledCFMetric:
+    """The sample-averaged metric the KL minimisation inverts:
+
+        M t = (1/S) sum_s (A_s H w_s H A_s t) + t
+
+    i.e. ``_kl_met`` (``src/re/optimize_kl.py:103-120``: ``ham.metric`` mapped over the samples and averaged with
+    ``reduce``) / ``SampledKLEnergyClass.apply_metric`` (``src/minimization/kl_energies.py:340-345``:
+    ``sample_list.average``) on the xi block.  Every sample is an expansion point of its own: amplitude tables
+    ``A_s`` and likelihood weight ``w_s``.
+
+    Per sample: one forward and one adjoint fused transform; the adjoint's epilogue scales by ``1/S`` and adds
+    the running sum in place, so the average costs no sweep of its own, and the curvature ``t.(M t)`` rides on
+    the last sample's last store.  ``comm`` (a :class:`niftyb200.distributed.Comm`-like object with
+    ``allreduce_``, ``size``): the samples are sharded over the ranks -- the reference's MPI sample parallelism
+    (``kl_energies.py:136-141``, ``utilities.py:331-390``) -- and the partial sums are all-reduced (one
+    N-vector per apply); ``n_total`` is then the global number of samples."""
+
+    def __init__(self, cf, tables_list, weights, convention=None, comm=None, n_total=None):
+        if len(tables_list) != len(weights):
+            raise ValueError("one weight per sample")
+        self.cf, self.convention, self.sample_comm = cf, convention, comm
+        self.tabs = [cf.streaming_tables(t) for t in tables_list]
+        self.ws = [w.to(device=cf.device, dtype=cf.dtype).contiguous() for w in weights]
+        self.n_local = len(self.ws)
+        self.n_total = int(n_total) if n_total is not None else self.n_local * (comm.size if comm is not None else 1)
+        if self.n_total < 1:
+            raise ValueError("at least one sample")
+        self.shape, self.dtype, self.device = tuple(cf.shape), cf.dtype, cf.device
+        self._u = torch.empty(self.shape, dtype=cf.dtype, device=cf.device)
+        # the running sum alternates between `out` and this buffer: a transform uses its output buffer for the
+        # intermediate passes, so the addend must never alias the output
+        self._acc = torch.empty(self.shape, dtype=cf.dtype, device=cf.device) if self.n_local > 1 else None
+        self._curv = torch.zeros((), dtype=torch.float64, device=cf.device)
+        self.napply = 0
+        # with samples on other ranks the curvature needs the all-reduced result: computed afterwards, on the host side
+        self.device_resident_cg = comm is None and self.n_local > 0
+
+    def __call__(self, t, out=None):
+        return self._apply(t, out, None, None)[0]
+
+    def apply_with_curvature(self, t, out=None, pre=None, curv_out=None):
+        """``(M t, t.(M t))``; see :meth:`CFMetric.apply_with_curvature`."""
+        if pre is not None:
+            raise ValueError("SampledCFMetric does not carry the fused direction update")
+        return self._apply(t, out, t, self._curv if curv_out is None else curv_out)
+
+    def _apply(self, t, out, dot, curv):
+        self.napply += 1
+        cf, S = self.cf, self.n_total
+        out = torch.empty_like(t) if out is None else out
+        local = self.sample_comm is None
+        prev = None
+        for s, (tab, w) in enumerate(zip(self.tabs, self.ws)):
+            u = cf.apply_xi(t, tab, out=self._u, convention=self.convention, offset=0.0, mul=w)
+            last = s == self.n_local - 1
+            dst = out if (self.n_local - 1 - s) % 2 == 0 else self._acc       # the last sample writes `out`
+            # first sample: + t (the prior's identity) when no other rank contributes; later: + running sum
+            add = (t if local else None) if s == 0 else prev
+            prev = dst
+            epi = PointOp(tab.amp_mode, tab.amp, tab.azm * cf.dvol / S, add=add, amp_sym=getattr(tab, "sym", False),
+                          dot=dot if (last and local) else None, dot_out=curv if (last and local) else None)
+            if cf.single:
+                cf.plans[0].hartley(u, out=dst, convention=self.convention, epi=epi)
+            else:
+                cur = cf.plans[-1].hartley(u, out=u, convention=self.convention)
+                for pl in reversed(cf.plans[1:-1]):
+                    cur = pl.hartley(cur, out=cur, convention=self.convention)
+                cf.plans[0].hartley(cur, out=dst, convention=self.convention, epi=epi)
+        if not local:
+            if self.n_local == 0:
+                out.zero_()
+            self.sample_comm.allreduce_(out)
+            out.add_(t)
+            if dot is not None:
+                from .transforms import vdot_device
+                curv.copy_(vdot_device(dot, out))
+        return out, curv

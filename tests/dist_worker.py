@@ -115,3 +115,46 @@ def launch(world, backend, emu_path, shape, port=29533, mode="full", dtype="f64"
     result = mgr.dict()
     mp.spawn(run, args=(world, port, backend, emu_path, shape, result, mode, dtype), nprocs=world, join=True)
     return dict(result)
+
+
+def run_sampled(rank, world, port, emu_path, shape, result):
+    """Samples sharded over the ranks (the reference's MPI sample parallelism, kl_energies.py:136-141) with one
+    all-reduce of the N-vector per apply, against the same SampledCFMetric holding every sample on one rank."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    from niftyb200 import _lib
+    _lib.use_library_for_testing(emu_path, "cpu")
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import niftyb200 as nb
+        import parity_cases as pc
+        from niftyb200.distributed import Comm
+        cgm = sys.modules["niftyb200.cg"]
+        cf, co = pc.make_pair(shape, tuple(1.0 / s for s in shape), torch.float64, kw=pc.GENTLE_KW)
+        rng = np.random.default_rng(3)
+        nsamp = 5
+        tabs, ws = [], []
+        for s in range(nsamp):
+            tabs.append(cf.tables(cf.init(50 + s)))
+            ws.append(pc.dev(np.exp(0.3 * rng.normal(size=shape))))
+        t = pc.dev(rng.normal(size=shape))
+        j = pc.dev(rng.normal(size=shape))
+        mine = list(range(rank, nsamp, world))
+        M = nb.SampledCFMetric(cf, [tabs[s] for s in mine], [ws[s] for s in mine], comm=Comm(), n_total=nsamp)
+        Mall = nb.SampledCFMetric(cf, tabs, ws)
+        q, curv = M.apply_with_curvature(t)
+        qa, curva = Mall.apply_with_curvature(t)
+        r = cgm._cg(M, j, None, resnorm=1e-8 * float(torch.linalg.vector_norm(j)), maxiter=100)
+        ra = cgm._cg(Mall, j, None, resnorm=1e-8 * float(torch.linalg.vector_norm(j)), maxiter=100)
+        if rank == 0:
+            result.update(err=pc.rel(pc.host(q), pc.host(qa)), errc=abs(float(curv) - float(curva)) / abs(float(curva)),
+                          nit=(r.nit, ra.nit), errx=pc.rel(pc.host(r.x), pc.host(ra.x)))
+    finally:
+        dist.destroy_process_group()
+
+
+def launch_sampled(world, emu_path, shape, port=29591):
+    import torch.multiprocessing as mp
+    mgr = mp.Manager()
+    result = mgr.dict()
+    mp.spawn(run_sampled, args=(world, port, emu_path, shape, result), nprocs=world, join=True)
+    return dict(result)

@@ -361,6 +361,54 @@ def check_metric(shape, dist, dt=np.float64, likelihood="gaussian"):
     assert abs(a - b) <= (1e-11 if dt == np.float64 else 1e-4) * max(abs(a), abs(b))
 
 
+def check_sampled_metric(shape, dist, dt=np.float64, nsamples=3, likelihood="gaussian"):
+    """SampledCFMetric == the mean over the samples of the oracle's per-sample metrics (optimize_kl.py:103-120),
+    every sample with its own amplitude tables and weight; curvature; a CG solve on it with identical counts."""
+    tdt = torch.float64 if dt == np.float64 else torch.float32
+    if likelihood == "poisson":
+        cf, co = make_pair(shape, dist, tdt, offset=0.0, kw=C2_KW, offset_std=(1e-3, 1e-4))
+    else:
+        cf, co = make_pair(shape, dist, tdt, kw=GENTLE_KW)
+    rng = np.random.default_rng(21)
+    tabs, ws, mats = [], [], []
+    for s in range(nsamples):
+        p = cf.init(100 + s)                          # expansion point of sample s: position + sample
+        amps_o, azm_o = co.normalized_amplitudes(p), co.azm(p)
+        tabs.append(cf.tables_from_amplitudes(amps_o, float(azm_o)))
+        w = (om.poisson_exp_weight(co(p)) if likelihood == "poisson" else np.exp(0.3 * rng.normal(size=shape))).astype(dt)
+        ws.append(dev(w))
+        A = azm_o * co.outer_amplitude(amps_o)
+        mats.append((A, w.astype(np.float64)))
+
+    def Mo(t):
+        acc = np.zeros(shape)
+        for A, w in mats:
+            h = co.harmonic_transform(A * t)
+            g = w * h
+            for gr, ax in reversed(list(zip(co.grids, co.axes))):
+                g = (1.0 / gr.total_volume) * otr.hartley(g, axes=ax)
+            acc += A * g
+        return acc / len(mats) + t
+    M = nb.SampledCFMetric(cf, tabs, ws)
+    x = rng.normal(size=shape).astype(dt)
+    ref = Mo(x.astype(np.float64))
+    q, curv = M.apply_with_curvature(dev(x))
+    assert rel(host(q), ref) <= TOL[dt], (shape, dt, rel(host(q), ref))
+    c_ref = np.vdot(x.astype(np.float64), host(q).astype(np.float64))
+    assert abs(float(curv.cpu()) - c_ref) <= 1e-12 * abs(c_ref)
+    assert rel(host(M(dev(x))), ref) <= TOL[dt]
+    # one sample == the plain metric
+    M1 = nb.SampledCFMetric(cf, tabs[:1], ws[:1])
+    assert rel(host(M1(dev(x))), host(nb.CFMetric(cf, tabs[0], ws[0])(dev(x)))) <= (1e-14 if dt == np.float64 else 1e-6)
+    if dt == np.float64:
+        j = rng.normal(size=shape)
+        kw = dict(resnorm=1e-6 * float(np.linalg.norm(j)), maxiter=200)
+        r, ro = cgm._cg(M, dev(j), None, **kw), ocg.cg_re(Mo, j, None, **kw)
+        s_ = cgm._static_cg(M, dev(j), None, **kw)            # device-resident loop on the sampled metric
+        assert abs(r.nit - ro.nit) <= 1 and r.info == ro.info == 0 and tuple(s_[1:]) == tuple(r[1:])
+        assert rel(host(r.x), ro.x) <= 1e-5 and rel(Mo(host(r.x)), j) <= 1e-5
+
+
 GENTLE_KW = dict(fluctuations=(1., .1), loglogavgslope=(-1.5, .1), flexibility=(1., .2), asperity=(.5, 5e-2))
 
 def check_baseline_size(shape, dt):

@@ -64,3 +64,9 @@ def test_symmetric_split_is_a_partition():
 def test_slab_two_ranks_gloo_fp32():
     res = dist_worker.launch(2, "gloo", conftest.build_emulator(), (16, 16, 32), port=29547, mode="large", dtype="f32")
     check(res)
+
+
+def test_sampled_metric_samples_sharded_over_ranks():
+    res = dist_worker.launch_sampled(2, conftest.build_emulator(), (16, 16))
+    assert res["err"] <= 1e-13 and res["errc"] <= 1e-13, res
+    assert res["nit"][0] == res["nit"][1] and res["errx"] <= 1e-10, res

@@ -110,6 +110,12 @@ def test_static_cg_device_resident(shape, dist):
     pc.check_static_cg_device_resident(shape, dist, np.float32, "poisson" if len(shape) == 2 else "gaussian")
 
 
+@pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((8, 8, 16), (1 / 8, 1 / 8, 1 / 16))])
+def test_sampled_metric(shape, dist):
+    pc.check_sampled_metric(shape, dist)
+    pc.check_sampled_metric(shape, dist, np.float32, 4, "poisson" if len(shape) == 2 else "gaussian")
+
+
 def test_cg_failure_modes():
     pc.check_cg_failure_modes()
 

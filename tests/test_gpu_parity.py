@@ -132,6 +132,12 @@ def test_static_cg_device_resident(shape, dist):
     pc.check_static_cg_device_resident(shape, dist, np.float32, "poisson" if len(shape) == 2 else "gaussian")
 
 
+@pytest.mark.parametrize("shape,dist", [((32, 32), 1 / 32), ((256, 256), 1 / 256), ((64, 64, 64), 1 / 64), ((256, 16, 256), (1 / 256, 1 / 16, 1 / 256))])
+def test_sampled_metric(shape, dist):
+    pc.check_sampled_metric(shape, dist)
+    pc.check_sampled_metric(shape, dist, np.float32, 4, "poisson" if len(shape) == 2 else "gaussian")
+
+
 def test_cg_failure_modes():
     pc.check_cg_failure_modes()
 
