@@ -226,14 +226,21 @@ int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, c
  *   (table[table_idx[k]] = amp[k], float if table_f32 else double: the ksq table of amp_mode 1);
  *   scratch (2 nb + 2 doubles) keeps what the VJP needs.
  * vjp: given ampbar (nb, cotangent of amp; entry 0 ignored) -> xibar (nb-2, 2) and
- *   scalars_bar[5] = cotangents of (flu, slope, flx, asp, azm) through the chain.  Consumes the scratch. */
+ *   scalars_bar[5] = cotangents of (flu, slope, flx, asp, azm) through the chain.  Needs `work` (2 nb doubles);
+ *   the forward's scratch is only read, so jvp / vjp may be called any number of times per forward. */
 int nb2_amplitude_forward(int64_t nb, const double* rel, const double* dt, const double* mult, double totvol,
                           const double* xi, double flu, double slope, double flx, double asp, double azm, int power_kind,
                           double* scratch, double* amp, void* table, const int64_t* table_idx, int table_f32, void* stream);
+/* jvp: tangents dxi (nb-2, 2; NULL = 0) and dscalars[5] = tangents of (flu, slope, flx, asp, azm) -> damp (nb),
+ *   the tangent of amp (damp[0] = 0).  Reads the forward's scratch, needs `work` (2 nb doubles) of its own. */
+int nb2_amplitude_jvp(int64_t nb, const double* rel, const double* dt, const double* mult, double totvol,
+                      const double* xi, double flu, double slope, double flx, double asp, double azm, int power_kind,
+                      const double* scratch, const double* amp, const double* dxi, const double* dscalars_host,
+                      double* work, double* damp, void* stream);
 int nb2_amplitude_vjp(int64_t nb, const double* rel, const double* dt, const double* mult, double totvol,
                       const double* xi, double flu, double slope, double flx, double asp, double azm, int power_kind,
-                      double* scratch, const double* amp, const double* ampbar, double* xibar, double* scalars_bar,
-                      void* stream);
+                      const double* scratch, const double* amp, const double* ampbar, double* work, double* xibar,
+                      double* scalars_bar, void* stream);
 
 /* ---- Device-resident conjugate gradient (static_cg, src/re/conjugate_gradient.py:219-389: the reference keeps
  * the whole loop on the device inside lax.while_loop, :382).  The scalars of the recurrence live in a DEVICE

@@ -170,8 +170,9 @@ struct AmplitudeVjp {
         const double* amp;      // forward output (nb)
         const double* sums;     // forward output: S, c
         const double* ampbar;   // (nb)
-        double* ln;             // forward scratch (nb): ln_k in, overwritten by lb_k
-        double* inc;            // scratch (nb - 2): overwritten by incbar_m
+        const double* ln;       // forward scratch (nb): ln_k, read only
+        double* lb;             // work (nb): cotangent of ln_k
+        double* inc;            // work (nb - 2): incbar_m
         double* xibar;          // out (nb - 2, 2) (may be NULL without flexibility)
         double* scalars_bar;    // out (5)
     };
@@ -219,7 +220,7 @@ struct AmplitudeVjp {
                 const double aa = p.ampbar[k] * p.amp[k];
                 const double lb = p.s.power_kind ? 0.5 * aa - 0.5 * G * p.g.mult[k] * sp / S
                                                  : aa - G * p.g.mult[k] * sp * sp / S;
-                p.ln[k] = lb;
+                p.lb[k] = lb;
                 acc += lb * p.g.rel[k];
             };
             if (tid == 0 && nb > 1) bin(1);
@@ -238,7 +239,7 @@ struct AmplitudeVjp {
             double acc = 0.0;
             if (flex) {
                 const double corr = -sc[1] / p.g.rel[nb - 1];
-                for (long long m = s0; m < s1; ++m) acc += p.ln[m + 2] + (m + 2 == nb - 1 ? corr : 0.0);
+                for (long long m = s0; m < s1; ++m) acc += p.lb[m + 2] + (m + 2 == nb - 1 ? corr : 0.0);
             }
             sm[tid] = acc;
         } else if (PH == 5 || PH == 7) {
@@ -248,7 +249,7 @@ struct AmplitudeVjp {
             if (flex) {
                 const double corr = -sc[1] / p.g.rel[nb - 1];
                 for (long long m = s1 - 1; m >= s0; --m) {
-                    suf += p.ln[m + 2] + (m + 2 == nb - 1 ? corr : 0.0);
+                    suf += p.lb[m + 2] + (m + 2 == nb - 1 ? corr : 0.0);
                     p.inc[m] = suf;
                     acc += p.g.dt[m] * suf;
                 }
@@ -281,6 +282,120 @@ struct AmplitudeVjp {
                 p.scalars_bar[2] = fa;
                 p.scalars_bar[3] = p.s.asp >= 0.0 ? aa : 0.0;
             }
+        }
+    }
+};
+
+// ---------------------------------------------------------------- JVP of the chain (forward mode)
+// Tangents (dxi (nb - 2, 2), dflu, dslope, dflx, dasp, dazm) -> damp (nb), the tangent of the normalised
+// amplitudes (damp_0 = 0), with the forward's ln / amp / S:
+//   da_m = dflx sqrt(dt_m);  ddev_m = da_m xi1 + a_m dxi1
+//   dlvl_m = (da_m xi0 + a_m dxi0) sqrt(q_m) + a_m xi0 dasp / (2 sqrt(q_m)) + dt_m ddev_m / 2
+//   drate / dinc / dtwolog: the same two prefix sums as the forward;  dln_k = dslope rel_k + dtwolog_k - dtwolog_last rel_k / rel_last
+//   power:      dS = sum mult spec dln,      damp_k = amp_k (dc/c + dln_k / 2)
+//   amplitude:  dS = sum 2 mult spec^2 dln,  damp_k = amp_k (dc/c + dln_k)
+//   dc/c = dflu / flu - dazm / azm - dS / (2 S)
+struct AmplitudeJvp {
+    static constexpr int NPHASES = 7;
+    static constexpr int MAX_THREADS = kAmpThreads;
+    static constexpr int MIN_BLOCKS = 1;
+    struct Params {
+        AmpGeom g;
+        AmpScalars s;
+        AmpScalars ds;          // tangents of (flu, slope, flx, asp, azm); power_kind unused
+        const double* xi;
+        const double* dxi;      // (nb - 2, 2) (NULL: zero)
+        const double* ln;       // forward scratch (nb), read only
+        const double* amp;      // forward output
+        const double* sums;     // forward: S, c
+        double* dinc;           // scratch (nb - 2)
+        double* dln;            // scratch (nb)
+        double* damp;           // out (nb)
+    };
+    static size_t smem_bytes(int nthreads) { return size_t(nthreads + 2) * sizeof(double); }
+    NB2_HDC static bool enabled(int) { return true; }
+
+    NB2_HD static void step(const Params& p, long long m, double asp, double& ddev, double& dlvl) {
+        const double dt = p.g.dt[m], sq = sqrt(dt), a = p.s.flx * sq, da = p.ds.flx * sq;
+        const double x0 = p.xi[2 * m], x1 = p.xi[2 * m + 1];
+        const double d0 = p.dxi ? p.dxi[2 * m] : 0.0, d1 = p.dxi ? p.dxi[2 * m + 1] : 0.0;
+        const double rq = sqrt(dt * dt / 12.0 + asp);
+        ddev = da * x1 + a * d1;
+        dlvl = (da * x0 + a * d0) * rq + (p.s.asp >= 0.0 ? a * x0 * p.ds.asp / (2.0 * rq) : 0.0) + 0.5 * dt * ddev;
+    }
+
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long, int tid, int nthreads, char* smem_raw) {
+        double* sm = reinterpret_cast<double*>(smem_raw);
+        const long long nb = p.g.nb, n = nb > 2 ? nb - 2 : 0;
+        const bool flex = p.s.flx >= 0.0 && n > 0 && p.xi != nullptr;
+        const double asp = p.s.asp >= 0.0 ? p.s.asp : 0.0;
+        long long s0, s1;
+        amp_segment(n, tid, nthreads, s0, s1);
+        if (PH == 0) {
+            double acc = 0.0;
+            if (flex)
+                for (long long m = s0; m < s1; ++m) {
+                    double ddev, dlvl;
+                    step(p, m, asp, ddev, dlvl);
+                    acc += ddev;
+                }
+            sm[tid] = acc;
+        } else if (PH == 1 || PH == 3) {
+            if (tid == 0) {
+                double run = 0.0;
+                for (int t = 0; t < nthreads; ++t) {
+                    const double v = sm[t];
+                    sm[t] = run;
+                    run += v;
+                }
+                sm[nthreads] = run;
+            }
+        } else if (PH == 2) {
+            double rate = sm[tid], acc = 0.0;
+            if (flex)
+                for (long long m = s0; m < s1; ++m) {
+                    double ddev, dlvl;
+                    step(p, m, asp, ddev, dlvl);
+                    const double dinc = dlvl + p.g.dt[m] * rate;
+                    p.dinc[m] = dinc;
+                    acc += dinc;
+                    rate += ddev;
+                }
+            sm[tid] = acc;
+        } else if (PH == 4) {
+            const double total = sm[nthreads];
+            const double rlast = nb > 1 ? p.g.rel[nb - 1] : 1.0;
+            double tw = sm[tid], acc = 0.0;
+            auto bin = [&](long long k, double dtw) {
+                const double r = p.g.rel[k];
+                const double dln = p.ds.slope * r + (flex ? dtw - total * (r / rlast) : 0.0);
+                p.dln[k] = dln;
+                const double sp = exp(p.ln[k]);
+                acc += p.g.mult[k] * (p.s.power_kind ? sp : 2.0 * sp * sp) * dln;
+            };
+            if (tid == 0) {
+                p.dln[0] = 0.0;
+                if (nb > 1) bin(1, 0.0);
+            }
+            for (long long m = s0; m < s1; ++m) {
+                if (flex) tw += p.dinc[m];
+                bin(m + 2, tw);
+            }
+            sm[tid] = acc;
+        } else if (PH == 5) {
+            if (tid == 0) {
+                double dS = 0.0;
+                for (int t = 0; t < nthreads; ++t) dS += sm[t];
+                sm[nthreads] = p.ds.flu / p.s.flu - p.ds.azm / p.s.azm - 0.5 * dS / p.sums[0];   // dc / c
+            }
+        } else if (PH == 6) {
+            const double dcc = sm[nthreads], f = p.s.power_kind ? 0.5 : 1.0;
+            if (tid == 0) {
+                p.damp[0] = 0.0;
+                if (nb > 1) p.damp[1] = p.amp[1] * (dcc + f * p.dln[1]);
+            }
+            for (long long m = s0; m < s1; ++m) p.damp[m + 2] = p.amp[m + 2] * (dcc + f * p.dln[m + 2]);
         }
     }
 };

@@ -881,17 +881,32 @@ int nb2_amplitude_forward(int64_t nb, const double* rel, const double* dt, const
     return rt_launch<AmplitudeForward>(1, kAmpThreads, AmplitudeForward::smem_bytes(kAmpThreads), (rt_stream)stream, p);
 }
 
+int nb2_amplitude_jvp(int64_t nb, const double* rel, const double* dt, const double* mult, double totvol,
+                      const double* xi, double flu, double slope, double flx, double asp, double azm, int power_kind,
+                      const double* scratch, const double* amp, const double* dxi, const double* dscalars_host,
+                      double* work, double* damp, void* stream) {
+    if (nb < 1 || !rel || !mult || !scratch || !amp || !dscalars_host || !work || !damp || (nb > 2 && !dt)) {
+        last_error() = "nb2_amplitude_jvp: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    const double* d = dscalars_host;
+    AmplitudeJvp::Params p{{nb, rel, dt, mult, totvol}, {flu, slope, flx, asp, azm, power_kind},
+                           {d[0], d[1], d[2], d[3], d[4], power_kind}, xi, dxi, scratch + nb, amp, scratch + 2 * nb,
+                           work, work + nb, damp};
+    return rt_launch<AmplitudeJvp>(1, kAmpThreads, AmplitudeJvp::smem_bytes(kAmpThreads), (rt_stream)stream, p);
+}
+
 int nb2_amplitude_vjp(int64_t nb, const double* rel, const double* dt, const double* mult, double totvol,
                       const double* xi, double flu, double slope, double flx, double asp, double azm, int power_kind,
-                      double* scratch, const double* amp, const double* ampbar, double* xibar, double* scalars_bar,
-                      void* stream) {
-    if (nb < 1 || !rel || !mult || !scratch || !amp || !ampbar || !scalars_bar || (nb > 2 && !dt) ||
+                      const double* scratch, const double* amp, const double* ampbar, double* work, double* xibar,
+                      double* scalars_bar, void* stream) {
+    if (nb < 1 || !rel || !mult || !scratch || !amp || !ampbar || !work || !scalars_bar || (nb > 2 && !dt) ||
         (flx >= 0.0 && nb > 2 && xi && !xibar)) {
         last_error() = "nb2_amplitude_vjp: invalid argument";
         return NB2_ERR_ARG;
     }
     AmplitudeVjp::Params p{{nb, rel, dt, mult, totvol}, {flu, slope, flx, asp, azm, power_kind}, xi, amp,
-                           scratch + 2 * nb, ampbar, scratch + nb, scratch, xibar, scalars_bar};
+                           scratch + 2 * nb, ampbar, scratch + nb, work + nb, work, xibar, scalars_bar};
     return rt_launch<AmplitudeVjp>(1, kAmpThreads, AmplitudeVjp::smem_bytes(kAmpThreads), (rt_stream)stream, p);
 }
 

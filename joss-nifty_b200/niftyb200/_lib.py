@@ -85,8 +85,12 @@ class Library:
         "nb2_amplitude_forward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_double, c_void_p, c_double, c_double,
                                           c_double, c_double, c_double, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_int, c_void_p]),
+        "nb2_amplitude_jvp": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_double, c_void_p, c_double, c_double, c_double,
+                                      c_double, c_double, c_int, c_void_p, c_void_p, c_void_p, POINTER(c_double), c_void_p,
+                                      c_void_p, c_void_p]),
         "nb2_amplitude_vjp": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_double, c_void_p, c_double, c_double, c_double,
-                                      c_double, c_double, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+                                      c_double, c_double, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_void_p]),
         "nb2_cg_decide": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
         "nb2_set_launch_gate": (c_int, [c_void_p]),
         "nb2_cg_update_dev": (c_int, [c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,

@@ -178,12 +178,13 @@ class _Fluctuations:
         xi, sc, lat = ctx["xi"], ctx["sc"], ctx["lat"]
         xibar = torch.zeros_like(xi) if xi is not None else None
         sbar = torch.zeros(5, dtype=torch.float64, device=g.device)
+        work = torch.empty(2 * nbins, dtype=torch.float64, device=g.device)
         from .transforms import _ptr, _stream
         ab = ampbar.to(device=g.device, dtype=torch.float64).contiguous()
         rc = lib.nb2_amplitude_vjp(nbins, _ptr(lib, rel), _ptr(lib, dt) if nbins > 2 else None, _ptr(lib, mult),
                                    float(g.total_volume), _ptr(lib, xi), sc["flu"], sc["slope"], sc["flx"], sc["asp"],
                                    sc["azm"], ctx["kind"], _ptr(lib, ctx["scratch"]), _ptr(lib, ctx["amp"]), _ptr(lib, ab),
-                                   _ptr(lib, xibar), _ptr(lib, sbar), _stream(ab))
+                                   _ptr(lib, work), _ptr(lib, xibar), _ptr(lib, sbar), _stream(ab))
         lib.check(rc, "nb2_amplitude_vjp")
         sb = sbar.cpu().numpy()
         out = {pf + "fluctuations": sb[0] * pr["fluctuations"].grad(lat["fluctuations"]),
@@ -194,6 +195,34 @@ class _Fluctuations:
         if "asperity" in lat:
             out[pf + "asperity"] = sb[3] * pr["asperity"].grad(lat["asperity"])
         return out, float(sb[4])
+
+    def jvp_kernel(self, ctx, t, dazm):
+        """Tangent of this sub-space's normalised amplitudes for the latent tangents ``t`` (dict of the
+        sub-space's leaves; missing = 0) and the tangent ``dazm`` of the zero-mode amplitude."""
+        import ctypes
+        lib = _lib.get()
+        g, pr, pf = self.grid, self.priors, self.prefix
+        rel, dt, mult = self._geom_args()
+        nbins = int(rel.numel())
+        xi, sc, lat = ctx["xi"], ctx["sc"], ctx["lat"]
+
+        def ds(name):
+            v = t.get(pf + name)
+            return 0.0 if (v is None or name not in lat) else float(np.asarray(v)) * pr[name].grad(lat[name])
+        dsc = (ctypes.c_double * 5)(ds("fluctuations"), ds("loglogavgslope"), ds("flexibility"), ds("asperity"), float(dazm))
+        dxi = t.get(pf + "spectrum") if xi is not None else None
+        if dxi is not None:
+            dxi = (dxi if isinstance(dxi, torch.Tensor) else torch.as_tensor(np.asarray(dxi))).to(device=g.device,
+                                                                                                  dtype=torch.float64).contiguous()
+        work = torch.empty(2 * nbins, dtype=torch.float64, device=g.device)
+        damp = torch.empty(nbins, dtype=torch.float64, device=g.device)
+        from .transforms import _ptr, _stream
+        rc = lib.nb2_amplitude_jvp(nbins, _ptr(lib, rel), _ptr(lib, dt) if nbins > 2 else None, _ptr(lib, mult),
+                                   float(g.total_volume), _ptr(lib, xi), sc["flu"], sc["slope"], sc["flx"], sc["asp"],
+                                   sc["azm"], ctx["kind"], _ptr(lib, ctx["scratch"]), _ptr(lib, ctx["amp"]), _ptr(lib, dxi),
+                                   dsc, _ptr(lib, work), _ptr(lib, damp), _stream(damp))
+        lib.check(rc, "nb2_amplitude_jvp")
+        return damp
 
     def amplitude(self, p):
         """Un-normalised amplitude per power bin (fp64 device tensor)."""
@@ -370,6 +399,43 @@ class CorrelatedField:
         tab = self.tables_from_amplitudes(amps, float(azm))
         tab.chain = ctxs          # what vjp_latent needs to continue through the amplitude chain
         return tab
+
+    def jvp_latent(self, t, p, convention=None, tab=None, mul=None, out=None):
+        """Directional derivative of the model along the latent tangent ``t`` (dict over the leaves; missing = 0):
+        ``d cf(p)[t]`` -- ``lin.jac(t)`` / ``jax.jvp`` (golden ``jvp`` vectors).  With
+        ``A = azm prod_g amp_g[pindex_g]``:  ``dy = (1/V) H(dA xi + A dxi) = (1/V) H(A (R xi + dxi))``,
+        ``R = dA / A = dazm/azm + sum_g damp_g/amp_g`` (amp_g[0] is a constant), so the tangent costs ONE fused
+        transform after an O(N) combine.  ``mul``: fused multiplier on the last store (likelihood weight)."""
+        tab = self.tables(p) if tab is None else tab
+        if getattr(tab, "chain", None) is None or any(c is None for c in tab.chain) or not isinstance(self._azm, _ScalarPrior):
+            raise NotImplementedError("jvp_latent: non-parametric spectra with standard (mean, std) priors")
+        zl = float(np.asarray(p[self.prefix + "zeromode"]))
+        azm = self._azm.value(zl)
+        tz = t.get(self.prefix + "zeromode")
+        dazm = 0.0 if tz is None else float(np.asarray(tz)) * self._azm.grad(zl)
+        ratio = None
+        iso = self.single and self.grids[0].isotropic and self.plans[0].is_fast
+        for f, g, ctx, a in zip(self.fl, self.grids, tab.chain, tab.amps):
+            damp = f.jvp_kernel(ctx, t, dazm)
+            r = damp / a
+            r[0] = 0.0                                           # amp[0] = totvol: constant
+            if iso:     # the gather through the ksq table, as for the amplitude itself: no N-sized index
+                ratio = self.plans[0].expand_table(g.ksq_table(r + dazm / azm, self.dtype))
+                break
+            e = g.expand(r, torch.float64)
+            if ratio is None:
+                ratio = e
+            else:
+                shp = list(ratio.shape) + [1] * e.dim()
+                ratio = ratio.reshape(shp) + e
+        if not iso:
+            ratio = (ratio + dazm / azm).to(self.dtype)
+        xi = self._as_dev(p[self.prefix + "xi"], self.dtype)
+        v = ratio * xi
+        dxi = t.get(self.prefix + "xi")
+        if dxi is not None:
+            v = v + self._as_dev(dxi, self.dtype)
+        return self.apply_xi(v.contiguous(), tab, out=out, convention=convention, offset=0.0, mul=mul)
 
     def vjp_latent(self, ybar, p, convention=None, tab=None):
         """Cotangent of EVERY latent leaf of the model for the position-space cotangent ``ybar`` -- the

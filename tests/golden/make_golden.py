@@ -128,6 +128,10 @@ def gen_cf():
             ntang = ift.MultiField.from_dict({k: ift.makeField(cf.domain[k], v) for k, v in tang.items()},
                                              cf.domain)
             jvp = lin.jac(ntang).val
+            # full-latent metric of a Gaussian likelihood with diagonal inverse noise covariance w:
+            # M t = J^T w J t + t  (SandwichOperator.make(J) with N^-1, + the prior's identity)
+            wgt = np.exp(0.3 * rng.normal(size=val.shape))
+            mt = lin.jac.adjoint_times(ift.makeField(cf.target, wgt * jvp)) + ntang
             tag = f"{name}_{conv}"
             for k, v in pos.items():
                 out[f"{tag}_pos_{k}"] = v
@@ -136,6 +140,9 @@ def gen_cf():
             out[f"{tag}_val"] = val
             out[f"{tag}_ybar"] = ybar
             out[f"{tag}_jvp"] = jvp
+            out[f"{tag}_mweight"] = wgt
+            for k in pos:
+                out[f"{tag}_mt_{k}"] = mt[k].val
             out[f"{tag}_azm"] = np.asarray(cfm.azm.force(npos).val)
             for i, a in enumerate(cfm.get_normalized_amplitudes()):
                 out[f"{tag}_namp{i}"] = a.force(npos).val

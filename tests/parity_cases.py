@@ -236,6 +236,47 @@ def check_cf_latent_vjp_golden(golden, names):
                 assert rel(got, ref) <= (1e-9 if k.endswith("zeromode") else 1e-10), (tag, k, rel(got, ref))
 
 
+def check_latent_metric_golden(golden, names):
+    """The metric over the FULL latent vector, ``M t = J^T w J t + t`` (evi.py:108-109, likelihood.py:568-576),
+    against vectors computed by the real reference (make_golden.py: ``mt_<leaf>`` = ``jac.adjoint_times(w *
+    jac(t)) + t``); the JVP against ``jvp``; symmetry; and a full MGVI sample draw (``draw_linear_residual``,
+    evi.py:83-144) whose solution must satisfy ``M x = j`` for the reference-built ``M``."""
+    from test_oracle_golden import CF_CASES, golden_pos, build_oracle_cf
+    g = golden["correlated_field"]
+    for name in names:
+        subs, off_mean, off_std = CF_CASES[name]
+        mk = nb.CorrelatedFieldMaker("")
+        mk.set_amplitude_total_offset(off_mean, off_std)
+        for i, (shape, dist, kw) in enumerate(subs):
+            mk.add_fluctuations(shape, dist, **kw, prefix="" if len(subs) == 1 else f"ax{i}", non_parametric_kind="power")
+        cf, co = mk.finalize(), build_oracle_cf(name)
+        for conv in CONVS:
+            tag = f"{name}_{conv}"
+            p, t = golden_pos(g, tag, co), golden_pos(g, tag, co, "tan")
+            assert rel(host(cf.jvp_latent(t, p, convention=conv)), g[f"{tag}_jvp"]) <= 1e-12, tag
+            M = nb.LatentMetric(cf, p, dev(g[f"{tag}_mweight"]), convention=conv)
+            lay = M.layout
+            tf = lay.flatten(t)
+            mt = lay.unflatten(M(tf))
+            for k in cf.domain:
+                ref = g[f"{tag}_mt_{k}"]
+                got = host(mt[k])
+                got = got.T if k.endswith("spectrum") else got
+                assert rel(got, ref) <= 1e-9, (tag, k, rel(got, ref))
+            # symmetric: <u, M v> == <M u, v>
+            rng = np.random.default_rng(1)
+            u, v = dev(rng.normal(size=lay.size)), dev(rng.normal(size=lay.size))
+            a, b = float(torch.dot(u, M(v))), float(torch.dot(M(u), v))
+            assert abs(a - b) <= 1e-10 * max(abs(a), abs(b)), tag
+        # MGVI sample on the full latent space: solve, then verify with the metric itself and its counts
+        wd, wp = rng.normal(size=cf.shape), dev(rng.normal(size=lay.size))
+        j = M.sample_rhs(dev(wd), wp)
+        x, info = nb.draw_linear_residual(M, dev(wd), wp, cg_kwargs=dict(resnorm=1e-9 * float(torch.linalg.vector_norm(j)),
+                                                                          maxiter=20 * lay.size))
+        assert info == 0
+        assert float(torch.linalg.vector_norm(M(x) - j) / torch.linalg.vector_norm(j)) <= 1e-8, name
+
+
 def check_cf_latent_vjp_directional(shape, dist, kind="power", seed=5):
     """<ybar, d cf(p)[t]> == <vjp_latent(ybar), t> with the directional derivative by central differences of the
     ORACLE model (fp64), for a random direction t over all latent leaves -- at bin counts beyond the golden

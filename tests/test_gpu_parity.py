@@ -77,6 +77,10 @@ def test_cf_latent_vjp_golden(golden):
     pc.check_cf_latent_vjp_golden(golden, ["cf1d", "cf2d", "cf2d_odd", "cf3d", "cfprod"])
 
 
+def test_latent_metric_golden(golden):
+    pc.check_latent_metric_golden(golden, ["cf1d", "cf2d", "cf2d_odd", "cf3d", "cfprod"])
+
+
 @pytest.mark.parametrize("shape,dist,kind", [((64, 64), 1 / 64, "power"), ((16, 16, 16), 1 / 16, "amplitude"), ((2048,), 0.01, "power"), ((512, 512), 1 / 512, "power"), ((64, 64, 64), 1 / 64, "amplitude")])
 def test_cf_latent_vjp_directional(shape, dist, kind):
     pc.check_cf_latent_vjp_directional(shape, dist, kind)
