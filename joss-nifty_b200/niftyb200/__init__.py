@@ -16,6 +16,8 @@ from .metric import CFMetric, SampledCFMetric  # noqa: F401
 from .cg import (ConjugateGradient, QuadraticEnergy, GradientNormController,  # noqa: F401
                  AbsDeltaEnergyController, cg, static_cg, CGResults)
 from .latent import LatentLayout, LatentMetric, draw_linear_residual  # noqa: F401
+from .optimize import newton_cg, OptimizeResults  # noqa: F401
+from .evi import GaussianCFModel, nonlinearly_update_residual  # noqa: F401
 from .distributed import SlabCorrelatedField, SlabHartley, SymmetricSplit  # noqa: F401
 from .operators import FFTOperator, HartleyOperator, HarmonicTransformOperator, RGSpace  # noqa: F401
 

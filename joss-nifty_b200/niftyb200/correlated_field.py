@@ -37,6 +37,13 @@ def lognormal_moments(mean, std):
     return math.log(mean) - 0.5 * logstd ** 2, logstd
 
 
+def _host_float(v):
+    """Scalar leaf (NumPy / Python number or 0-d tensor on any device) as a Python float."""
+    if isinstance(v, torch.Tensor):
+        return float(v.detach().cpu())
+    return float(np.asarray(v))
+
+
 class _ScalarPrior:
     """Standard-normal excitation -> parameter (re/num/stats_distributions.py:41-88), callable on torch
     tensors like the plain lambdas, plus value and derivative as host floats for the scalar leaves (the
@@ -125,13 +132,13 @@ class _Fluctuations:
 
     def _chain_inputs(self, p, azm):
         g, pr, pf = self.grid, self.priors, self.prefix
-        lat = {k: float(np.asarray(p[pf + k])) for k in ("fluctuations", "loglogavgslope")}
+        lat = {k: _host_float(p[pf + k]) for k in ("fluctuations", "loglogavgslope")}
         flex = pr["flexibility"] is not None and g.log_volume.numel() > 0
         asp = flex and pr["asperity"] is not None
         if flex:
-            lat["flexibility"] = float(np.asarray(p[pf + "flexibility"]))
+            lat["flexibility"] = _host_float(p[pf + "flexibility"])
         if asp:
-            lat["asperity"] = float(np.asarray(p[pf + "asperity"]))
+            lat["asperity"] = _host_float(p[pf + "asperity"])
         xi = None
         if flex:
             v = p[pf + "spectrum"]
@@ -208,7 +215,7 @@ class _Fluctuations:
 
         def ds(name):
             v = t.get(pf + name)
-            return 0.0 if (v is None or name not in lat) else float(np.asarray(v)) * pr[name].grad(lat[name])
+            return 0.0 if (v is None or name not in lat) else _host_float(v) * pr[name].grad(lat[name])
         dsc = (ctypes.c_double * 5)(ds("fluctuations"), ds("loglogavgslope"), ds("flexibility"), ds("asperity"), float(dazm))
         dxi = t.get(pf + "spectrum") if xi is not None else None
         if dxi is not None:
@@ -376,7 +383,7 @@ class CorrelatedField:
         Matern spectra / user prior callables use torch ops."""
         zl = p[self.prefix + "zeromode"]
         if isinstance(self._azm, _ScalarPrior):
-            azm = self._azm.value(float(np.asarray(zl.cpu() if isinstance(zl, torch.Tensor) else zl)))
+            azm = self._azm.value(_host_float(zl))
         else:
             azm = self._azm(self._as_dev(zl))
         out, ctxs, pd = [], [], None
@@ -409,10 +416,10 @@ class CorrelatedField:
         tab = self.tables(p) if tab is None else tab
         if getattr(tab, "chain", None) is None or any(c is None for c in tab.chain) or not isinstance(self._azm, _ScalarPrior):
             raise NotImplementedError("jvp_latent: non-parametric spectra with standard (mean, std) priors")
-        zl = float(np.asarray(p[self.prefix + "zeromode"]))
+        zl = _host_float(p[self.prefix + "zeromode"])
         azm = self._azm.value(zl)
         tz = t.get(self.prefix + "zeromode")
-        dazm = 0.0 if tz is None else float(np.asarray(tz)) * self._azm.grad(zl)
+        dazm = 0.0 if tz is None else _host_float(tz) * self._azm.grad(zl)
         ratio = None
         iso = self.single and self.grids[0].isotropic and self.plans[0].is_fast
         for f, g, ctx, a in zip(self.fl, self.grids, tab.chain, tab.amps):
@@ -455,7 +462,7 @@ class CorrelatedField:
             leaves, azm_chain = f.vjp_kernel(ctx, ab)
             out.update(leaves)
             azmbar += azm_chain
-        zl = float(np.asarray(p[self.prefix + "zeromode"]))
+        zl = _host_float(p[self.prefix + "zeromode"])
         out[self.prefix + "zeromode"] = azmbar * self._azm.grad(zl)
         return out
 

@@ -785,6 +785,97 @@ def check_static_cg_device_resident(shape, dist, dt=np.float64, likelihood="gaus
     assert (r.info, r.nit) == (-1, 1)
 
 
+def check_newton_cg_parity(n=64, seed=2):
+    """``newton_cg`` against the oracle's restatement of ``_newton_cg`` (optimize.py:102-240) on analytic convex
+    functions: identical nit / status / nfev / njev / nhev and the same minimiser -- the control flow (CG tolerances
+    per step, line search with the steepest-descent reset, stopping tests)."""
+    from oracle import optimize as oopt
+    rng = np.random.default_rng(seed)
+    a, b, d = rng.uniform(0.5, 2.0, n), rng.normal(size=n), rng.uniform(0.1, 3.0, n)
+    at, bt, dt_ = dev(a), dev(b), dev(d)
+
+    def f_np(x):
+        return float(np.sum(np.cosh(a * x)) - b @ x + 0.5 * np.sum(d * x * x)), a * np.sinh(a * x) - b + d * x
+
+    def h_np(x, t):
+        return (a * a * np.cosh(a * x) + d) * t
+
+    def f_t(x):
+        return float((torch.cosh(at * x).sum() - bt @ x + 0.5 * (dt_ * x * x).sum()).cpu()), at * torch.sinh(at * x) - bt + dt_ * x
+
+    def h_t(x, t):
+        return (at * at * torch.cosh(at * x) + dt_) * t
+    x0 = rng.normal(size=n) * 2.0
+    for kw in (dict(), dict(absdelta=1e-8, miniter=2), dict(xtol=1e-9, maxiter=7), dict(energy_reduction_factor=None, absdelta=1e-6)):
+        r = nb.newton_cg(f_t, dev(x0), h_t, **kw)
+        ro = oopt.newton_cg(f_np, x0, h_np, **kw)
+        assert (r.nit, r.status, r.nfev, r.njev, r.nhev) == (ro.nit, ro.status, ro.nfev, ro.njev, ro.nhev), (kw, r[2:], ro[2:])
+        # inexact inner solves: the iterates agree to the rounding of the two stacks amplified by the CG
+        # (a run cut off mid-descent by maxiter is the least converged: 2e-7 in x)
+        assert rel(host(r.x), ro.x) <= 1e-5 and abs(r.fun - ro.fun) <= 1e-6 * abs(ro.fun), (kw, rel(host(r.x), ro.x), r.fun - ro.fun)
+
+
+def check_gaussian_model_and_geovi(shape, dist, seed=4):
+    """GaussianCFModel: energy against the oracle model, gradient by central differences of the oracle energy,
+    a MAP fit with newton_cg (energy decreases to a stationary point), the sample-averaged KL, and the geoVI
+    update (evi.py:201-266): its solution must zero the residual it minimises, and ``maxiter=0`` must skip."""
+    cf, co = make_pair(shape, dist, torch.float64, kw=GENTLE_KW)
+    rng = np.random.default_rng(seed)
+    truth = cf.init(seed)
+    sig = co(truth)
+    w = np.full(shape, 1.0 / 0.1 ** 2)
+    data = sig + 0.1 * rng.normal(size=shape)
+    model = nb.GaussianCFModel(cf, dev(data), dev(w))
+    lay = model.layout
+
+    def e_oracle(p):
+        r = data - co(p)
+        return 0.5 * float(np.sum(w * r * r)) + 0.5 * sum(float(np.sum(np.asarray(v) ** 2)) for v in p.values())
+    p0 = cf.init(seed + 1)
+    x = lay.flatten(p0)
+    e, g = model.energy_and_grad(x)
+    assert abs(e - e_oracle(p0)) <= 1e-11 * abs(e)
+    t = {k: rng.standard_normal(np.shape(v)) for k, v in p0.items()}
+    eps = 1e-6
+    fd = (e_oracle({k: p0[k] + eps * t[k] for k in p0}) - e_oracle({k: p0[k] - eps * t[k] for k in p0})) / (2 * eps)
+    an = float(torch.dot(g, lay.flatten(t)))
+    assert abs(fd - an) <= 1e-6 * max(abs(fd), abs(an)), (fd, an)
+    # MAP
+    res = nb.newton_cg(model.energy_and_grad, x, model.metric_at and (lambda pos, tt: model.metric_at(pos)(tt)), maxiter=15,
+                       absdelta=1e-3)
+    assert res.fun < e and res.status >= 0
+    e2, g2 = model.energy_and_grad(res.x)
+    assert abs(e2 - res.fun) <= 1e-10 * abs(e2)
+    # MGVI sample at the MAP point, its mirror, the KL value / gradient / metric over the pair
+    M = model.metric_at(res.x)
+    wd, wp = dev(rng.normal(size=shape)), dev(rng.normal(size=lay.size))
+    smpl, info = nb.draw_linear_residual(M, wd, wp, cg_kwargs=dict(resnorm=1e-8 * float(torch.linalg.vector_norm(M.sample_rhs(wd, wp))),
+                                                                 maxiter=10 * lay.size))
+    assert info == 0
+    samples = [smpl, -smpl]
+    ek, gk = model.kl_energy_and_grad(samples)(res.x)
+    ea, ga = model.energy_and_grad(res.x + smpl)
+    eb, gb = model.energy_and_grad(res.x - smpl)
+    assert abs(ek - 0.5 * (ea + eb)) <= 1e-12 * abs(ek) and rel(host(gk), host(0.5 * (ga + gb))) <= 1e-12
+    tt = dev(rng.normal(size=lay.size))
+    mk = model.kl_metric(samples).at(res.x)(tt)
+    assert rel(host(mk), host(0.5 * (model.metric_at(res.x + smpl)(tt) + model.metric_at(res.x - smpl)(tt)))) <= 1e-12
+    # geoVI update of the residual sample
+    same, st0 = nb.nonlinearly_update_residual(model, res.x, smpl, wd, wp, minimize_kwargs=dict(maxiter=0))
+    assert rel(host(same), host(smpl)) <= 1e-14 and st0.status == 0
+    from niftyb200 import evi
+    ms, _ = nb.draw_linear_residual(M, wd, wp, from_inverse=False)
+    f0, _ = evi._residual_vg(model, res.x, model.transformation(res.x), ms, res.x + smpl)
+    new, st = nb.nonlinearly_update_residual(model, res.x, smpl, wd, wp, minimize_kwargs=dict(xtol=1e-10, maxiter=25,
+                                                                                               cg_kwargs=dict(miniter=3)))
+    assert st.status >= 0 and st.fun <= 1e-6 * max(f0, 1e-30) + 1e-18, (f0, st.fun, st.status)
+    # the geoVI metric is symmetric
+    u, v = dev(rng.normal(size=lay.size)), dev(rng.normal(size=lay.size))
+    a_ = float(torch.dot(u, evi._geovi_metric(model, res.x, res.x + new, v)))
+    b_ = float(torch.dot(evi._geovi_metric(model, res.x, res.x + new, u), v))
+    assert abs(a_ - b_) <= 1e-9 * max(abs(a_), abs(b_))
+
+
 def check_cg_failure_modes():
     """Non-positive-definite operator: same error behaviour as the reference
     (re/conjugate_gradient.py:151-167,276-279; conjugate_gradient.py:86-96)."""

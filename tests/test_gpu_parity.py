@@ -142,6 +142,15 @@ def test_sampled_metric(shape, dist):
     pc.check_sampled_metric(shape, dist, np.float32, 4, "poisson" if len(shape) == 2 else "gaussian")
 
 
+def test_newton_cg_parity():
+    pc.check_newton_cg_parity()
+
+
+@pytest.mark.parametrize("shape,dist", [((16, 16), 1 / 16), ((64, 64), 1 / 64), ((16, 16, 16), 1 / 16)])
+def test_gaussian_model_and_geovi(shape, dist):
+    pc.check_gaussian_model_and_geovi(shape, dist)
+
+
 def test_cg_failure_modes():
     pc.check_cg_failure_modes()
 
