@@ -242,6 +242,20 @@ int nb2_amplitude_vjp(int64_t nb, const double* rel, const double* dt, const dou
                       const double* scratch, const double* amp, const double* ampbar, double* work, double* xibar,
                       double* scalars_bar, void* stream);
 
+/* ---- Line-of-sight response of the tomography configuration.  Replaces
+ * SamplingCartesianGridLOS.__call__ / _los (src/re/extra/sampling_los.py:15-91; multilinear interpolation of
+ * jax.scipy.ndimage.map_coordinates, order 1, constant mode, cval = NaN) and its linear transpose.
+ * shape / distances: HOST arrays of ndim (1..3) entries; start / end: DEVICE fp64 arrays (n_los, ndim), or (ndim)
+ * with the stride argument 0 (one point shared by every line); x / out / ybar / xbar in the precision `dtype`.
+ * forward: out[l] = |end_l - start_l| / n * sum_a interp(x, point_a).  adjoint: xbar += R^T ybar (zero xbar first;
+ * accumulated with atomics, so the summation order -- not the result to rounding -- varies between runs). */
+int nb2_los_forward(int dtype, int ndim, const int64_t* shape, const double* distances, int64_t n_los, int n_sampling,
+                    const double* start, int64_t start_stride, const double* end, int64_t end_stride, const void* x,
+                    void* out, void* stream);
+int nb2_los_adjoint(int dtype, int ndim, const int64_t* shape, const double* distances, int64_t n_los, int n_sampling,
+                    const double* start, int64_t start_stride, const double* end, int64_t end_stride, const void* ybar,
+                    void* xbar, void* stream);
+
 /* ---- Device-resident conjugate gradient (static_cg, src/re/conjugate_gradient.py:219-389: the reference keeps
  * the whole loop on the device inside lax.while_loop, :382).  The scalars of the recurrence live in a DEVICE
  * array `state` of NB2_CG_STATE_SIZE doubles (integers stored as doubles); the kernels of an iteration read

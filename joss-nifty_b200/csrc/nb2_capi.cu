@@ -7,6 +7,7 @@
 #include "nb2_amplitude.cuh"
 #include "nb2_c2c.cuh"
 #include "nb2_generic.cuh"
+#include "nb2_los.cuh"
 #include "nb2_plan.h"
 #include "nb2_passes.cuh"
 #include "nb2_vector.cuh"
@@ -908,6 +909,65 @@ int nb2_amplitude_vjp(int64_t nb, const double* rel, const double* dt, const dou
     AmplitudeVjp::Params p{{nb, rel, dt, mult, totvol}, {flu, slope, flx, asp, azm, power_kind}, xi, amp,
                            scratch + 2 * nb, ampbar, scratch + nb, work + nb, work, xibar, scalars_bar};
     return rt_launch<AmplitudeVjp>(1, kAmpThreads, AmplitudeVjp::smem_bytes(kAmpThreads), (rt_stream)stream, p);
+}
+
+static int los_geom(LosGeom& g, int ndim, const int64_t* shape, const double* distances, int64_t n_los, int n_sampling,
+                    const double* start, int64_t start_stride, const double* end, int64_t end_stride) {
+    if (ndim < 1 || ndim > kLosMaxDim || !shape || !distances || n_los < 0 || n_sampling < 1 || !start || !end ||
+        (start_stride != 0 && start_stride != ndim) || (end_stride != 0 && end_stride != ndim)) {
+        last_error() = "nb2_los: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    g.ndim = ndim;
+    for (int i = 0; i < ndim; ++i) {
+        if (shape[i] < 1 || !(distances[i] > 0.0)) {
+            last_error() = "nb2_los: invalid shape / distances";
+            return NB2_ERR_ARG;
+        }
+        g.shape[i] = shape[i];
+        g.l2i[i] = (double(shape[i] - 1) / double(shape[i])) / distances[i];
+    }
+    g.n_los = n_los;
+    g.n_sampling = n_sampling;
+    g.start = start;
+    g.end = end;
+    g.start_stride = start_stride;
+    g.end_stride = end_stride;
+    return NB2_OK;
+}
+
+int nb2_los_forward(int dtype, int ndim, const int64_t* shape, const double* distances, int64_t n_los, int n_sampling,
+                    const double* start, int64_t start_stride, const double* end, int64_t end_stride, const void* x,
+                    void* out, void* stream) {
+    LosGeom g{};
+    if (int rc = los_geom(g, ndim, shape, distances, n_los, n_sampling, start, start_stride, end, end_stride)) return rc;
+    if (!x || !out || (dtype != NB2_F32 && dtype != NB2_F64)) {
+        last_error() = "nb2_los_forward: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (dtype == NB2_F32) {
+        LosForward<float>::Params p{g, (const float*)x, (float*)out};
+        return rt_launch<LosForward<float>>(n_los, 128, LosForward<float>::smem_bytes(128), (rt_stream)stream, p);
+    }
+    LosForward<double>::Params p{g, (const double*)x, (double*)out};
+    return rt_launch<LosForward<double>>(n_los, 128, LosForward<double>::smem_bytes(128), (rt_stream)stream, p);
+}
+
+int nb2_los_adjoint(int dtype, int ndim, const int64_t* shape, const double* distances, int64_t n_los, int n_sampling,
+                    const double* start, int64_t start_stride, const double* end, int64_t end_stride, const void* ybar,
+                    void* xbar, void* stream) {
+    LosGeom g{};
+    if (int rc = los_geom(g, ndim, shape, distances, n_los, n_sampling, start, start_stride, end, end_stride)) return rc;
+    if (!ybar || !xbar || (dtype != NB2_F32 && dtype != NB2_F64)) {
+        last_error() = "nb2_los_adjoint: invalid argument";
+        return NB2_ERR_ARG;
+    }
+    if (dtype == NB2_F32) {
+        LosAdjoint<float>::Params p{g, (const float*)ybar, (float*)xbar};
+        return rt_launch<LosAdjoint<float>>(n_los, 128, 0, (rt_stream)stream, p);
+    }
+    LosAdjoint<double>::Params p{g, (const double*)ybar, (double*)xbar};
+    return rt_launch<LosAdjoint<double>>(n_los, 128, 0, (rt_stream)stream, p);
 }
 
 int nb2_set_launch_gate(const int* gate) {

@@ -18,6 +18,7 @@ from .cg import (ConjugateGradient, QuadraticEnergy, GradientNormController,  # 
 from .latent import LatentLayout, LatentMetric, draw_linear_residual  # noqa: F401
 from .optimize import newton_cg, OptimizeResults  # noqa: F401
 from .evi import GaussianCFModel, nonlinearly_update_residual  # noqa: F401
+from .los import SamplingCartesianGridLOS, LOSMetric  # noqa: F401
 from .distributed import SlabCorrelatedField, SlabHartley, SymmetricSplit  # noqa: F401
 from .operators import FFTOperator, HartleyOperator, HarmonicTransformOperator, RGSpace  # noqa: F401
 

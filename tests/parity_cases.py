@@ -876,6 +876,64 @@ def check_gaussian_model_and_geovi(shape, dist, seed=4):
     assert abs(a_ - b_) <= 1e-9 * max(abs(a_), abs(b_))
 
 
+def check_los(shape, dist, n_los=24, n_sampling=64, dt=np.float64, seed=8):
+    """SamplingCartesianGridLOS forward / adjoint against the oracle (restatement of sampling_los.py:15-91 incl.
+    jax's map_coordinates edge rule), adjointness, NaN for lines that leave the grid, shared start point; and the
+    tomography metric A H f' R^T N^-1 R f' H A + 1 against the oracle composition, with a CG solve on it."""
+    from oracle import los as olos
+    tdt = torch.float64 if dt == np.float64 else torch.float32
+    rng = np.random.default_rng(seed)
+    nd = len(shape)
+    ext = np.array(shape) * np.broadcast_to(np.asarray(dist, float), (nd,))
+    start = rng.uniform(0.05, 0.9, size=(n_los, nd)) * ext
+    end = rng.uniform(0.05, 0.9, size=(n_los, nd)) * ext
+    x = rng.normal(size=shape).astype(dt)
+    for st in (start, start[0]):                                  # per-line start points / one shared point (:84-90)
+        R = nb.SamplingCartesianGridLOS(st, end, shape=shape, distances=dist, n_sampling_points=n_sampling, dtype=tdt)
+        Ro = olos.SamplingCartesianGridLOS(st, end, shape=shape, distances=dist, n_sampling_points=n_sampling)
+        assert rel(host(R(dev(x))), Ro(x.astype(np.float64))) <= TOL[dt]
+        yb = rng.normal(size=n_los).astype(dt)
+        assert rel(host(R.adjoint(dev(yb))), Ro.adjoint(yb.astype(np.float64))) <= TOL[dt]
+        lhs = np.vdot(host(R(dev(x))).astype(np.float64), yb.astype(np.float64))
+        rhs = np.vdot(x.astype(np.float64), host(R.adjoint(dev(yb))).astype(np.float64))
+        assert abs(lhs - rhs) <= (1e-12 if dt == np.float64 else 1e-4) * max(abs(lhs), abs(rhs))
+    # a line that leaves the grid: NaN, exactly where the reference's rule gives NaN
+    bad_end = end.copy()
+    bad_end[0] = ext * 1.2
+    Rb = nb.SamplingCartesianGridLOS(start, bad_end, shape=shape, distances=dist, n_sampling_points=n_sampling, dtype=tdt)
+    Rbo = olos.SamplingCartesianGridLOS(start, bad_end, shape=shape, distances=dist, n_sampling_points=n_sampling)
+    got, ref = host(Rb(dev(x))), Rbo(x.astype(np.float64))
+    assert np.array_equal(np.isnan(got), np.isnan(ref)) and np.isnan(got[0]) and not np.isnan(got[1:]).any()
+    # tomography metric
+    cf, co = make_pair(shape, dist, tdt, kw=GENTLE_KW)
+    p = cf.init(seed)
+    amps_o, azm_o = co.normalized_amplitudes(p), co.azm(p)
+    tab = cf.tables_from_amplitudes(amps_o, float(azm_o))
+    fp = np.exp(0.2 * rng.normal(size=shape)).astype(dt)
+    ninv = rng.uniform(0.5, 2.0, size=n_los).astype(dt)
+    R = nb.SamplingCartesianGridLOS(start, end, shape=shape, distances=dist, n_sampling_points=n_sampling, dtype=tdt)
+    Ro = olos.SamplingCartesianGridLOS(start, end, shape=shape, distances=dist, n_sampling_points=n_sampling)
+    M = nb.LOSMetric(cf, tab, R, dev(fp), dev(ninv))
+    A = azm_o * co.outer_amplitude(amps_o)
+    f64, n64 = fp.astype(np.float64), ninv.astype(np.float64)
+
+    def Mo(t):
+        s = f64 * co.harmonic_transform(A * t)
+        z = f64 * Ro.adjoint(n64 * Ro(s))
+        return A * co.harmonic_transform(z) + t
+    t = rng.normal(size=shape).astype(dt)
+    q, curv = M.apply_with_curvature(dev(t))
+    ref = Mo(t.astype(np.float64))
+    assert rel(host(q), ref) <= TOL[dt], rel(host(q), ref)
+    c_ref = np.vdot(t.astype(np.float64), host(q).astype(np.float64))
+    assert abs(float(curv.cpu()) - c_ref) <= 1e-12 * abs(c_ref)
+    if dt == np.float64:
+        j = rng.normal(size=shape)
+        kw = dict(resnorm=1e-8 * float(np.linalg.norm(j)), maxiter=300)
+        r, ro = cgm._cg(M, dev(j), None, **kw), ocg.cg_re(Mo, j, None, **kw)
+        assert abs(r.nit - ro.nit) <= 1 and r.info == ro.info == 0 and rel(host(r.x), ro.x) <= 1e-6
+
+
 def check_cg_failure_modes():
     """Non-positive-definite operator: same error behaviour as the reference
     (re/conjugate_gradient.py:151-167,276-279; conjugate_gradient.py:86-96)."""

@@ -151,6 +151,12 @@ def test_gaussian_model_and_geovi(shape, dist):
     pc.check_gaussian_model_and_geovi(shape, dist)
 
 
+@pytest.mark.parametrize("shape,dist", [((16, 16, 16), 1 / 16), ((32, 16), (0.1, 0.3)), ((64,), 0.5), ((64, 64, 64), 1 / 64), ((128, 128, 128), 1 / 128)])
+def test_los_response_and_tomography_metric(shape, dist):
+    pc.check_los(shape, dist)
+    pc.check_los(shape, dist, n_los=7, n_sampling=33, dt=np.float32)
+
+
 def test_cg_failure_modes():
     pc.check_cg_failure_modes()
 
