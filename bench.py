@@ -510,17 +510,18 @@ def run_b200(args):
         emit(out)
     if rank == 0 and world == 1:
         # ---- per-kernel timing (CUDA events, same stream) and the roofline of the dominant kernel
-        plan = cf.plans[0]
+        plan = cf.plans[0] if getattr(cf, "joint", None) is None else cf.joint
+        pl_ = plan is not cf.plans[0]          # product of two spaces on one joint plan (NB2_HARTLEY_PRODUCT_LAST)
         t_fwd_g = tk(lambda: cf.apply_xi(a, tab, out=b)) if tab is not tabs else t_fwd
         t_adj_g = tk(lambda: cf.adjoint_xi(a, tab, out=b)) if tab is not tabs else t_adj
         names = {0: "StridedPass(axis0)", 1: "StridedPass(axis1)", 2: "RowPass(contiguous+Hartley combine)"}
         passes = {}
-        if plan.is_fast and cf.single:
+        if plan.is_fast and (cf.single or pl_):
             pro = PointOp(tab.amp_mode, tab.amp, tab.azm)
             for which in range(3):
                 if len(shape) - 3 + which < 0:
                     continue
-                passes[names[which]] = tk(lambda w=which: plan.run_pass(w, a, b))
+                passes[names[which]] = tk(lambda w=which: plan.run_pass(w, a, b, product_last=pl_))
             if len(shape) > 1:
                 pros = PointOp(tabs.amp_mode, tabs.amp, tabs.azm, amp_sym=tabs.sym)
                 passes["StridedPass(first axis)+amplitude field"] = tk(lambda: plan.run_pass(3 - len(shape), a, b, pro=pros))
@@ -530,10 +531,10 @@ def run_b200(args):
                     prod = PointOp(tabs.amp_mode, tabs.amp, tabs.azm, amp_sym=tabs.sym, pre_add=j, pre_scale=0.5, pre_out=a)
                     passes[FUSED] = tk(lambda: plan.run_pass(3 - len(shape), a, b, pro=prod))
             passes["RowPass+weight (metric fwd epilogue)"] = tk(lambda: plan.run_pass(
-                2, a, b, epi=PointOp(scale=cf.dvol, mul=M.w)))
+                2, a, b, epi=PointOp(scale=cf.dvol, mul=M.w), product_last=pl_))
             passes["RowPass+amplitude field+add+dot (metric adj epilogue)"] = tk(lambda: plan.run_pass(
                 2, a, b, epi=PointOp(tabs.amp_mode, tabs.amp, tabs.azm * cf.dvol, add=x0, dot=x0, dot_out=M._curv,
-                                     amp_sym=tabs.sym)))
+                                     amp_sym=tabs.sym), product_last=pl_))
         t_upd = tk(lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r))
         t_axp = tk(lambda: loop.vec.axpby(1.0, loop.r, 1.0, b))
         # the kernels that run inside one CG iteration (the gather variant is reported, not used there)

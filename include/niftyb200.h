@@ -31,6 +31,8 @@ extern "C" {
  * 1 = "canonical_hartley" (Re F - Im F). */
 #define NB2_HARTLEY_NONCANONICAL 0
 #define NB2_HARTLEY_CANONICAL 1
+/* flag OR-ed into the convention of nb2_hartley: product of (leading axes) x (last axis), see there */
+#define NB2_HARTLEY_PRODUCT_LAST 2
 
 #define NB2_OK 0
 #define NB2_ERR_ARG (-1)
@@ -119,7 +121,15 @@ int64_t nb2_plan_ksq_size(const nb2_plan* plan);
  * operators.  Replaces ducc_dispatch.hartley (src/ducc_dispatch.py:75-78,46-50) and, with
  * pro/epi, the correlated-field hot tail ht(azm*corr*xi)+offset
  * (src/library/correlated_fields.py:801-818, src/re/correlated_field.py:690-693) and its
- * adjoint.  `in` is not modified unless in == out (in-place is allowed). */
+ * adjoint.  `in` is not modified unless in == out (in-place is allowed).
+ *
+ * convention | NB2_HARTLEY_PRODUCT_LAST (fast-path plans): the transformed axes are a product of two
+ * spaces, (leading axes) x (last axis); the result is the 1-D Hartley transform over the last axis
+ * composed with the genuine Hartley transform over the leading axes -- what the reference computes with
+ * one HarmonicTransformOperator per sub-space (src/library/correlated_fields.py:790-793,
+ * src/re/correlated_field.py:671-679) -- out of the SAME three passes: with F the joint spectrum of the
+ * real input, H[k, k2] = Re F[k, -k2] + sgn Im F[k, k2], and both terms come from the two rows of a
+ * mirror pair.  amp_mode 1 and bin_x (|k|^2 of ONE isotropic space) are rejected with it. */
 int nb2_hartley(nb2_plan* plan, const void* in, void* out, int convention, const nb2_pointop* pro,
                 const nb2_pointop* epi, void* stream);
 

@@ -574,9 +574,20 @@ static int check_pre_update(const nb2_plan* pl, const nb2_pointop* pro, const nb
 
 int nb2_hartley(nb2_plan* pl, const void* in, void* out, int conv, const nb2_pointop* pro, const nb2_pointop* epi,
                 void* stream) {
-    if (!pl || !in || !out || (conv != 0 && conv != 1)) {
+    if (!pl || !in || !out || conv < 0 || conv > 3) {
         last_error() = "nb2_hartley: invalid argument";
         return NB2_ERR_ARG;
+    }
+    if (conv & NB2_PRODUCT_LAST) {
+        if (!pl->fast) {
+            last_error() = "nb2_hartley: NB2_HARTLEY_PRODUCT_LAST needs a fast-path plan (see nb2_plan_is_fast)";
+            return NB2_ERR_UNSUPPORTED;
+        }
+        if ((pro && pro->amp_mode == 1) || (epi && (epi->amp_mode == 1 || epi->bin_x))) {
+            last_error() = "nb2_hartley: |k|^2 tables and the binned reduction belong to one isotropic space, "
+                           "not to a product of spaces (use amp_mode 2)";
+            return NB2_ERR_ARG;
+        }
     }
     if (int rc = check_pre_update(pl, pro, epi, out, pl->g.logN0 > 0 || pl->g.logN1 > 0)) return rc;
     rt_stream st = (rt_stream)stream;
@@ -616,7 +627,7 @@ int nb2_expand_table(nb2_plan* pl, const void* table, double scale, void* out, v
 
 int nb2_hartley_pass(nb2_plan* pl, int which, const void* in, void* out, int conv, const nb2_pointop* pro,
                      const nb2_pointop* epi, void* stream) {
-    if (!pl || !in || !out || which < 0 || which > 2 || (conv != 0 && conv != 1)) {
+    if (!pl || !in || !out || which < 0 || which > 2 || conv < 0 || conv > 3) {
         last_error() = "nb2_hartley_pass: invalid argument";
         return NB2_ERR_ARG;
     }

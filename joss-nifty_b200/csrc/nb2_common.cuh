@@ -55,7 +55,7 @@ NB2_HD bool is_pow2(long long v) { return v > 0 && (v & (v - 1)) == 0; }
 
 // Hartley sign: +1 -> "non_canonical_hartley" (Re F + Im F, the reference default,
 // src/ducc_dispatch.py:46-50), -1 -> "canonical_hartley" (Re F - Im F).
-enum : int { NB2_NONCANONICAL = 0, NB2_CANONICAL = 1 };
+enum : int { NB2_NONCANONICAL = 0, NB2_CANONICAL = 1, NB2_PRODUCT_LAST = 2 };
 
 // ---------------------------------------------------------------- cache-hinted global access
 // Streaming data is touched exactly once per pass: keep it out of L1.

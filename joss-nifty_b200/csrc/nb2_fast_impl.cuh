@@ -194,7 +194,7 @@ int run_rows_part(nb2_plan* pl, const void* in, void* out, int conv, const nb2_p
     // compile-time epilogues for the three operand sets of the hot path (plain transform, metric forward
     // `* weight`, metric adjoint `* field + add, dot`) on rows of 512..2048 scalars
     int mask = -1;
-    if (logm >= 8 && logm <= 10) {
+    if (logm >= 8 && logm <= 10 && !(conv & NB2_PRODUCT_LAST)) {
         if (!epi) {
             mask = 0;
         } else if (!epi->bin_x && epi->amp_mode != 1 && (!epi->dot || epi->dot == epi->add)) {

@@ -353,7 +353,8 @@ struct RowPass {
         Geom g;
         long long ctas_per_item;
         int G;     // mirror pairs per CTA (2G rows)
-        int conv;  // NB2_NONCANONICAL / NB2_CANONICAL
+        int conv;  // NB2_NONCANONICAL / NB2_CANONICAL, | NB2_PRODUCT_LAST: Hartley over the last axis
+                   // composed with the genuine Hartley over the leading axes (a product of two spaces)
         int has_pro;
         PointOp<T> pro;
         PointOp<T> epi;
@@ -593,7 +594,11 @@ struct RowPass {
             // untangle + Hartley combine + epilogue
             double acc = 0.0;
             const long long itemrows = 1ll << (p.g.logN0 + p.g.logN1);
-            const T sgn = p.conv == NB2_CANONICAL ? T(-1) : T(1);
+            const T sgn = (p.conv & NB2_CANONICAL) ? T(-1) : T(1);
+            // Product of a leading-axes space with the last axis: with F the joint spectrum of the real
+            // field, H_last H_lead x [k, k2] = Re F[k, -k2] + sgn Im F[k, k2].  F[k, -k2] comes from the
+            // same two rows: index (M - j) of this row and index j of the mirror row.
+            const bool prod = EPI < 0 && (p.conv & NB2_PRODUCT_LAST);
             int prev_s = -1;
             RowSlot rs{};
             if (M >= 4) {
@@ -626,6 +631,10 @@ struct RowPass {
                     const cplx<T>* zb = smem + (s ^ 1) * PITCH;
                     const cplx<T>* zb0 = zb + slot_of_k((M - k) & (M - 1));
                     const cplx<T>* zb4 = zb + slot_of_k(M - k - 4);
+                    const cplx<T>* zr = smem + s * PITCH;
+                    const cplx<T>* za0p = zr + slot_of_k((M - k) & (M - 1));
+                    const cplx<T>* za4p = zr + slot_of_k(M - k - 4);
+                    const cplx<T>* zbk = zb + slot_of_k(k);
                     const vec4<T> w01 = ld4_ro(reinterpret_cast<const T*>(p.tw + k));
                     const vec4<T> w23 = ld4_ro(reinterpret_cast<const T*>(p.tw + k + 2));
                     vec4<T> h1, h2;
@@ -639,8 +648,17 @@ struct RowPass {
                         // with cas(z) = Re z + sgn Im z
                         const T Er = a.re + bz.re, Ei = a.im - bz.im;
                         const T Or = a.im + bz.im, Oi = bz.re - a.re;
-                        const T ce = Er + sgn * Ei;
-                        const T co = Or * (wr + sgn * wi) + Oi * (sgn * wr - wi);
+                        T ce = Er + sgn * Ei;
+                        T co = Or * (wr + sgn * wi) + Oi * (sgn * wr - wi);
+                        if (prod) {
+                            // a' = Z[(M - j) mod M] of this row, b' = Z'[j] of the mirror row; their twiddle
+                            // is W^(M - j) = -conj W^j (also right for j = 0, where the halves swap)
+                            const cplx<T> ap = i == 0 ? za0p[0] : za4p[(4 - i) * KS1];
+                            const cplx<T> bp = zbk[i * KS1];
+                            const T Epr = ap.re + bp.re, Opr = ap.im + bp.im, Opi = bp.re - ap.re;
+                            ce = Epr + sgn * Ei;
+                            co = wr * (Opr + sgn * Oi) + wi * (Opi + sgn * Or);
+                        }
                         h1.v[i] = ce + co;
                         h2.v[i] = ce - co;
                     }
@@ -664,7 +682,18 @@ struct RowPass {
                     const cplx<T> O = mul_mi(a - bb);      // 2 * odd-sample spectrum
                     const cplx<T> WO = ldc_ro(p.tw + k) * O;
                     const cplx<T> F1 = E + WO, F2 = E - WO;  // 2 F[k], 2 F[k + M]
-                    const T h1 = T(0.5) * (F1.re + sgn * F1.im), h2 = T(0.5) * (F2.re + sgn * F2.im);
+                    T h1 = T(0.5) * (F1.re + sgn * F1.im), h2 = T(0.5) * (F2.re + sgn * F2.im);
+                    if (prod) {
+                        const cplx<T> ap = smem[s * PITCH + slot_of_k((M - k) & (M - 1))];
+                        const cplx<T> bp = conj(smem[(s ^ 1) * PITCH + slot_of_k(k)]);
+                        const cplx<T> Ep = ap + bp, Op = mul_mi(ap - bp);
+                        const cplx<T> w = ldc_ro(p.tw + k);
+                        const cplx<T> wp = {-w.re, w.im};   // W^(M - k) = -conj W^k
+                        const cplx<T> WOp = wp * Op;
+                        // 2 F[M - k] = Ep + WOp and 2 F[2M - k] = Ep - WOp
+                        h1 = T(0.5) * ((Ep.re - WOp.re) + sgn * F1.im);
+                        h2 = T(0.5) * ((Ep.re + WOp.re) + sgn * F2.im);
+                    }
                     const long long idx = rs.row * (2 * M) + k;
                     const long long item = (rs.row & (itemrows - 1)) * (2 * M) + k;
                     const T o1 = apply_epi(p.epi, p.g, h1, rs.k0, rs.k1, k, item, idx, acc);
@@ -743,7 +772,7 @@ struct MirrorCombine {
             const RowPairs rp = row_pairs(p.g);
             const long long N0 = 1ll << p.g.logN0, N1 = 1ll << p.g.logN1, M = 1ll << p.g.logM;
             const long long total = p.g.batch * rp.Q * M, stride = p.nctas * nthreads;
-            const T sgn = p.conv == NB2_CANONICAL ? T(-1) : T(1);
+            const T sgn = (p.conv & NB2_CANONICAL) ? T(-1) : T(1);
             for (long long i = bid * nthreads + tid; i < total; i += stride) {
                 const long long m = i & (M - 1), pr = i >> p.g.logM;
                 const long long item = pr / rp.Q, q = pr - item * rp.Q;

@@ -355,6 +355,14 @@ class CorrelatedField:
         self.device = _device()
         self.plans = [Plan(self.shape, ax, dtype) for ax in self.axes]
         self.single = len(self.grids) == 1
+        # (space) x (1-D space), all powers of two: ONE joint fast-path plan whose row pass combines the
+        # two rows of a mirror pair into the product of the two Hartley transforms
+        # (NB2_HARTLEY_PRODUCT_LAST) -- 3 passes instead of one transform per sub-space
+        self.joint = None
+        if len(self.grids) == 2 and len(self.grids[1].shape) == 1 and len(self.shape) <= 3:
+            jp = Plan(self.shape, None, dtype)
+            if jp.is_fast:
+                self.joint = jp
         # joint harmonic volume factor prod_g 1/V_g (re/correlated_field.py:654,663-668)
         self.dvol = float(np.prod([1.0 / g.total_volume for g in self.grids]))
 
@@ -492,7 +500,7 @@ class CorrelatedField:
     def fuses_direction_update(self):
         """True when the first pass of :meth:`apply_xi` is a strided pass of the fast path, which can
         carry the CG direction update ``xi <- pre[0] + pre[1] * xi`` (``nb2_pointop.pre_add``)."""
-        pl = self.plans[0]
+        pl = self.plans[0] if self.joint is None else self.joint
         nax = sum(1 for a in pl.axes if self.shape[a] > 1)
         return (pl.kind == 1 and nax >= 2) or (pl.kind == 2 and nax >= 1)
 
@@ -515,6 +523,9 @@ class CorrelatedField:
         if self.single:
             return self.plans[0].hartley(xi, out=out, convention=convention, pro=pro,
                                          epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))
+        if self.joint is not None:
+            return self.joint.hartley(xi, out=out, convention=convention, pro=pro, product_last=True,
+                                      epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))
         cur = self.plans[0].hartley(xi, out=out, convention=convention, pro=pro)
         for pl in self.plans[1:-1]:
             cur = pl.hartley(cur, out=cur, convention=convention)
@@ -528,6 +539,8 @@ class CorrelatedField:
                       amp_sym=getattr(tab, "sym", False))
         if self.single:
             return self.plans[0].hartley(ybar, out=out, convention=convention, epi=epi)
+        if self.joint is not None:     # the sub-space transforms act on different axes: they commute
+            return self.joint.hartley(ybar, out=out, convention=convention, epi=epi, product_last=True)
         cur = self.plans[-1].hartley(ybar, out=out, convention=convention)
         for pl in reversed(self.plans[1:-1]):
             cur = pl.hartley(cur, out=cur, convention=convention)

@@ -144,17 +144,21 @@ class Plan:
                 pass
 
     # ---- device API ---------------------------------------------------------------
-    def hartley(self, x, out=None, convention=None, pro=None, epi=None):
+    def hartley(self, x, out=None, convention=None, pro=None, epi=None, product_last=False):
         """Genuine Hartley transform of the real tensor ``x`` (device), optional fused ops.
 
-        ``out`` may be ``x`` itself (in place).  Returns ``out``."""
+        ``out`` may be ``x`` itself (in place).  Returns ``out``.  ``product_last``: the transformed axes
+        are a product of two spaces, (leading axes) x (last axis) -- the result is the Hartley transform over
+        the last axis composed with the genuine one over the leading axes, i.e. two
+        ``HarmonicTransformOperator(..., space=i)`` in a row (correlated_fields.py:790-793), from the SAME
+        three passes (``NB2_HARTLEY_PRODUCT_LAST``, fast-path plans)."""
         if tuple(x.shape) != self.shape or x.dtype != self.dtype:
             raise ValueError(f"plan is for shape {self.shape} {self.dtype}, got {tuple(x.shape)} {x.dtype}")
         if out is None:
             out = torch.empty_like(x)
         elif tuple(out.shape) != self.shape or out.dtype != self.dtype:
             raise ValueError("output tensor does not match the plan")
-        conv = config.convention_code(convention)
+        conv = config.convention_code(convention) | (2 if product_last else 0)
         cpro = pro.to_c(self.lib) if pro is not None else None
         cepi = epi.to_c(self.lib) if epi is not None else None
         rc = self.lib.nb2_hartley(self._h, _ptr(self.lib, x, "x"), _ptr(self.lib, out, "out"), conv,
@@ -177,12 +181,12 @@ class Plan:
         self.lib.check(rc, "nb2_expand_table")
         return out
 
-    def run_pass(self, which, x, out, convention=None, pro=None, epi=None):
+    def run_pass(self, which, x, out, convention=None, pro=None, epi=None, product_last=False):
         """Profiling hook: one pass of the fast path (``nb2_hartley_pass``)."""
         cpro = pro.to_c(self.lib) if pro is not None else None
         cepi = epi.to_c(self.lib) if epi is not None else None
         rc = self.lib.nb2_hartley_pass(self._h, int(which), _ptr(self.lib, x, "x"), _ptr(self.lib, out, "out"),
-                                       config.convention_code(convention),
+                                       config.convention_code(convention) | (2 if product_last else 0),
                                        ctypes.byref(cpro) if cpro is not None else None,
                                        ctypes.byref(cepi) if cepi is not None else None, _stream(x))
         self.lib.check(rc, "nb2_hartley_pass")

@@ -85,6 +85,99 @@ def check_hartley_shapes(shapes, dtypes=(np.float64, np.float32), seed=42):
                 assert rel(got, ref) <= TOL[dt], (shape, axes, dt, c, rel(got, ref))
 
 
+def check_product_hartley(shapes, dtypes=(np.float64, np.float32), seed=23):
+    """``Plan.hartley(product_last=True)`` -- the joint three-pass transform of a (leading axes) x (last axis)
+    product of spaces -- against the oracle's one transform per sub-space (correlated_fields.py:790-793), both
+    conventions, plain and with the fused prologue / epilogue operands of the hot tail."""
+    from niftyb200.transforms import PointOp, Plan
+    rng = np.random.default_rng(seed)
+    for shape in shapes:
+        d = len(shape)
+        a64 = rng.normal(size=shape)
+        f64 = np.exp(0.3 * rng.normal(size=shape))
+        m64, add64 = rng.normal(size=shape), rng.normal(size=shape)
+        for dt in dtypes:
+            tdt = torch.float64 if dt == np.float64 else torch.float32
+            pl = Plan(shape, None, tdt)
+            assert pl.is_fast
+            a = a64.astype(dt)
+            for c in CONVS:
+                def ref_of(x):
+                    lead = otr.hartley(x, tuple(range(d - 1)), c) if d > 1 else x
+                    return otr.hartley(lead, (d - 1,), c)
+                got = host(pl.hartley(dev(a), convention=c, product_last=True))
+                ref = ref_of(a.astype(np.float64))
+                assert rel(got, ref) <= TOL[dt], (shape, dt, c, rel(got, ref))
+                # hot tail: field prologue, scale / offset / multiplier epilogue; adjoint: field + add + dot
+                f, m, ad = f64.astype(dt), m64.astype(dt), add64.astype(dt)
+                got = host(pl.hartley(dev(a), convention=c, product_last=True,
+                                      pro=PointOp(2, dev(f), 0.7, amp_sym=False),
+                                      epi=PointOp(scale=0.25, add_scalar=1.5, mul=dev(m))))
+                ref = 0.25 * ref_of(0.7 * f.astype(np.float64) * a.astype(np.float64)) * m.astype(np.float64) + 1.5
+                assert rel(got, ref) <= TOL[dt], (shape, dt, c, rel(got, ref))
+                dot_out = torch.zeros(1, dtype=torch.float64, device=dev(a).device)
+                got = host(pl.hartley(dev(a), convention=c, product_last=True,
+                                      epi=PointOp(2, dev(f), 0.5, add=dev(ad), dot=dev(ad), dot_out=dot_out)))
+                ref = 0.5 * f.astype(np.float64) * ref_of(a.astype(np.float64)) + ad.astype(np.float64)
+                assert rel(got, ref) <= TOL[dt], (shape, dt, c, rel(got, ref))
+                dref = float(np.vdot(ad.astype(np.float64), ref))
+                assert abs(float(dot_out[0]) - dref) <= 10 * TOL[dt] * max(abs(dref), np.linalg.norm(ref)), (shape, dt)
+                # the sub-space transforms commute, so the product transform is its own inverse up to N
+                back = host(pl.hartley(pl.hartley(dev(a), convention=c, product_last=True), convention=c,
+                                       product_last=True, epi=PointOp(scale=1.0 / a.size)))
+                assert rel(back, a) <= 4 * TOL[dt]
+            # |k|^2 tables belong to one isotropic space
+            with pytest.raises(RuntimeError):
+                pl.hartley(dev(a), product_last=True,
+                           epi=PointOp(1, torch.ones(pl.ksq_size, dtype=tdt, device=dev(a).device), 1.0))
+    gp = Plan((6, 10), None, torch.float64)
+    assert not gp.is_fast
+    with pytest.raises(RuntimeError):
+        gp.hartley(dev(rng.normal(size=(6, 10))), product_last=True)
+
+
+def check_product_cf(subs, dt=np.float64, seed=9):
+    """Correlated field on a product of two spaces whose joint grid is a power of two: the model runs on ONE
+    joint plan (``cf.joint``); forward, xi-adjoint, full VJP and the metric against the oracle."""
+    tdt = torch.float64 if dt == np.float64 else torch.float32
+    mk, mo = nb.CorrelatedFieldMaker("", dtype=tdt), ocf.CorrelatedFieldMaker("")
+    for m in (mk, mo):
+        m.set_amplitude_total_offset(0.5, (1e-2, 1e-3))
+        for i, (shape, dist) in enumerate(subs):
+            m.add_fluctuations(shape, dist, **NP_KW, prefix=f"ax{i}", non_parametric_kind="power")
+    cf, co = mk.finalize(), mo.finalize()
+    assert cf.joint is not None and cf.fuses_direction_update
+    shape = cf.shape
+    p = cf.init(seed)
+    p["xi"] = p["xi"].astype(dt)
+    tab = cf.tables(p)
+    amps_o, azm_o = co.normalized_amplitudes(p), co.azm(p)
+    rng = np.random.default_rng(seed + 1)
+    for conv in CONVS:
+        y = cf(p, convention=conv)
+        assert rel(y, co(p, conv)) <= TOL[dt], (shape, dt, conv, rel(y, co(p, conv)))
+        yb = rng.normal(size=shape).astype(dt)
+        xb = host(cf.adjoint_xi(dev(yb), tab, convention=conv))
+        ref = co.adjoint(amps_o, azm_o, yb.astype(np.float64), convention=conv)[0]
+        assert rel(xb, ref) <= TOL[dt], (shape, dt, conv, rel(xb, ref))
+    w = np.exp(0.3 * rng.normal(size=shape)).astype(dt)
+    M = nb.CFMetric(cf, tab, dev(w))
+    Mo = om.cf_metric_xi(co, amps_o, azm_o, w.astype(np.float64))
+    x = rng.normal(size=shape).astype(dt)
+    q, curv = M.apply_with_curvature(dev(x))
+    qo = Mo(x.astype(np.float64))
+    assert rel(host(q), qo) <= 4 * TOL[dt], (shape, dt, rel(host(q), qo))
+    co_ = float(np.vdot(x.astype(np.float64), qo))
+    assert abs(float(curv) - co_) <= 10 * TOL[dt] * abs(co_)
+    # fused direction update d <- r + beta d inside the first pass
+    r, d0 = rng.normal(size=shape).astype(dt), rng.normal(size=shape).astype(dt)
+    d = dev(d0.copy())
+    q2 = M.apply_with_curvature(d, pre=(dev(r), 0.37))[0]
+    dref = r.astype(np.float64) + 0.37 * d0.astype(np.float64)
+    assert rel(host(d), dref) <= TOL[dt]
+    assert rel(host(q2), Mo(dref)) <= 4 * TOL[dt]
+
+
 def check_c2c_shapes(shapes, dtypes=(np.complex128, np.complex64), seed=17, expect_fast=None):
     """``fftn`` / ``ifftn`` drop-ins (ducc_dispatch.py:66-72) against the oracle (scipy pocketfft): complex and
     real input, forward unnormalised, backward scaled 1/N over the transformed axes."""

@@ -223,3 +223,14 @@ def test_hartley_leading_axes_inner_batch():
         if ax is not None:
             assert nb.Plan(shp, ax, torch.float64).kind == 2, (shp, ax)
     pc.check_hartley_shapes([s for s in shapes if s[1] is not None])
+
+
+def test_product_hartley_joint_plan():
+    # (leading axes) x (last axis) product of spaces from ONE three-pass plan (NB2_HARTLEY_PRODUCT_LAST)
+    pc.check_product_hartley([(8, 16), (4, 8, 16), (16, 4, 4), (2, 2, 4), (8, 4), (4, 4, 64), (1, 4, 8), (32,),
+                              (2, 4, 512)])
+
+
+def test_product_correlated_field_joint_plan():
+    pc.check_product_cf([((8, 16), (1 / 8, 1 / 16)), ((8,), 0.7)])
+    pc.check_product_cf([((16,), 1 / 16), ((32,), 0.3)], np.float32)

@@ -313,7 +313,28 @@ def test_product_space_c5_properties(dt):
     ref = get_plan((2048, 2048), None, dt).hartley(x[:, :, 5].contiguous())
     assert float(torch.linalg.vector_norm((y[:, :, 5] - ref).double()) / torch.linalg.vector_norm(ref.double())) <= tol
     y = pf.hartley(y, out=y)
+    # the joint three-pass plan (NB2_HARTLEY_PRODUCT_LAST) == the two sub-space transforms in a row
+    yj = get_plan(shape, None, dt).hartley(x, product_last=True)
+    errj = float(torch.linalg.vector_norm((yj - y).double()) / torch.linalg.vector_norm(y.double()))
+    assert errj <= 2 * tol, errj
+    del yj
     y = pf.hartley(y, out=y, epi=PointOp(scale=1.0 / 128))
     y = ps.hartley(y, out=y, epi=PointOp(scale=1.0 / (2048 * 2048)))
     err = float(torch.linalg.vector_norm((y - x).double())) / nx
     assert err <= 4 * tol, err
+
+
+@pytest.mark.gpu
+def test_product_hartley_joint_plan():
+    # (leading axes) x (last axis) product of spaces from ONE three-pass plan, incl. the TMA strided passes
+    # (256..1024-point axes) and three-step rows
+    pc.check_product_hartley([(8, 16), (4, 8, 16), (16, 4, 4), (2, 2, 4), (8, 4), (4, 4, 64), (1, 4, 8), (32,),
+                              (2, 4, 512), (256, 256, 64), (512, 32, 128), (64, 2048, 16), (16, 8192)])
+
+
+@pytest.mark.gpu
+def test_product_correlated_field_joint_plan():
+    pc.check_product_cf([((8, 16), (1 / 8, 1 / 16)), ((8,), 0.7)])
+    pc.check_product_cf([((16,), 1 / 16), ((32,), 0.3)], np.float32)
+    pc.check_product_cf([((256, 256), (1 / 256, 1 / 256)), ((64,), 0.7)], np.float32)
+    pc.check_product_cf([((128, 64), (1 / 128, 1 / 64)), ((32,), 0.7)])
