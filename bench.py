@@ -303,13 +303,16 @@ def setup_problem(nb, torch, subs, offset, lik, tdt, seed=42, slab=False):
     return cf, tab, M, j, x0
 
 
-def verify_slab(nb, torch, dist, rank, world, shape=(256, 256, 256)):
-    """Pre-timing parity check of a multi-GPU run, OUTSIDE the timed region: a 256^3 fp64 metric apply
-    through the same SlabCorrelatedField / PeerExchange code path the timed loop uses, gathered and compared
-    on rank 0 with the CPU oracle (the checker: oracle.metric.cf_metric_xi).  Returns the rel-L2 error."""
+def verify_slab(nb, torch, dist, rank, world, vsubs=None, voffset=OFFSET):
+    """Pre-timing parity check of a multi-GPU run, OUTSIDE the timed region: a 256^3 (product spaces:
+    256 x 256 x 64) fp64 metric apply through the same SlabCorrelatedField / PeerExchange code path the timed
+    loop uses, gathered and compared on rank 0 with the CPU oracle (the checker: oracle.metric.cf_metric_xi).
+    Returns the rel-L2 error."""
     from niftyb200.transforms import device as nb_device
     dev = nb_device()
-    cf0 = make_field(nb, [(shape, CF_KW)], OFFSET, torch.float64)
+    vsubs = [((256, 256, 256), CF_KW)] if vsubs is None else vsubs
+    shape = tuple(n for sh, _ in vsubs for n in sh)
+    cf0 = make_field(nb, vsubs, voffset, torch.float64)
     cf = nb.SlabCorrelatedField(cf0)
     rng = np.random.default_rng(43)
     p = {k: rng.standard_normal(s) for k, s in cf0.domain.items() if not k.endswith("xi")}
@@ -321,8 +324,10 @@ def verify_slab(nb, torch, dist, rank, world, shape=(256, 256, 256)):
         from oracle import correlated_field as ocf, metric as om, transforms as otr
         otr.set_nthreads(max(1, (os.cpu_count() or 2) // 2))
         mk = ocf.CorrelatedFieldMaker("")
-        mk.set_amplitude_total_offset(*OFFSET)
-        mk.add_fluctuations(shape, 1.0 / shape[0], **CF_KW, non_parametric_kind="power")
+        mk.set_amplitude_total_offset(*voffset)
+        for i, (sh, kw) in enumerate(vsubs):
+            mk.add_fluctuations(sh, 1.0 / sh[0], **kw, prefix="" if len(vsubs) == 1 else f"ax{i}",
+                                non_parametric_kind="power")
         co = mk.finalize()
         amps, azm = co.normalized_amplitudes(p), co.azm(p)
         ref = om.cf_metric_xi(co, amps, azm, w)(t)
@@ -389,12 +394,15 @@ def run_b200(args):
 
     parity = None
     if world > 1:
-        if len(subs) != 1 or len(shape) != 3:
-            raise SystemExit("bench.py: --gpus > 1 shards one 3-D grid (c3, c4); c2 / c5 run on one GPU")
+        product = len(subs) == 2 and len(subs[0][0]) == 2 and len(subs[1][0]) == 1
+        if len(shape) != 3 or not (len(subs) == 1 or product):
+            raise SystemExit("bench.py: --gpus > 1 shards one 3-D grid (c3, c4, c5); c2 runs on one GPU")
         if not args.no_verify:
-            err = verify_slab(nb, torch, dist, rank, world)
+            vs = [((256, 256), subs[0][1]), ((64,), subs[1][1])] if product else None
+            err = verify_slab(nb, torch, dist, rank, world, vs, offset if product else OFFSET)
             parity = {"checked": True, "rel_l2": err, "ranks": world, "tolerance": 1e-12,
-                      "what": "256^3 fp64 metric apply (two consecutive, both exchange buffers) through the same slab / "
+                      "what": ("256x256 space x 64 frequency" if product else "256^3") +
+                              " fp64 metric apply (two consecutive, both exchange buffers) through the same slab / "
                               "peer-exchange code path, gathered, vs the CPU oracle, before the timed region"}
             if not err <= 1e-12:
                 if rank == 0:

@@ -220,9 +220,10 @@ class SlabHartley:
                 works[c].wait()
             after(c)
 
-    def x_to_y(self, x, out, convention=None, pro=None, epi=None):
-        """Hartley transform of ``x`` (layout X) into ``out`` (layout Y)."""
-        mc = self.mc
+    def x_to_y(self, x, out, convention=None, pro=None, epi=None, product_last=False):
+        """Hartley transform of ``x`` (layout X) into ``out`` (layout Y).  ``product_last``: (axes 0, 1) x
+        (axis 2) product of spaces (``Plan.hartley(product_last=True)``): only the row pass differs."""
+        mc, pl = self.mc, product_last
         if self.peer is not None:
             b = self.peer.turn
             self.peer.turn = (b + 1) % PeerExchange.NBUF
@@ -231,17 +232,17 @@ class SlabHartley:
             self.plan_x.run_strided_scatter(1, x, mine, pro, out_rowoff=self.p2p_x[b], out_outer_off=self.p2p_x_outer)
             self.peer.arrive()
             self.plan_y.run_pass(0, mine, out)
-            return self.plan_y.run_pass(2, out, out, convention, epi=epi)
+            return self.plan_y.run_pass(2, out, out, convention, epi=epi, product_last=pl)
         self._exchange(
             lambda c: self.plan_x.run_strided_remap(1, x, self.send[c], pro, out_rowoff=self.rowoff1,
                                                     out_ostride=self.ostride1, col0=c * mc, ncols=mc),
             lambda c: self.plan_y.run_strided_remap(0, self.recv[c], out, in_rowoff=self.rowoff0, col0=c * mc,
                                                     ncols=self.n1 * mc, run=mc, run_stride=self.m))
-        return self.plan_y.run_pass(2, out, out, convention, epi=epi)               # rows + Hartley combine
+        return self.plan_y.run_pass(2, out, out, convention, epi=epi, product_last=pl)   # rows + Hartley combine
 
-    def y_to_x(self, y, out, convention=None, pro=None, epi=None):
+    def y_to_x(self, y, out, convention=None, pro=None, epi=None, product_last=False):
         """Hartley transform of ``y`` (layout Y) into ``out`` (layout X)."""
-        mc = self.mc
+        mc, pl = self.mc, product_last
         if self.peer is not None:
             b = self.peer.turn
             self.peer.turn = (b + 1) % PeerExchange.NBUF
@@ -249,13 +250,13 @@ class SlabHartley:
             self.plan_y.run_strided_scatter(0, y, mine, pro, out_rowoff=self.p2p_y[b], out_col_off=self.p2p_y_col)
             self.peer.arrive()
             self.plan_x.run_pass(1, mine, out)
-            return self.plan_x.run_pass(2, out, out, convention, epi=epi)
+            return self.plan_x.run_pass(2, out, out, convention, epi=epi, product_last=pl)
         self._exchange(
             lambda c: self.plan_y.run_strided_remap(0, y, self.send[c], pro, out_rowoff=self.rowoff0, col0=c * mc,
                                                     ncols=self.n1 * mc, run=mc, run_stride=self.m),
             lambda c: self.plan_x.run_strided_remap(1, self.recv[c], out, in_rowoff=self.rowoff1,
                                                     in_ostride=self.ostride1, col0=c * mc, ncols=mc))
-        return self.plan_x.run_pass(2, out, out, convention, epi=epi)
+        return self.plan_x.run_pass(2, out, out, convention, epi=epi, product_last=pl)
 
     def close(self):
         """Unmap the peers' receive buffers and free this rank's (collective: every rank calls it, after a
@@ -299,7 +300,9 @@ class SlabTables:
 
 
 class SlabCorrelatedField:
-    """The hot tail of a single-space 3-D correlated field on a slab-decomposed grid.
+    """The hot tail of a 3-D correlated field on a slab-decomposed grid: one isotropic 3-D space, or the
+    product of a 2-D space with a 1-D space (``cf.joint``: the space x frequency fields of
+    correlated_field.py:663-688; the joint transform differs from the single-space one in the row pass only).
 
     Wraps a :class:`niftyb200.correlated_field.CorrelatedField` (which supplies the O(n_bins)
     amplitude chain and the geometry) and offers the same ``apply_xi`` / ``adjoint_xi`` /
@@ -307,8 +310,9 @@ class SlabCorrelatedField:
     work unchanged; latent vectors live in layout X, position-space fields in layout Y."""
 
     def __init__(self, cf, group=None):
-        if not cf.single or len(cf.shape) != 3 or not cf.grids[0].isotropic:
-            raise ValueError("slab decomposition: one isotropic 3-D sub-space")
+        self.product = getattr(cf, "joint", None) is not None and len(cf.shape) == 3 and len(cf.grids[0].shape) == 2
+        if not self.product and (not cf.single or len(cf.shape) != 3 or not cf.grids[0].isotropic):
+            raise ValueError("slab decomposition: one isotropic 3-D sub-space, or a power-of-two 2-D x 1-D product")
         self.cf, self.comm = cf, Comm(group)
         self.dtype, self.device, self.dvol, self.offset_mean = cf.dtype, cf.device, cf.dvol, cf.offset_mean
         self.ht = SlabHartley(cf.shape, cf.dtype, self.comm)
@@ -320,12 +324,25 @@ class SlabCorrelatedField:
         self.ht.close()
 
     def tables(self, p):
+        if self.product:       # only the O(n_bins) amplitude chain: the full outer product is never built
+            from types import SimpleNamespace
+            amps, azm, _ = self.cf._amplitudes(p)
+            return self.streaming_tables(SimpleNamespace(amps=[self.cf._as_dev(a) for a in amps], azm=float(azm)))
         return self.streaming_tables(self.cf.tables(p))
 
     def streaming_tables(self, tab):
         """Local part of ``azm * amp[pindex]`` from the ksq table (global coordinates)."""
         if isinstance(tab, SlabTables):
             return tab
+        if self.product:
+            # outer product of the two expanded spectra (correlated_field.py:681-688), own planes of axis 0
+            g0, g1 = self.cf.grids
+            e0 = g0.expand(tab.amps[0], torch.float64)[self.ht.own0[self.comm.rank]]     # (n0, N1)
+            e1 = g1.expand(tab.amps[1], torch.float64) * float(getattr(tab, "azm_value", tab.azm))
+            field = torch.empty(self.latent_shape, dtype=self.dtype, device=self.device)
+            for i in range(self.ht.n0):
+                field[i] = (e0[i][:, None] * e1[None, :]).to(self.dtype)
+            return SlabTables(field, tab.amps, float(getattr(tab, "azm_value", tab.azm)))
         grid = self.cf.grids[0]
         table = grid.ksq_table(tab.amps[0], torch.float64)
         N0, N1, N2 = self.shape
@@ -357,12 +374,12 @@ class SlabCorrelatedField:
                 pro.pre_scale_dev = pre[1]
             else:
                 pro.pre_scale = float(pre[1])
-        return self.ht.x_to_y(xi, out, convention, pro=pro,
+        return self.ht.x_to_y(xi, out, convention, pro=pro, product_last=self.product,
                               epi=PointOp(scale=self.dvol, add_scalar=off, mul=mul))
 
     def adjoint_xi(self, ybar, tab, out=None, convention=None, add=None, dot=None, dot_out=None):
         out = torch.empty(self.latent_shape, dtype=self.dtype, device=self.device) if out is None else out
-        res = self.ht.y_to_x(ybar, out, convention,
+        res = self.ht.y_to_x(ybar, out, convention, product_last=self.product,
                              epi=PointOp(2, tab.amp, self.dvol, add=add, dot=dot, dot_out=dot_out))
         if dot is not None:
             self.comm.allreduce_(dot_out)                 # CG curvature: a single fp64 scalar

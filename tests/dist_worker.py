@@ -16,7 +16,8 @@ for p in (ROOT, os.path.join(ROOT, "joss-nifty_b200"), os.path.join(ROOT, "tests
 
 def run(rank, world, port, backend, emu_path, shape, result, mode="full", dtype="f64"):
     """mode "full": forward, adjoint, metric, 5 back-to-back transforms and a CG solve against the oracle;
-    mode "large": the same without the CG solve (grids where the oracle CG would take minutes)."""
+    mode "large": the same without the CG solve (grids where the oracle CG would take minutes);
+    mode "product": as "large" for the (axes 0, 1) x (axis 2) product of two spaces on the joint plan."""
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     from niftyb200 import _lib
     if backend == "gloo":
@@ -34,13 +35,21 @@ def run(rank, world, port, backend, emu_path, shape, result, mode="full", dtype=
         if rank == 0:
             otr.set_nthreads(max(1, (os.cpu_count() or 1) // 2))
         dist_ = tuple(1.0 / s for s in shape)      # isotropic harmonic pixels
-        cf, co = pc.make_pair(shape, dist_, tdt, kw=pc.GENTLE_KW)
+        if mode == "product":
+            cf, co = pc.make_product_pair([(shape[:2], dist_[:2]), (shape[2:], 0.7)], tdt, kw=pc.GENTLE_KW)
+        else:
+            cf, co = pc.make_pair(shape, dist_, tdt, kw=pc.GENTLE_KW)
         scf = nb.SlabCorrelatedField(cf)
+        assert scf.product == (mode == "product")
         ht = scf.ht
         p = cf.init(5)
         p["xi"] = p["xi"].astype(dt)
         amps_o, azm_o = co.normalized_amplitudes(p), co.azm(p)
         tab = scf.streaming_tables(cf.tables_from_amplitudes(amps_o, float(azm_o)))
+        if mode == "product":      # the slab tables straight from the latent parameters (no full outer product)
+            t2 = scf.tables(p)
+            assert float(torch.linalg.vector_norm((t2.amp - tab.amp).double())
+                         / torch.linalg.vector_norm(tab.amp.double())) <= (1e-12 if dtype == "f64" else 1e-6)
 
         def f64(a):
             return np.asarray(a, dtype=np.float64)

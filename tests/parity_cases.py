@@ -136,16 +136,22 @@ def check_product_hartley(shapes, dtypes=(np.float64, np.float32), seed=23):
         gp.hartley(dev(rng.normal(size=(6, 10))), product_last=True)
 
 
-def check_product_cf(subs, dt=np.float64, seed=9):
-    """Correlated field on a product of two spaces whose joint grid is a power of two: the model runs on ONE
-    joint plan (``cf.joint``); forward, xi-adjoint, full VJP and the metric against the oracle."""
-    tdt = torch.float64 if dt == np.float64 else torch.float32
+def make_product_pair(subs, tdt, kw=None):
+    """(ours, oracle) correlated field on a product of sub-spaces ``[(shape, distances), ...]``."""
+    kw = NP_KW if kw is None else kw
     mk, mo = nb.CorrelatedFieldMaker("", dtype=tdt), ocf.CorrelatedFieldMaker("")
     for m in (mk, mo):
         m.set_amplitude_total_offset(0.5, (1e-2, 1e-3))
         for i, (shape, dist) in enumerate(subs):
-            m.add_fluctuations(shape, dist, **NP_KW, prefix=f"ax{i}", non_parametric_kind="power")
-    cf, co = mk.finalize(), mo.finalize()
+            m.add_fluctuations(shape, dist, **kw, prefix=f"ax{i}", non_parametric_kind="power")
+    return mk.finalize(), mo.finalize()
+
+
+def check_product_cf(subs, dt=np.float64, seed=9):
+    """Correlated field on a product of two spaces whose joint grid is a power of two: the model runs on ONE
+    joint plan (``cf.joint``); forward, xi-adjoint, full VJP and the metric against the oracle."""
+    tdt = torch.float64 if dt == np.float64 else torch.float32
+    cf, co = make_product_pair(subs, tdt)
     assert cf.joint is not None and cf.fuses_direction_update
     shape = cf.shape
     p = cf.init(seed)

@@ -70,3 +70,11 @@ def test_sampled_metric_samples_sharded_over_ranks():
     res = dist_worker.launch_sampled(2, conftest.build_emulator(), (16, 16))
     assert res["err"] <= 1e-13 and res["errc"] <= 1e-13, res
     assert res["nit"][0] == res["nit"][1] and res["errx"] <= 1e-10, res
+
+
+def test_slab_product_space_two_and_four_ranks_gloo():
+    # (2-D space) x (1-D space) on the joint plan, slab-decomposed: only the row pass differs
+    res = dist_worker.launch(2, "gloo", conftest.build_emulator(), (16, 8, 32), port=29549, mode="product")
+    check(res)
+    res = dist_worker.launch(4, "gloo", conftest.build_emulator(), (16, 16, 8), port=29551, mode="product", dtype="f32")
+    check(res)

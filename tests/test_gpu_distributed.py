@@ -40,3 +40,14 @@ def test_slab_nccl_all_to_all(monkeypatch):
     res = dist_worker.launch(world, "nccl", None, (64, 128, 64), port=29571)
     assert not res["p2p"]
     check(res, strict=False)
+
+
+@pytest.mark.parametrize("world,shape,dtype", [(2, (256, 128, 64), "f64"), (4, (512, 512, 32), "f32"), (8, (256, 256, 64), "f64")])
+def test_slab_product_space(world, shape, dtype):
+    """(2-D space) x (1-D frequency space) on the joint plan, slab-decomposed over the first space axis: the
+    BASELINE configs[4] kind of grid on several GPUs (forward / adjoint / metric / back-to-back transforms)."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    res = dist_worker.launch(world, "nccl", None, shape, port=29580 + world, mode="product", dtype=dtype)
+    assert res["p2p"] and res["world"] == world
+    check(res)
