@@ -67,9 +67,12 @@ def _verify_worker(rank, world, port, emu, result):
     try:
         import bench
         import niftyb200 as nb
-        err = bench.verify_slab(nb, torch, dist, rank, world, shape=(16, 16, 16))
+        err = bench.verify_slab(nb, torch, dist, rank, world, [((16, 16, 16), bench.CF_KW)])
+        # product of two spaces (the c5 kind of grid) through the joint plan
+        errp = bench.verify_slab(nb, torch, dist, rank, world, [((16, 8), bench.CF_KW_2D), ((16,), bench.CF_KW_FREQ)],
+                                 bench.OFFSET_2D)
         if rank == 0:
-            result["err"] = err
+            result["err"] = max(err, errp)
     finally:
         dist.destroy_process_group()
 
