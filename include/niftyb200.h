@@ -75,6 +75,16 @@ typedef struct nb2_pointop {
      * zero it first).  NULL = off. */
     const void* bin_x;
     double* bin_out;
+    /* Order-independent (bit-reproducible) variant of the binned reduction: if bin_fixed != NULL the
+     * contributions are accumulated as two-limb fixed-point integers with integer atomics (exact, hence
+     * independent of the order in which CTAs arrive) instead of the fp64 atomics of bin_out, which is then
+     * ignored.  Layout: int64 [2 + 2 * nbins], zeroed by the caller: entry 0 is set non-zero if a
+     * contribution was not finite or exceeded 2^62 / bin_fixed_scale (entry 1: unused); entry 2+2b / 3+2b =
+     * high / low limb of bin b, value = (hi + lo * 2^-40) / bin_fixed_scale.  bin_fixed_scale: a power of two with
+     * |bin_x[i] * transform[i] * scale| * bin_fixed_scale <= 2^42 for every i (e.g. from
+     * |transform[i]| <= sqrt(N) * ||in||_2), which leaves room for 2^20 contributions per bin. */
+    int64_t* bin_fixed;
+    double bin_fixed_scale;
     /* Fused direction update of the conjugate gradient (PROLOGUE of a fast-path transform whose first
      * pass is a strided pass, i.e. >= 2 transformed axes; NULL = off): before anything else
      *   in'[i] = pre_add[i] + pre_scale * in[i]        (d = r + beta d, conjugate_gradient.py:124,

@@ -591,7 +591,11 @@ int nb2_hartley(nb2_plan* pl, const void* in, void* out, int conv, const nb2_poi
     }
     if (int rc = check_pre_update(pl, pro, epi, out, pl->g.logN0 > 0 || pl->g.logN1 > 0)) return rc;
     rt_stream st = (rt_stream)stream;
-    if ((pro && pro->bin_x) || (epi && epi->bin_x && (!pl->fast || !epi->bin_out))) {
+    if (epi && epi->bin_x && epi->bin_fixed && !(epi->bin_fixed_scale > 0.0)) {
+        last_error() = "nb2_hartley: bin_fixed needs a positive power-of-two bin_fixed_scale";
+        return NB2_ERR_ARG;
+    }
+    if ((pro && pro->bin_x) || (epi && epi->bin_x && (!pl->fast || !(epi->bin_out || epi->bin_fixed)))) {
         last_error() = "nb2_hartley: the binned reduction (bin_x/bin_out) is an epilogue of fast-path plans";
         return NB2_ERR_UNSUPPORTED;
     }

@@ -417,12 +417,22 @@ struct RowPass {
         return (k & (R1 - 1)) * KS1 + ((k / R1) & (R2 - 1)) * (R3 + 1) + k / (R1 * R2);
     }
 
+    // one contribution to the spectrum cotangent: fp64 atomics, or the order-independent fixed-point bins
+    template <typename OP>
+    NB2_HD static void bin_add(const OP& e, long long bin, double v) {
+        if (e.bin_fixed) {
+            atomic_add_fixed(e.bin_fixed + 2, bin, e.bin_fixed, v, e.bin_fixed_scale);   // entry 0: the flag
+        } else {
+            atomic_add_f64(e.bin_out + bin, v);
+        }
+    }
+
     template <typename OP>
     NB2_HD static T apply_epi(const OP& e, const Geom& g, T h, long long k0, long long k1, long long k2,
                               long long item, long long idx, double& acc) {
         if (e.bin_x) {
             const long long ksq = sq_mirror(k0, g.logN0) + sq_mirror(k1, g.logN1) + sq_mirror(k2, g.logM + 1);
-            atomic_add_f64(e.bin_out + ksq, double(ld_stream(e.bin_x + idx)) * double(h * e.scale));
+            bin_add(e, ksq, double(ld_stream(e.bin_x + idx)) * double(h * e.scale));
         }
         T v = h * amp_factor(e, g, k0, k1, k2, item);
         if (e.mul) v *= ld_stream(e.mul + idx);
@@ -466,7 +476,7 @@ struct RowPass {
             T v = h.v[i] * e.scale;
             if (e.bin_x) {
                 const int km = down ? kq - i : kq + i;
-                atomic_add_f64(e.bin_out + f01 + km * km, double(L.bx.v[i]) * double(v));
+                bin_add(e, f01 + km * km, double(L.bx.v[i]) * double(v));
             }
             if (e.amp_mode != 0) v *= L.f.v[i];
             if (e.mul) v *= L.m.v[i];

@@ -79,6 +79,8 @@ PointOp<T> to_pointop(const nb2_pointop* o, double* partials) {
     r.dot_partials = partials;
     r.bin_x = o ? (const T*)o->bin_x : nullptr;
     r.bin_out = o ? o->bin_out : nullptr;
+    r.bin_fixed = o ? (long long*)o->bin_fixed : nullptr;
+    r.bin_fixed_scale = o ? o->bin_fixed_scale : 0.0;
     r.pre_add = o ? (const T*)o->pre_add : nullptr;
     r.pre_scale = o ? (T)o->pre_scale : T(0);
     r.pre_out = o ? (T*)o->pre_out : nullptr;

@@ -34,6 +34,9 @@ struct PointOp {
     // in the ksq parametrisation of the bins; fp64 atomics
     const T* bin_x;
     double* bin_out;
+    // bit-reproducible variant: two-limb fixed-point integers, integer atomics (see niftyb200.h)
+    long long* bin_fixed;
+    double bin_fixed_scale;
     // prologue of a strided pass only: in' = pre_add + pre_scale * in, stored to pre_out if set
     const T* pre_add;
     T pre_scale;
@@ -50,6 +53,30 @@ NB2_HD void atomic_add_f64(double* p, double v) {
     atomicAdd(p, v);
 #else
     *p += v;
+#endif
+}
+
+// bins[2b] += hi, bins[2b + 1] += lo with v * S = hi + lo * 2^-40: integer additions commute exactly, so the
+// result does not depend on the order of the atomics.  `flag`: set when v * S is not representable.
+NB2_HD void atomic_add_fixed(long long* bins, long long b, long long* flag, double v, double S) {
+    const double q = v * S;                       // exact: S is a power of two
+    if (!(q > -4.6e18 && q < 4.6e18)) {           // also catches NaN
+#if defined(__CUDA_ARCH__)
+        atomicExch(reinterpret_cast<unsigned long long*>(flag), 1ull);
+#else
+        *flag = 1;
+#endif
+        return;
+    }
+    const double hi = rint(q);
+    const long long ihi = (long long)hi;
+    const long long ilo = (long long)rint((q - hi) * 1099511627776.0);   // 2^40; q - hi is exact
+#if defined(__CUDA_ARCH__)
+    atomicAdd(reinterpret_cast<unsigned long long*>(bins + 2 * b), (unsigned long long)ihi);
+    if (ilo) atomicAdd(reinterpret_cast<unsigned long long*>(bins + 2 * b + 1), (unsigned long long)ilo);
+#else
+    bins[2 * b] += ihi;
+    bins[2 * b + 1] += ilo;
 #endif
 }
 

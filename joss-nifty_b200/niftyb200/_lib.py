@@ -36,6 +36,8 @@ class PointOp(ctypes.Structure):
         ("dot_out", c_void_p),
         ("bin_x", c_void_p),
         ("bin_out", c_void_p),
+        ("bin_fixed", c_void_p),
+        ("bin_fixed_scale", c_double),
         ("pre_add", c_void_p),
         ("pre_scale", c_double),
         ("pre_out", c_void_p),

@@ -558,10 +558,22 @@ class CorrelatedField:
         amps = tab.amps
         if self.single and self.grids[0].isotropic and self.plans[0].is_fast:
             g = self.grids[0]
-            bins = torch.zeros(self.plans[0].ksq_size, dtype=torch.float64, device=self.device)
-            epi = PointOp(tab.amp_mode, tab.amp, tab.azm * self.dvol, bin_x=xi, bin_out=bins,
+            # Order-independent accumulation (two-limb fixed point, integer atomics: nb2_pointop.bin_fixed) --
+            # the cotangent of the spectrum is bit-reproducible from run to run.  Scale from the rigorous bound
+            # |H(y)_i| <= sqrt(N) ||y||_2 on every transform value.
+            nbins = self.plans[0].ksq_size
+            scale = float(tab.azm) * self.dvol
+            bound = 2.0 * (float(torch.linalg.vector_norm(xi, ord=float("inf"))) * math.sqrt(ybar.numel())
+                           * float(torch.linalg.vector_norm(ybar)) * abs(scale))
+            fscale = 2.0 ** (42 - math.ceil(math.log2(bound))) if 0.0 < bound < float("inf") else 1.0
+            fixed = torch.zeros(2 + 2 * nbins, dtype=torch.int64, device=self.device)
+            epi = PointOp(tab.amp_mode, tab.amp, scale, bin_x=xi, bin_fixed=fixed, bin_fixed_scale=fscale,
                           amp_sym=getattr(tab, "sym", False))
             xibar = self.plans[0].hartley(ybar, convention=convention, epi=epi)
+            limbs = fixed[2:].view(nbins, 2).to(torch.float64)
+            bins = (limbs[:, 0] + limbs[:, 1] * 2.0 ** -40) / fscale
+            if int(fixed[0]) != 0 or not bound < float("inf"):     # non-finite input
+                bins = torch.full_like(bins, float("nan"))
             # bins[ksq] = sum_i xi_i * (azm' * h_i) over the points of that ksq, azm' = tab.azm
             per_bin = bins[g.unique_ksq.to(self.device)]
             true_azm = float(tab.azm) if tab.amp_mode == 1 else float(getattr(tab, "azm_value", tab.azm))

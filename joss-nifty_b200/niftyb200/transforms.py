@@ -81,12 +81,14 @@ class PointOp:
 
     def __init__(self, amp_mode=0, amp=None, scale=1.0, mul=None, add=None, add_scalar=0.0,
                  dot=None, dot_out=None, bin_x=None, bin_out=None, amp_sym=False, pre_add=None, pre_scale=0.0,
-                 pre_out=None, pre_scale_dev=None):
+                 pre_out=None, pre_scale_dev=None, bin_fixed=None, bin_fixed_scale=0.0):
         self.amp_mode, self.amp, self.scale = int(amp_mode), amp, float(scale)
         self.amp_sym = bool(amp_sym)      # NB2_AMP_SYMMETRIC: amp_mode-2 field with field[k] == field[-k]
         self.mul, self.add, self.add_scalar = mul, add, float(add_scalar)
         self.dot, self.dot_out = dot, dot_out
         self.bin_x, self.bin_out = bin_x, bin_out
+        # bit-reproducible bins: int64 [2 + 2 * nbins] (flag, pad, limbs) two-limb fixed point (nb2_pointop.bin_fixed)
+        self.bin_fixed, self.bin_fixed_scale = bin_fixed, float(bin_fixed_scale)
         # prologue only: in' = pre_add + pre_scale * in (stored to pre_out), the fused CG direction update
         self.pre_add, self.pre_scale, self.pre_out = pre_add, float(pre_scale), pre_out
         self.pre_scale_dev = pre_scale_dev     # 1-element fp64 device tensor: pre_scale read on the device
@@ -104,6 +106,8 @@ class PointOp:
         c.dot_out = _ptr(lib, self.dot_out, "dot_out")
         c.bin_x = _ptr(lib, self.bin_x, "bin_x")
         c.bin_out = _ptr(lib, self.bin_out, "bin_out")
+        c.bin_fixed = _ptr(lib, self.bin_fixed, "bin_fixed")
+        c.bin_fixed_scale = self.bin_fixed_scale
         c.pre_add = _ptr(lib, self.pre_add, "pre_add")
         c.pre_scale = self.pre_scale
         c.pre_out = _ptr(lib, self.pre_out, "pre_out")

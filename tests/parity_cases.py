@@ -184,6 +184,36 @@ def check_product_cf(subs, dt=np.float64, seed=9):
     assert rel(host(q2), Mo(dref)) <= 4 * TOL[dt]
 
 
+def check_vjp_reproducible(shape, dist, dt=np.float64, seed=31):
+    """The spectrum cotangent (binned reduction in the row-pass epilogue, distributors.py:105-112) is accumulated
+    in two-limb fixed point with integer atomics: bit-identical from run to run, equal (to rounding) to the fp64
+    atomics of ``bin_out``, and a non-finite input poisons the bins instead of being dropped."""
+    tdt = torch.float64 if dt == np.float64 else torch.float32
+    cf, co = make_pair(shape, dist, tdt)
+    p = cf.init(seed)
+    tab = cf.tables(p)
+    assert tab.amp_mode == 1 and cf.plans[0].is_fast
+    rng = np.random.default_rng(seed)
+    xi, yb = dev(rng.normal(size=shape).astype(dt)), dev(rng.normal(size=shape).astype(dt))
+    runs = [cf.vjp(yb, tab, xi) for _ in range(3)]
+    for r in runs[1:]:
+        assert torch.equal(r[1][0], runs[0][1][0]) and r[2] == runs[0][2]
+    bins = torch.zeros(cf.plans[0].ksq_size, dtype=torch.float64, device=xi.device)
+    cf.plans[0].hartley(yb, epi=PointOp(tab.amp_mode, tab.amp, tab.azm * cf.dvol, bin_x=xi, bin_out=bins))
+    ref = host(bins[cf.grids[0].unique_ksq.to(bins.device)])
+    assert rel(host(runs[0][1][0]), ref) <= (1e-13 if dt == np.float64 else 1e-6)
+    # tiny and huge magnitudes: the scale follows the data
+    for fac in (1e-30, 1e30) if dt == np.float64 else (1e-12, 1e12):
+        a = cf.vjp(yb * fac, tab, xi)[1][0]
+        assert rel(host(a) / fac, ref) <= (1e-13 if dt == np.float64 else 1e-6), fac
+    bad = yb.clone()
+    bad.view(-1)[3] = float("nan")
+    assert bool(torch.isnan(cf.vjp(bad, tab, xi)[1][0]).all())
+    with pytest.raises(RuntimeError):
+        cf.plans[0].hartley(yb, epi=PointOp(bin_x=xi, bin_fixed=torch.zeros(2 * cf.plans[0].ksq_size + 2, dtype=torch.int64,
+                                                                             device=xi.device)))
+
+
 def check_c2c_shapes(shapes, dtypes=(np.complex128, np.complex64), seed=17, expect_fast=None):
     """``fftn`` / ``ifftn`` drop-ins (ducc_dispatch.py:66-72) against the oracle (scipy pocketfft): complex and
     real input, forward unnormalised, backward scaled 1/N over the transformed axes."""

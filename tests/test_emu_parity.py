@@ -234,3 +234,8 @@ def test_product_hartley_joint_plan():
 def test_product_correlated_field_joint_plan():
     pc.check_product_cf([((8, 16), (1 / 8, 1 / 16)), ((8,), 0.7)])
     pc.check_product_cf([((16,), 1 / 16), ((32,), 0.3)], np.float32)
+
+
+def test_spectrum_cotangent_is_order_independent():
+    pc.check_vjp_reproducible((16, 32), (1 / 16, 1 / 32))
+    pc.check_vjp_reproducible((8, 8, 16), (1 / 8, 1 / 8, 1 / 16), np.float32)

@@ -338,3 +338,10 @@ def test_product_correlated_field_joint_plan():
     pc.check_product_cf([((16,), 1 / 16), ((32,), 0.3)], np.float32)
     pc.check_product_cf([((256, 256), (1 / 256, 1 / 256)), ((64,), 0.7)], np.float32)
     pc.check_product_cf([((128, 64), (1 / 128, 1 / 64)), ((32,), 0.7)])
+
+
+def test_spectrum_cotangent_is_order_independent():
+    # thousands of CTAs race on the same bins: the fixed-point accumulation makes the result bit-reproducible
+    pc.check_vjp_reproducible((512, 512), (1 / 512, 1 / 512))
+    pc.check_vjp_reproducible((128, 128, 128), (1 / 128,) * 3, np.float32)
+    pc.check_vjp_reproducible((16, 32), (1 / 16, 1 / 32))
