@@ -383,7 +383,6 @@ int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* ax
         if ((e = std::getenv("NB2_TMA"))) pl->knob_tma = e[0] != '0';
         if ((e = std::getenv("NB2_TMA_SCATTER"))) pl->knob_tma_scatter = e[0] == '1';
         if ((e = std::getenv("NB2_TMA_FX"))) pl->knob_tma_fx = e[0] != '0';
-        if ((e = std::getenv("NB2_CLUSTER"))) pl->knob_cluster = e[0] != '0';
     }
     for (int i = 0; i < ndim; ++i) {
         if (shape[i] < 1) {

@@ -50,11 +50,6 @@ template <typename T>
 int run_strided_tma(const nb2_plan* pl, int axis, int logn, long long inner, long long outer, const void* in, void* out,
                     const nb2_pointop* pro, rt_stream st, bool* done, const RowRemap* rm = nullptr);
 
-// Cluster variant for 2048- and 4096-point axes (nb2_cluster.cuh); nb2_fast_cluster_impl.cuh / _f32.cu / _f64.cu
-template <typename T>
-int run_strided_cluster(const nb2_plan* pl, int axis, int logn, long long inner, long long outer, const void* in,
-                        void* out, const nb2_pointop* pro, rt_stream st, bool* done);
-
 template <typename T>
 int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const nb2_pointop* pro, rt_stream st,
                 const RowRemap* rm) {
@@ -63,12 +58,6 @@ int run_strided(const nb2_plan* pl, int axis, const void* in, void* out, const n
         return NB2_ERR_ARG;
     }
     const long long inner = axis == 0 ? (1ll << (pl->g.logN1 + pl->g.logM)) : (1ll << pl->g.logM);
-    if (!rm && logn >= 11) {
-        bool done = false;
-        const int rc = run_strided_cluster<T>(pl, axis, logn, inner, axis == 0 ? pl->g.batch : (pl->g.batch << pl->g.logN0),
-                                              in, out, pro, st, &done);
-        if (rc || done) return rc;
-    }
     // natural input, all columns: the TMA kernel (its stores may be scattered through the out tables)
     if (!rm || (!rm->in_rowoff && !rm->ncols && !rm->col0)) {
         bool done = false;

@@ -37,7 +37,7 @@ struct nb2_plan {
     double* partials = nullptr;
     long long npartials = 0;
     // developer knobs, read from the environment once at plan creation (never on the dispatch path)
-    bool knob_tma = true, knob_tma_scatter = false, knob_tma_fx = true, knob_cluster = true;
+    bool knob_tma = true, knob_tma_scatter = false, knob_tma_fx = true;
     // generic path
     void* roots[nb2::kMaxDim] = {nullptr};  // cplx<double>[n] per transformed axis
     void* work0 = nullptr;
