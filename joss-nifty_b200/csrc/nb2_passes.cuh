@@ -27,6 +27,9 @@
 #ifndef NB2_MINB256_F32
 #define NB2_MINB256_F32 1   // radix-32 kernels: compiled for up to 512 threads -> <= 128 registers
 #endif
+#ifndef NB2_MINB_SHORT_F32
+#define NB2_MINB_SHORT_F32 3   // row pass, generic epilogue, CTAs of <= 256 threads: x 3 -> <= 85 registers
+#endif
 #ifndef NB2_MINB512_F32
 #define NB2_MINB512_F32 2   // radix <= 16 kernels, 512 threads: <= 64 registers
 #endif
@@ -342,9 +345,20 @@ struct RowPass {
     static constexpr int PITCH = slot_pitch<R1, R2, R3>();
     static constexpr int NPHASES = 7;
     static constexpr bool BIG = (R1 >= 32 || R3 >= 32);
-    static constexpr int MAX_THREADS = (BIG && sizeof(T) == 8) ? 256 : 512;
-    static constexpr int MIN_BLOCKS = sizeof(T) == 4 ? (BIG ? NB2_MINB256_F32 : NB2_MINB512_F32)
-                                                     : (MAX_THREADS == 256 ? NB2_MINB256_F64 : NB2_MINB512_F64);
+    // radix <= 16 plans whose CTAs never have more than 256 threads (2 G R2 R3: rows of up to 512 and of 4096
+    // scalars) are compiled for that: the generic epilogue keeps its state in registers (at 512 x 2 it spilled
+    // 10 % of its instructions through the LSU pipe that bounds these kernels)
+    static constexpr int gmax_of(size_t row_bytes) {     // == choose_G (nb2_fast_impl.cuh) without the row-count cap
+        int g = 1;
+        while (g < 16 && size_t(4 * g) * row_bytes <= 36 * 1024) g *= 2;
+        return g;
+    }
+    static constexpr int THREADS_NEEDED = 2 * gmax_of(size_t(PITCH) * sizeof(cplx<T>)) * R2 * R3;
+    static constexpr bool SHORT = (!BIG && EPI < 0 && THREADS_NEEDED <= 256);
+    static constexpr int MAX_THREADS = SHORT ? 256 : ((BIG && sizeof(T) == 8) ? 256 : 512);
+    static constexpr int MIN_BLOCKS = SHORT ? (sizeof(T) == 4 ? NB2_MINB_SHORT_F32 : 1)
+                                     : sizeof(T) == 4 ? (BIG ? NB2_MINB256_F32 : NB2_MINB512_F32)
+                                                      : (MAX_THREADS == 256 ? NB2_MINB256_F64 : NB2_MINB512_F64);
 
     struct Params {
         const cplx<T>* in;
