@@ -30,6 +30,9 @@
 #ifndef NB2_MINB_SHORT_F32
 #define NB2_MINB_SHORT_F32 3   // row pass, generic epilogue, CTAs of <= 256 threads: x 3 -> <= 85 registers
 #endif
+#ifndef NB2_MINB_SHORT_F64
+#define NB2_MINB_SHORT_F64 2   // <= 128 registers
+#endif
 #ifndef NB2_MINB512_F32
 #define NB2_MINB512_F32 2   // radix <= 16 kernels, 512 threads: <= 64 registers
 #endif
@@ -356,7 +359,7 @@ struct RowPass {
     static constexpr int THREADS_NEEDED = 2 * gmax_of(size_t(PITCH) * sizeof(cplx<T>)) * R2 * R3;
     static constexpr bool SHORT = (!BIG && EPI < 0 && THREADS_NEEDED <= 256);
     static constexpr int MAX_THREADS = SHORT ? 256 : ((BIG && sizeof(T) == 8) ? 256 : 512);
-    static constexpr int MIN_BLOCKS = SHORT ? (sizeof(T) == 4 ? NB2_MINB_SHORT_F32 : 1)
+    static constexpr int MIN_BLOCKS = SHORT ? (sizeof(T) == 4 ? NB2_MINB_SHORT_F32 : NB2_MINB_SHORT_F64)
                                      : sizeof(T) == 4 ? (BIG ? NB2_MINB256_F32 : NB2_MINB512_F32)
                                                       : (MAX_THREADS == 256 ? NB2_MINB256_F64 : NB2_MINB512_F64);
 

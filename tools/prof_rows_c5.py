@@ -14,12 +14,13 @@ def tk(fn, reps=5):
     return e0.elapsed_time(e1) / reps
 
 shape = tuple(int(v) for v in (sys.argv[1] if len(sys.argv) > 1 else "2048,2048,128").split(","))
-a = torch.randn(shape, dtype=torch.float32, device="cuda"); b = torch.empty_like(a)
-f = torch.rand(shape, dtype=torch.float32, device="cuda") + 0.5
-w = torch.rand(shape, dtype=torch.float32, device="cuda") + 0.5
+DT = torch.float64 if (len(sys.argv) > 2 and sys.argv[2] == "f64") else torch.float32
+a = torch.randn(shape, dtype=DT, device="cuda"); b = torch.empty_like(a)
+f = torch.rand(shape, dtype=DT, device="cuda") + 0.5
+w = torch.rand(shape, dtype=DT, device="cuda") + 0.5
 curv = torch.zeros((), dtype=torch.float64, device="cuda")
 pl = Plan(shape, None, torch.float32)
-byt = 2 * a.numel() * 4
+byt = 2 * a.numel() * a.element_size()
 for prod in (False, True):
     for name, epi in (("plain", None), ("+weight", PointOp(scale=0.5, mul=w)),
                       ("+field+add+dot", PointOp(2, f, 0.5, add=w, dot=w, dot_out=curv, amp_sym=True))):
