@@ -2,6 +2,7 @@
 //
 // Built with nvcc for sm_100a into libniftyb200.so.  With -DNB2_EMU (host compiler) the
 // same file builds the sequential thread emulator used by the CPU-only index tests.
+#include <complex>
 #include <mutex>
 
 #include "nb2_amplitude.cuh"
@@ -180,11 +181,115 @@ int ensure_work(nb2_plan* pl) {
     return 0;
 }
 
+// Bluestein applies from this length on (below it the direct sum is as fast and exact to the last bit) and up
+// to the longest padded line the contiguous-axis kernel takes (L = 8192, i.e. n <= 4096)
+constexpr long long kBlueMinN = 32, kBlueMaxLogL = 13;
+
+inline int blue_logl(long long n) {
+    int l = 1;
+    while ((1ll << l) < 2 * n - 1) ++l;
+    return l;
+}
+
+// in-place radix-2 transform of a power-of-two host vector (plan creation only)
+inline void host_fft(std::vector<std::complex<long double>>& a) {
+    const size_t n = a.size();
+    for (size_t i = 1, j = 0; i < n; ++i) {
+        size_t bit = n >> 1;
+        for (; j & bit; bit >>= 1) j ^= bit;
+        j ^= bit;
+        if (i < j) std::swap(a[i], a[j]);
+    }
+    const long double pi = 3.141592653589793238462643383279502884L;
+    for (size_t len = 2; len <= n; len <<= 1) {
+        for (size_t i = 0; i < n; i += len)
+            for (size_t k = 0; k < len / 2; ++k) {
+                const long double ang = -2 * pi * (long double)k / (long double)len;
+                const std::complex<long double> w(cosl(ang), sinl(ang));
+                const std::complex<long double> u = a[i + k], v = a[i + k + len / 2] * w;
+                a[i + k] = u + v;
+                a[i + k + len / 2] = u - v;
+            }
+    }
+}
+
+// chirp, filter spectrum and roots of axis t (first use); the shared line buffer grows to the largest need
+template <typename T>
+int blue_prepare(nb2_plan* pl, int t, long long n, long long nlines, rt_stream st) {
+    const int logL = blue_logl(n);
+    const long long L = 1ll << logL;
+    if (!pl->blue_w[t]) {
+        const long double pi = 3.141592653589793238462643383279502884L;
+        std::vector<std::complex<long double>> w(n), bt(L, std::complex<long double>(0, 0));
+        for (long long j = 0; j < n; ++j) {
+            const long long q = (j * j) % (2 * n);          // exact phase reduction: j^2 mod 2n
+            const long double ang = -pi * (long double)q / (long double)n;
+            w[j] = std::complex<long double>(cosl(ang), sinl(ang));
+        }
+        for (long long m = 0; m < n; ++m) {
+            bt[m] = std::conj(w[m]);
+            if (m) bt[L - m] = std::conj(w[m]);
+        }
+        host_fft(bt);
+        std::vector<cplx<T>> hw(n), hB(L);
+        for (long long j = 0; j < n; ++j) hw[j] = mk<T>((T)w[j].real(), (T)w[j].imag());
+        for (long long m = 0; m < L; ++m) hB[m] = mk<T>((T)bt[m].real(), (T)bt[m].imag());
+        if (rt_malloc(&pl->blue_w[t], n * sizeof(cplx<T>)) || rt_malloc(&pl->blue_B[t], L * sizeof(cplx<T>)))
+            return NB2_ERR_CUDA;
+        if (rt_h2d(pl->blue_w[t], hw.data(), n * sizeof(cplx<T>), nullptr) ||
+            rt_h2d(pl->blue_B[t], hB.data(), L * sizeof(cplx<T>), nullptr))
+            return NB2_ERR_CUDA;
+        if (upload_table<T>(&pl->blue_tw[t], L, L)) return NB2_ERR_CUDA;
+        pl->blue_logL[t] = logL;
+    }
+    if (nlines * L > pl->blue_buf_elems) {
+        rt_sync(st);
+        rt_free(pl->blue_buf);
+        pl->blue_buf = nullptr;
+        pl->blue_buf_elems = 0;
+        if (rt_malloc(&pl->blue_buf, nlines * L * sizeof(cplx<T>))) return NB2_ERR_CUDA;
+        pl->blue_buf_elems = nlines * L;
+    }
+    return 0;
+}
+
+template <typename T>
+int blue_axis(nb2_plan* pl, int t, const cplx<T>* in, cplx<T>* out, long long outer, long long n, long long inner,
+              int forward, rt_stream st) {
+    const long long nlines = outer * inner;
+    int rc = blue_prepare<T>(pl, t, n, nlines, st);
+    if (rc) return rc;
+    const int logL = pl->blue_logL[t];
+    const long long L = 1ll << logL;
+    cplx<T>* buf = (cplx<T>*)pl->blue_buf;
+    const long long gridL = vec_grid(nlines * L), gridN = vec_grid(nlines * n);
+    typename BlueGather<T>::Params gp{in, buf, (const cplx<T>*)pl->blue_w[t], outer, n, inner, L, forward, gridL};
+    if ((rc = rt_launch<BlueGather<T>>(gridL, kVecThreads, 0, st, gp))) return rc;
+    if ((rc = run_rows_c2c<T>(buf, buf, pl->blue_tw[t], logL, nlines, 0, 0, 1.0, st))) return rc;
+    typename BlueMulConj<T>::Params mp{buf, (const cplx<T>*)pl->blue_B[t], nlines, L, forward, gridL};
+    if ((rc = rt_launch<BlueMulConj<T>>(gridL, kVecThreads, 0, st, mp))) return rc;
+    if ((rc = run_rows_c2c<T>(buf, buf, pl->blue_tw[t], logL, nlines, 0, 0, 1.0, st))) return rc;
+    typename BlueScatter<T>::Params sp{buf, out, (const cplx<T>*)pl->blue_w[t], outer, n, inner, L, forward, gridN};
+    return rt_launch<BlueScatter<T>>(gridN, kVecThreads, 0, st, sp);
+}
+
 // transform work buffer `a` over all plan axes; result pointer returned in *res (a or b)
 template <typename T>
 int generic_axes(nb2_plan* pl, cplx<T>* a, cplx<T>* b, int forward, rt_stream st, cplx<T>** res) {
     for (int t = 0; t < pl->naxes; ++t) {
         const int ax = pl->axes[t];
+        {
+            const long long n = pl->shape[ax];
+            if (n >= kBlueMinN && blue_logl(n) <= kBlueMaxLogL && pl->knob_bluestein) {
+                long long outer = 1, inner = 1;
+                for (int i = 0; i < ax; ++i) outer *= pl->shape[i];
+                for (int i = ax + 1; i < pl->ndim; ++i) inner *= pl->shape[i];
+                const int rc = blue_axis<T>(pl, t, a, b, outer, n, inner, forward, st);
+                if (rc) return rc;
+                std::swap(a, b);
+                continue;
+            }
+        }
         typename NaiveDft<T>::Params p;
         p.in = a;
         p.out = b;
@@ -383,6 +488,7 @@ int nb2_plan_create(int ndim, const int64_t* shape, int naxes, const int32_t* ax
         if ((e = std::getenv("NB2_TMA"))) pl->knob_tma = e[0] != '0';
         if ((e = std::getenv("NB2_TMA_SCATTER"))) pl->knob_tma_scatter = e[0] == '1';
         if ((e = std::getenv("NB2_TMA_FX"))) pl->knob_tma_fx = e[0] != '0';
+        if ((e = std::getenv("NB2_BLUESTEIN"))) pl->knob_bluestein = e[0] != '0';
     }
     for (int i = 0; i < ndim; ++i) {
         if (shape[i] < 1) {
@@ -527,7 +633,13 @@ int nb2_plan_destroy(nb2_plan* pl) {
     rt_free(pl->partials);
     rt_free(pl->work0);
     rt_free(pl->work1);
-    for (int t = 0; t < kMaxDim; ++t) rt_free(pl->roots[t]);
+    for (int t = 0; t < kMaxDim; ++t) {
+        rt_free(pl->roots[t]);
+        rt_free(pl->blue_w[t]);
+        rt_free(pl->blue_B[t]);
+        rt_free(pl->blue_tw[t]);
+    }
+    rt_free(pl->blue_buf);
     delete pl;
     return NB2_OK;
 }

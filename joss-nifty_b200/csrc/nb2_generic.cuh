@@ -115,4 +115,99 @@ struct CplxScale {
     }
 };
 
+// ---------------------------------------------------------------- Bluestein (chirp-z) for one axis of any length n
+// X[k] = w[k] * sum_j (x[j] w[j]) conj(w[k - j]),  w[j] = exp(-+ i pi j^2 / n): a circular convolution of length
+// L = 2^ceil(log2(2n - 1)) done with the power-of-two contiguous-axis kernel (RowC2C): O(n log n) per line instead
+// of the O(n^2) direct sum.  Lines are gathered into a padded contiguous buffer and scattered back.
+
+// buf[line, j] = in[o, j, i] * w[j] (j < n), 0 (n <= j < L); line = o * inner + i
+template <typename T>
+struct BlueGather {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
+    struct Params {
+        const cplx<T>* in;
+        cplx<T>* buf;
+        const cplx<T>* w;      // forward chirp exp(-i pi j^2 / n)
+        long long outer, n, inner, L;
+        int forward;
+        long long nctas;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+        const long long total = p.outer * p.inner * p.L, stride = p.nctas * nthreads;
+        for (long long e = bid * nthreads + tid; e < total; e += stride) {
+            const long long j = e % p.L, line = e / p.L, i = line % p.inner, o = line / p.inner;
+            cplx<T> v = mk<T>(T(0), T(0));
+            if (j < p.n) {
+                cplx<T> w = p.w[j];
+                if (!p.forward) w.im = -w.im;
+                v = p.in[(o * p.n + j) * p.inner + i] * w;
+            }
+            p.buf[e] = v;
+        }
+    }
+};
+
+// buf[line, m] = conj(buf[line, m] * B[m])   (B of the other direction is conj(B): the filter is symmetric);
+// the conjugate turns the following FORWARD transform into the inverse one
+template <typename T>
+struct BlueMulConj {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
+    struct Params {
+        cplx<T>* buf;
+        const cplx<T>* B;
+        long long nlines, L;
+        int forward;
+        long long nctas;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+        const long long total = p.nlines * p.L, stride = p.nctas * nthreads;
+        for (long long e = bid * nthreads + tid; e < total; e += stride) {
+            cplx<T> b = p.B[e % p.L];
+            if (!p.forward) b.im = -b.im;
+            const cplx<T> v = p.buf[e] * b;
+            p.buf[e] = mk<T>(v.re, -v.im);
+        }
+    }
+};
+
+// out[o, k, i] = w[k] * conj(buf[line, k]) / L
+template <typename T>
+struct BlueScatter {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
+    struct Params {
+        const cplx<T>* buf;
+        cplx<T>* out;
+        const cplx<T>* w;
+        long long outer, n, inner, L;
+        int forward;
+        long long nctas;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char*) {
+        const long long total = p.outer * p.n * p.inner, stride = p.nctas * nthreads;
+        const T s = T(1) / T(p.L);
+        for (long long e = bid * nthreads + tid; e < total; e += stride) {
+            const long long i = e % p.inner, k = (e / p.inner) % p.n, o = e / (p.inner * p.n);
+            cplx<T> w = p.w[k];
+            if (!p.forward) w.im = -w.im;
+            const cplx<T> y = p.buf[(o * p.inner + i) * p.L + k];
+            p.out[e] = (w * mk<T>(y.re, -y.im)) * s;
+        }
+    }
+};
+
 }  // namespace nb2

@@ -37,11 +37,19 @@ struct nb2_plan {
     double* partials = nullptr;
     long long npartials = 0;
     // developer knobs, read from the environment once at plan creation (never on the dispatch path)
-    bool knob_tma = true, knob_tma_scatter = false, knob_tma_fx = true;
+    bool knob_tma = true, knob_tma_scatter = false, knob_tma_fx = true, knob_bluestein = true;
     // generic path
     void* roots[nb2::kMaxDim] = {nullptr};  // cplx<double>[n] per transformed axis
     void* work0 = nullptr;
     void* work1 = nullptr;  // complex scratch
+    // Bluestein (chirp-z) tables of the generic path, per transformed axis, built on first use: chirp w[n], filter
+    // spectrum B[L], roots of the length-L contiguous transform; one padded line buffer shared by the axes
+    void* blue_w[nb2::kMaxDim] = {nullptr};
+    void* blue_B[nb2::kMaxDim] = {nullptr};
+    void* blue_tw[nb2::kMaxDim] = {nullptr};
+    int blue_logL[nb2::kMaxDim] = {0};
+    void* blue_buf = nullptr;
+    long long blue_buf_elems = 0;
 };
 
 

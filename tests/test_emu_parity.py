@@ -239,3 +239,11 @@ def test_product_correlated_field_joint_plan():
 def test_spectrum_cotangent_is_order_independent():
     pc.check_vjp_reproducible((16, 32), (1 / 16, 1 / 32))
     pc.check_vjp_reproducible((8, 8, 16), (1 / 8, 1 / 8, 1 / 16), np.float32)
+
+
+def test_non_power_of_two_axes_bluestein():
+    # generic path: axes of 32..4096 points go through the chirp-z convolution on the power-of-two row kernel,
+    # shorter and longer ones through the direct sum
+    pc.check_hartley_shapes([((100,), None), ((33,), None), ((96, 40), None), ((50, 36, 10), None), ((3, 48), (1,)),
+                             ((45, 6), (0,)), ((1000,), None), ((4097,), None), ((4000,), None)])
+    pc.check_c2c_shapes([((100,), None), ((12, 90), None), ((35, 8), (0,)), ((63, 65), None)], expect_fast=False)

@@ -345,3 +345,11 @@ def test_spectrum_cotangent_is_order_independent():
     pc.check_vjp_reproducible((512, 512), (1 / 512, 1 / 512))
     pc.check_vjp_reproducible((128, 128, 128), (1 / 128,) * 3, np.float32)
     pc.check_vjp_reproducible((16, 32), (1 / 16, 1 / 32))
+
+
+def test_non_power_of_two_axes_bluestein():
+    pc.check_hartley_shapes([((100,), None), ((33,), None), ((96, 40), None), ((50, 36, 10), None), ((3, 48), (1,)),
+                             ((45, 6), (0,)), ((1000, 1000), None), ((4097,), None), ((4000, 3), None), ((384, 96, 100), None)])
+    pc.check_c2c_shapes([((100,), None), ((12, 90), None), ((35, 8), (0,)), ((63, 65), None), ((1000, 300), None)],
+                        expect_fast=False)
+    pc.check_cf_vs_oracle((96, 100), (1 / 96, 1 / 100), np.float64, None)
