@@ -206,6 +206,28 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------- CPU arm: the reference's algorithm on host cores
+def tune_blas_threads(cores):
+    """The CPU arm should be as fast as this host allows: the FFTs use every core (scipy workers); for the level-1
+    BLAS behind np.vdot the fastest of {all cores, 1 thread} is taken -- on some containers a multi-threaded ddot
+    is 100x slower than a single-threaded one (threads spinning against the FFT pool).  Returns the count used."""
+    try:
+        from threadpoolctl import threadpool_limits
+    except Exception:
+        return None
+    a = np.ones(1 << 24)
+    best, best_t = cores, None
+    for n in (cores, 1):
+        threadpool_limits(limits=n)
+        np.vdot(a, a)
+        t0 = time.perf_counter()
+        np.vdot(a, a)
+        t = time.perf_counter() - t0
+        if best_t is None or t < best_t:
+            best, best_t = n, t
+    threadpool_limits(limits=best)
+    return best
+
+
 def cpu_cg_iters_per_s(subs, offset, lik, dtype, iters=1):
     """Oracle (NumPy/SciPy restatement of the reference, oracle/) CG iterations on the host cores: the
     reference's fallback path, scipy pocketfft with workers = all cores.  `iters` CG iterations from x0 = 0
@@ -214,11 +236,7 @@ def cpu_cg_iters_per_s(subs, offset, lik, dtype, iters=1):
     from oracle import correlated_field as ocf, metric as om, cg as ocg, transforms as otr
     cores = os.cpu_count() or 1
     otr.set_nthreads(cores)
-    try:
-        from threadpoolctl import threadpool_limits
-        threadpool_limits(limits=cores)
-    except Exception:
-        pass
+    tune_blas_threads(cores)
     dt = np.float32 if dtype == "f32" else np.float64
     mk = ocf.CorrelatedFieldMaker("")
     mk.set_amplitude_total_offset(*offset)
