@@ -253,9 +253,40 @@ int blue_prepare(nb2_plan* pl, int t, long long n, long long nlines, rt_stream s
     return 0;
 }
 
+// power-of-two axis of a generic plan (more than three axes, leading axes, ...): gather the lines, ONE pass of the
+// contiguous-axis kernel (backward = conj-in / conj-out), scatter back
+template <typename T>
+int pow2_axis(nb2_plan* pl, int t, const cplx<T>* in, cplx<T>* out, long long outer, long long n, long long inner,
+              int forward, rt_stream st) {
+    const long long nlines = outer * inner;
+    int logn = 0;
+    while ((1ll << logn) < n) ++logn;
+    if (!pl->blue_tw[t]) {
+        if (upload_table<T>(&pl->blue_tw[t], n, n)) return NB2_ERR_CUDA;
+        pl->blue_logL[t] = logn;
+    }
+    if (nlines * n > pl->blue_buf_elems) {
+        rt_sync(st);
+        rt_free(pl->blue_buf);
+        pl->blue_buf = nullptr;
+        pl->blue_buf_elems = 0;
+        if (rt_malloc(&pl->blue_buf, nlines * n * sizeof(cplx<T>))) return NB2_ERR_CUDA;
+        pl->blue_buf_elems = nlines * n;
+    }
+    cplx<T>* buf = (cplx<T>*)pl->blue_buf;
+    const long long grid = vec_grid(nlines * n);
+    int rc;
+    typename BlueGather<T>::Params gp{in, buf, nullptr, outer, n, inner, n, forward, grid};
+    if ((rc = rt_launch<BlueGather<T>>(grid, kVecThreads, 0, st, gp))) return rc;
+    if ((rc = run_rows_c2c<T>(buf, buf, pl->blue_tw[t], logn, nlines, forward ? 0 : 1, forward ? 0 : 1, 1.0, st))) return rc;
+    typename BlueScatter<T>::Params sp{buf, out, nullptr, outer, n, inner, n, forward, grid};
+    return rt_launch<BlueScatter<T>>(grid, kVecThreads, 0, st, sp);
+}
+
 template <typename T>
 int blue_axis(nb2_plan* pl, int t, const cplx<T>* in, cplx<T>* out, long long outer, long long n, long long inner,
               int forward, rt_stream st) {
+    if ((n & (n - 1)) == 0) return pow2_axis<T>(pl, t, in, out, outer, n, inner, forward, st);
     const long long nlines = outer * inner;
     int rc = blue_prepare<T>(pl, t, n, nlines, st);
     if (rc) return rc;
@@ -280,7 +311,8 @@ int generic_axes(nb2_plan* pl, cplx<T>* a, cplx<T>* b, int forward, rt_stream st
         const int ax = pl->axes[t];
         {
             const long long n = pl->shape[ax];
-            if (n >= kBlueMinN && blue_logl(n) <= kBlueMaxLogL && pl->knob_bluestein) {
+            const bool pow2 = (n & (n - 1)) == 0 && n <= (1ll << kBlueMaxLogL);
+            if (n >= kBlueMinN && (pow2 || blue_logl(n) <= kBlueMaxLogL) && pl->knob_bluestein) {
                 long long outer = 1, inner = 1;
                 for (int i = 0; i < ax; ++i) outer *= pl->shape[i];
                 for (int i = ax + 1; i < pl->ndim; ++i) inner *= pl->shape[i];

@@ -143,9 +143,12 @@ struct BlueGather {
             const long long j = e % p.L, line = e / p.L, i = line % p.inner, o = line / p.inner;
             cplx<T> v = mk<T>(T(0), T(0));
             if (j < p.n) {
-                cplx<T> w = p.w[j];
-                if (!p.forward) w.im = -w.im;
-                v = p.in[(o * p.n + j) * p.inner + i] * w;
+                v = p.in[(o * p.n + j) * p.inner + i];
+                if (p.w) {                         // nullptr: power-of-two axis, plain gather (L == n)
+                    cplx<T> w = p.w[j];
+                    if (!p.forward) w.im = -w.im;
+                    v = v * w;
+                }
             }
             p.buf[e] = v;
         }
@@ -202,9 +205,13 @@ struct BlueScatter {
         const T s = T(1) / T(p.L);
         for (long long e = bid * nthreads + tid; e < total; e += stride) {
             const long long i = e % p.inner, k = (e / p.inner) % p.n, o = e / (p.inner * p.n);
+            const cplx<T> y = p.buf[(o * p.inner + i) * p.L + k];
+            if (!p.w) {                            // power-of-two axis: the row kernel's result as it is
+                p.out[e] = y;
+                continue;
+            }
             cplx<T> w = p.w[k];
             if (!p.forward) w.im = -w.im;
-            const cplx<T> y = p.buf[(o * p.inner + i) * p.L + k];
             p.out[e] = (w * mk<T>(y.re, -y.im)) * s;
         }
     }

@@ -247,3 +247,7 @@ def test_non_power_of_two_axes_bluestein():
     pc.check_hartley_shapes([((100,), None), ((33,), None), ((96, 40), None), ((50, 36, 10), None), ((3, 48), (1,)),
                              ((45, 6), (0,)), ((1000,), None), ((4097,), None), ((4000,), None)])
     pc.check_c2c_shapes([((100,), None), ((12, 90), None), ((35, 8), (0,)), ((63, 65), None)], expect_fast=False)
+    # power-of-two axes of generic plans (4-D grids, leading axes): one pass of the row kernel per axis
+    pc.check_hartley_shapes([((32, 6), None), ((4, 4, 32, 64), None), ((64, 3), (0,)), ((100, 64), None),
+                             ((2, 2, 2, 2, 32), None)])
+    pc.check_c2c_shapes([((64, 3), (0,)), ((4, 4, 32, 64), None), ((128, 5), None)], expect_fast=False)

@@ -353,3 +353,5 @@ def test_non_power_of_two_axes_bluestein():
     pc.check_c2c_shapes([((100,), None), ((12, 90), None), ((35, 8), (0,)), ((63, 65), None), ((1000, 300), None)],
                         expect_fast=False)
     pc.check_cf_vs_oracle((96, 100), (1 / 96, 1 / 100), np.float64, None)
+    pc.check_hartley_shapes([((32, 6), None), ((16, 16, 32, 64), None), ((64, 3), (0,)), ((8192, 3), (0,)), ((100, 64), None)])
+    pc.check_c2c_shapes([((64, 3), (0,)), ((4, 4, 32, 64), None), ((128, 5), None)], expect_fast=False)
