@@ -253,6 +253,20 @@ int blue_prepare(nb2_plan* pl, int t, long long n, long long nlines, rt_stream s
     return 0;
 }
 
+// gather / scatter of the lines of one axis: through shared-memory tiles when the lines are strided (inner > 1)
+template <typename T>
+int blue_gather(const typename BlueGather<T>::Params& gp, rt_stream st) {
+    if (gp.inner >= 8)
+        return rt_launch<BlueGatherTiled<T>>(BlueGatherTiled<T>::grid(gp), 256, BlueGatherTiled<T>::smem_bytes(256), st, gp);
+    return rt_launch<BlueGather<T>>(gp.nctas, kVecThreads, 0, st, gp);
+}
+template <typename T>
+int blue_scatter(const typename BlueScatter<T>::Params& sp, rt_stream st) {
+    if (sp.inner >= 8)
+        return rt_launch<BlueScatterTiled<T>>(BlueScatterTiled<T>::grid(sp), 256, BlueScatterTiled<T>::smem_bytes(256), st, sp);
+    return rt_launch<BlueScatter<T>>(sp.nctas, kVecThreads, 0, st, sp);
+}
+
 // power-of-two axis of a generic plan (more than three axes, leading axes, ...): gather the lines, ONE pass of the
 // contiguous-axis kernel (backward = conj-in / conj-out), scatter back
 template <typename T>
@@ -277,10 +291,10 @@ int pow2_axis(nb2_plan* pl, int t, const cplx<T>* in, cplx<T>* out, long long ou
     const long long grid = vec_grid(nlines * n);
     int rc;
     typename BlueGather<T>::Params gp{in, buf, nullptr, outer, n, inner, n, forward, grid};
-    if ((rc = rt_launch<BlueGather<T>>(grid, kVecThreads, 0, st, gp))) return rc;
+    if ((rc = blue_gather<T>(gp, st))) return rc;
     if ((rc = run_rows_c2c<T>(buf, buf, pl->blue_tw[t], logn, nlines, forward ? 0 : 1, forward ? 0 : 1, 1.0, st))) return rc;
     typename BlueScatter<T>::Params sp{buf, out, nullptr, outer, n, inner, n, forward, grid};
-    return rt_launch<BlueScatter<T>>(grid, kVecThreads, 0, st, sp);
+    return blue_scatter<T>(sp, st);
 }
 
 template <typename T>
@@ -295,13 +309,13 @@ int blue_axis(nb2_plan* pl, int t, const cplx<T>* in, cplx<T>* out, long long ou
     cplx<T>* buf = (cplx<T>*)pl->blue_buf;
     const long long gridL = vec_grid(nlines * L), gridN = vec_grid(nlines * n);
     typename BlueGather<T>::Params gp{in, buf, (const cplx<T>*)pl->blue_w[t], outer, n, inner, L, forward, gridL};
-    if ((rc = rt_launch<BlueGather<T>>(gridL, kVecThreads, 0, st, gp))) return rc;
+    if ((rc = blue_gather<T>(gp, st))) return rc;
     if ((rc = run_rows_c2c<T>(buf, buf, pl->blue_tw[t], logL, nlines, 0, 0, 1.0, st))) return rc;
     typename BlueMulConj<T>::Params mp{buf, (const cplx<T>*)pl->blue_B[t], nlines, L, forward, gridL};
     if ((rc = rt_launch<BlueMulConj<T>>(gridL, kVecThreads, 0, st, mp))) return rc;
     if ((rc = run_rows_c2c<T>(buf, buf, pl->blue_tw[t], logL, nlines, 0, 0, 1.0, st))) return rc;
     typename BlueScatter<T>::Params sp{buf, out, (const cplx<T>*)pl->blue_w[t], outer, n, inner, L, forward, gridN};
-    return rt_launch<BlueScatter<T>>(gridN, kVecThreads, 0, st, sp);
+    return blue_scatter<T>(sp, st);
 }
 
 // transform work buffer `a` over all plan axes; result pointer returned in *res (a or b)

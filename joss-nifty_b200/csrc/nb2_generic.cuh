@@ -155,6 +155,44 @@ struct BlueGather {
     }
 };
 
+// The same gather through 32 x 32 shared-memory tiles for axes with inner > 1: reads run along `i` (contiguous in
+// the source), writes along `j` (contiguous in the line buffer).  One CTA per (o, j-tile, i-tile), 256 threads.
+template <typename T>
+struct BlueGatherTiled {
+    static constexpr int NPHASES = 2;
+    static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
+    typedef typename BlueGather<T>::Params Params;
+    static size_t smem_bytes(int) { return 32 * 33 * sizeof(cplx<T>); }
+    NB2_HDC static bool enabled(int) { return true; }
+    static long long grid(const Params& p) { return p.outer * ((p.L + 31) / 32) * ((p.inner + 31) / 32); }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        cplx<T>* tile = reinterpret_cast<cplx<T>*>(smem_raw);
+        const long long ti = (p.inner + 31) / 32, tj = (p.L + 31) / 32;
+        const long long it = bid % ti, jt = (bid / ti) % tj, o = bid / (ti * tj);
+        const int tx = tid & 31;
+        for (int r = tid >> 5; r < 32; r += nthreads >> 5) {
+            if (PH == 0) {
+                const long long j = jt * 32 + r, i = it * 32 + tx;
+                cplx<T> v = mk<T>(T(0), T(0));
+                if (j < p.n && i < p.inner) {
+                    v = p.in[(o * p.n + j) * p.inner + i];
+                    if (p.w) {
+                        cplx<T> w = p.w[j];
+                        if (!p.forward) w.im = -w.im;
+                        v = v * w;
+                    }
+                }
+                tile[r * 33 + tx] = v;
+            } else {
+                const long long i = it * 32 + r, j = jt * 32 + tx;
+                if (i < p.inner && j < p.L) p.buf[(o * p.inner + i) * p.L + j] = tile[tx * 33 + r];
+            }
+        }
+    }
+};
+
 // buf[line, m] = conj(buf[line, m] * B[m])   (B of the other direction is conj(B): the filter is symmetric);
 // the conjugate turns the following FORWARD transform into the inverse one
 template <typename T>
@@ -213,6 +251,44 @@ struct BlueScatter {
             cplx<T> w = p.w[k];
             if (!p.forward) w.im = -w.im;
             p.out[e] = (w * mk<T>(y.re, -y.im)) * s;
+        }
+    }
+};
+
+// tiled twin of BlueScatter: reads along `k` (contiguous in the line buffer), writes along `i`
+template <typename T>
+struct BlueScatterTiled {
+    static constexpr int NPHASES = 2;
+    static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
+    typedef typename BlueScatter<T>::Params Params;
+    static size_t smem_bytes(int) { return 32 * 33 * sizeof(cplx<T>); }
+    NB2_HDC static bool enabled(int) { return true; }
+    static long long grid(const Params& p) { return p.outer * ((p.n + 31) / 32) * ((p.inner + 31) / 32); }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        cplx<T>* tile = reinterpret_cast<cplx<T>*>(smem_raw);
+        const long long ti = (p.inner + 31) / 32, tk = (p.n + 31) / 32;
+        const long long it = bid % ti, kt = (bid / ti) % tk, o = bid / (ti * tk);
+        const int tx = tid & 31;
+        const T s = T(1) / T(p.L);
+        for (int r = tid >> 5; r < 32; r += nthreads >> 5) {
+            if (PH == 0) {
+                const long long i = it * 32 + r, k = kt * 32 + tx;
+                if (i < p.inner && k < p.n) tile[r * 33 + tx] = p.buf[(o * p.inner + i) * p.L + k];
+            } else {
+                const long long k = kt * 32 + r, i = it * 32 + tx;
+                if (k < p.n && i < p.inner) {
+                    const cplx<T> y = tile[tx * 33 + r];
+                    cplx<T> res = y;
+                    if (p.w) {
+                        cplx<T> w = p.w[k];
+                        if (!p.forward) w.im = -w.im;
+                        res = (w * mk<T>(y.re, -y.im)) * s;
+                    }
+                    p.out[(o * p.n + k) * p.inner + i] = res;
+                }
+            }
         }
     }
 };
