@@ -251,3 +251,19 @@ def test_non_power_of_two_axes_bluestein():
     pc.check_hartley_shapes([((32, 6), None), ((4, 4, 32, 64), None), ((64, 3), (0,)), ((100, 64), None),
                              ((2, 2, 2, 2, 32), None)])
     pc.check_c2c_shapes([((64, 3), (0,)), ((4, 4, 32, 64), None), ((128, 5), None)], expect_fast=False)
+
+
+def test_generic_path_random_shapes():
+    # seeded sweep over arbitrary extents and axis subsets: direct sums, chirp-z axes, power-of-two axes of generic
+    # plans, tiled and plain gathers in any combination
+    rng = np.random.default_rng(77)
+    cases = []
+    while len(cases) < 30:
+        nd = int(rng.integers(1, 4))
+        shape = tuple(int(rng.integers(1, 70)) if rng.random() < 0.6 else int(rng.integers(70, 300)) for _ in range(nd))
+        if np.prod(shape) > 40000 or np.prod(shape) < 2:
+            continue
+        k = int(rng.integers(1, nd + 1))
+        cases.append((shape, tuple(sorted(rng.choice(nd, size=k, replace=False).tolist()))))
+    pc.check_hartley_shapes(cases)
+    pc.check_c2c_shapes(cases[:12], expect_fast=None)
