@@ -181,13 +181,21 @@ int ensure_work(nb2_plan* pl) {
     return 0;
 }
 
-// Bluestein applies from this length on (below it the direct sum is as fast and exact to the last bit) and up
-// to the longest padded line the contiguous-axis kernel takes (L = 8192, i.e. n <= 4096)
-constexpr long long kBlueMinN = 32, kBlueMaxLogL = 13;
+// The generic path treats one axis at a time: lines are gathered into a contiguous buffer, transformed with the
+// power-of-two contiguous-axis kernel and scattered back.  Axes of kBlueMinN points and more take this route (below
+// it the direct sum is as fast and exact to the last bit): power-of-two lengths up to 2^26 directly, any other
+// length up to 2^23 by the chirp-z (Bluestein) convolution with padded lines of up to 2^24 points.
+constexpr long long kBlueMinN = 32;
+constexpr int kRowMaxLog = 13, kLineMaxLog = 26, kBlueMaxLogL = 24;
 
 inline int blue_logl(long long n) {
     int l = 1;
     while ((1ll << l) < 2 * n - 1) ++l;
+    return l;
+}
+inline int ilog2ll(long long n) {
+    int l = 0;
+    while ((1ll << l) < n) ++l;
     return l;
 }
 
@@ -213,43 +221,96 @@ inline void host_fft(std::vector<std::complex<long double>>& a) {
     }
 }
 
-// chirp, filter spectrum and roots of axis t (first use); the shared line buffer grows to the largest need
 template <typename T>
-int blue_prepare(nb2_plan* pl, int t, long long n, long long nlines, rt_stream st) {
+int grow(void** buf, long long* have, long long want, rt_stream st) {
+    if (want <= *have) return 0;
+    rt_sync(st);
+    rt_free(*buf);
+    *buf = nullptr;
+    *have = 0;
+    if (rt_malloc(buf, want * sizeof(cplx<T>))) return NB2_ERR_CUDA;
+    *have = want;
+    return 0;
+}
+
+// roots of the contiguous-axis kernel for lines of 2^logl points (cached per length)
+template <typename T>
+int line_table(nb2_plan* pl, int logl, const void** tw) {
+    if (!pl->line_tw[logl] && upload_table<T>(&pl->line_tw[logl], 1ll << logl, 1ll << logl)) return NB2_ERR_CUDA;
+    *tw = pl->line_tw[logl];
+    return 0;
+}
+
+// In-place unnormalised transform (forward or backward sign) of `nlines` contiguous lines of 2^logl points.
+// Up to 8192 points: one pass of the row kernel.  Longer lines: four-step -- view the line as (n1, n2); transpose,
+// n1-point rows, transpose back with the twiddles W_n^(j2 k1), n2-point rows, transpose into natural order.
+template <typename T>
+int lines_fft(nb2_plan* pl, cplx<T>* buf, long long nlines, int logl, int forward, rt_stream st) {
+    int rc;
+    const void* tw;
+    const int cj = forward ? 0 : 1;          // backward = conj(fft(conj(.)))
+    if (logl <= kRowMaxLog) {
+        if ((rc = line_table<T>(pl, logl, &tw))) return rc;
+        return run_rows_c2c<T>(buf, buf, tw, logl, nlines, cj, cj, 1.0, st);
+    }
+    const int l1 = logl / 2, l2 = logl - l1;
+    const long long n = 1ll << logl, n1 = 1ll << l1, n2 = 1ll << l2;
+    if ((rc = grow<T>(&pl->fs_buf, &pl->fs_buf_elems, nlines * n, st))) return rc;
+    cplx<T>* tmp = (cplx<T>*)pl->fs_buf;
+    typedef LineTranspose<T> LT;
+    const size_t sm = LT::smem_bytes(256);
+    typename LT::Params a{buf, tmp, nlines, n1, n2, 0, forward};                   // (n1, n2) -> (n2, n1)
+    if ((rc = rt_launch<LT>(LT::grid(a), 256, sm, st, a))) return rc;
+    if ((rc = line_table<T>(pl, l1, &tw))) return rc;
+    if ((rc = run_rows_c2c<T>(tmp, tmp, tw, l1, nlines * n2, cj, cj, 1.0, st))) return rc;   // over j1 -> [j2][k1]
+    typename LT::Params b{tmp, buf, nlines, n2, n1, 1, forward};                   // -> [k1][j2] * W_n^(j2 k1)
+    if ((rc = rt_launch<LT>(LT::grid(b), 256, sm, st, b))) return rc;
+    if ((rc = line_table<T>(pl, l2, &tw))) return rc;
+    if ((rc = run_rows_c2c<T>(buf, buf, tw, l2, nlines * n1, cj, cj, 1.0, st))) return rc;   // over j2 -> [k1][k2]
+    typename LT::Params c{buf, tmp, nlines, n1, n2, 0, forward};                   // -> [k2][k1]: k = k1 + n1 k2
+    if ((rc = rt_launch<LT>(LT::grid(c), 256, sm, st, c))) return rc;
+    return rt_d2d(buf, tmp, nlines * n * sizeof(cplx<T>), st);
+}
+
+// chirp and filter spectrum of axis t (first use)
+template <typename T>
+int blue_prepare(nb2_plan* pl, int t, long long n, rt_stream st) {
+    if (pl->blue_w[t]) return 0;
     const int logL = blue_logl(n);
     const long long L = 1ll << logL;
-    if (!pl->blue_w[t]) {
-        const long double pi = 3.141592653589793238462643383279502884L;
-        std::vector<std::complex<long double>> w(n), bt(L, std::complex<long double>(0, 0));
-        for (long long j = 0; j < n; ++j) {
-            const long long q = (j * j) % (2 * n);          // exact phase reduction: j^2 mod 2n
-            const long double ang = -pi * (long double)q / (long double)n;
-            w[j] = std::complex<long double>(cosl(ang), sinl(ang));
+    const long double pi = 3.141592653589793238462643383279502884L;
+    std::vector<cplx<T>> hw(n);
+    std::vector<std::complex<long double>> bt;
+    const bool on_host = logL <= kRowMaxLog;       // long filters are transformed on the device
+    if (on_host) bt.assign(L, std::complex<long double>(0, 0));
+    std::vector<cplx<T>> hb(on_host ? 0 : L, mk<T>(T(0), T(0)));
+    for (long long j = 0; j < n; ++j) {
+        const long long q = (long long)(((unsigned __int128)j * (unsigned __int128)j) % (unsigned __int128)(2 * n));
+        const long double ang = -pi * (long double)q / (long double)n;   // exact phase reduction: j^2 mod 2n
+        const long double c = cosl(ang), sn = sinl(ang);
+        hw[j] = mk<T>((T)c, (T)sn);
+        if (on_host) {
+            bt[j] = std::complex<long double>(c, -sn);
+            if (j) bt[L - j] = bt[j];
+        } else {
+            hb[j] = mk<T>((T)c, (T)-sn);
+            if (j) hb[L - j] = hb[j];
         }
-        for (long long m = 0; m < n; ++m) {
-            bt[m] = std::conj(w[m]);
-            if (m) bt[L - m] = std::conj(w[m]);
-        }
+    }
+    if (rt_malloc(&pl->blue_w[t], n * sizeof(cplx<T>)) || rt_malloc(&pl->blue_B[t], L * sizeof(cplx<T>)))
+        return NB2_ERR_CUDA;
+    if (rt_h2d(pl->blue_w[t], hw.data(), n * sizeof(cplx<T>), nullptr)) return NB2_ERR_CUDA;
+    if (on_host) {
         host_fft(bt);
-        std::vector<cplx<T>> hw(n), hB(L);
-        for (long long j = 0; j < n; ++j) hw[j] = mk<T>((T)w[j].real(), (T)w[j].imag());
+        std::vector<cplx<T>> hB(L);
         for (long long m = 0; m < L; ++m) hB[m] = mk<T>((T)bt[m].real(), (T)bt[m].imag());
-        if (rt_malloc(&pl->blue_w[t], n * sizeof(cplx<T>)) || rt_malloc(&pl->blue_B[t], L * sizeof(cplx<T>)))
-            return NB2_ERR_CUDA;
-        if (rt_h2d(pl->blue_w[t], hw.data(), n * sizeof(cplx<T>), nullptr) ||
-            rt_h2d(pl->blue_B[t], hB.data(), L * sizeof(cplx<T>), nullptr))
-            return NB2_ERR_CUDA;
-        if (upload_table<T>(&pl->blue_tw[t], L, L)) return NB2_ERR_CUDA;
-        pl->blue_logL[t] = logL;
+        if (rt_h2d(pl->blue_B[t], hB.data(), L * sizeof(cplx<T>), nullptr)) return NB2_ERR_CUDA;
+    } else {
+        if (rt_h2d(pl->blue_B[t], hb.data(), L * sizeof(cplx<T>), nullptr)) return NB2_ERR_CUDA;
+        rt_sync(nullptr);
+        if (int rc = lines_fft<T>(pl, (cplx<T>*)pl->blue_B[t], 1, logL, 1, st)) return rc;
     }
-    if (nlines * L > pl->blue_buf_elems) {
-        rt_sync(st);
-        rt_free(pl->blue_buf);
-        pl->blue_buf = nullptr;
-        pl->blue_buf_elems = 0;
-        if (rt_malloc(&pl->blue_buf, nlines * L * sizeof(cplx<T>))) return NB2_ERR_CUDA;
-        pl->blue_buf_elems = nlines * L;
-    }
+    pl->blue_logL[t] = logL;
     return 0;
 }
 
@@ -267,55 +328,40 @@ int blue_scatter(const typename BlueScatter<T>::Params& sp, rt_stream st) {
     return rt_launch<BlueScatter<T>>(sp.nctas, kVecThreads, 0, st, sp);
 }
 
-// power-of-two axis of a generic plan (more than three axes, leading axes, ...): gather the lines, ONE pass of the
-// contiguous-axis kernel (backward = conj-in / conj-out), scatter back
+// one axis of a generic plan: power-of-two lengths = gather, transform the lines, scatter; other lengths = the same
+// around the chirp-z convolution (gather * chirp into zero-padded lines, transform, * filter spectrum, transform
+// back, * chirp on the scatter)
 template <typename T>
-int pow2_axis(nb2_plan* pl, int t, const cplx<T>* in, cplx<T>* out, long long outer, long long n, long long inner,
+int line_axis(nb2_plan* pl, int t, const cplx<T>* in, cplx<T>* out, long long outer, long long n, long long inner,
               int forward, rt_stream st) {
     const long long nlines = outer * inner;
-    int logn = 0;
-    while ((1ll << logn) < n) ++logn;
-    if (!pl->blue_tw[t]) {
-        if (upload_table<T>(&pl->blue_tw[t], n, n)) return NB2_ERR_CUDA;
-        pl->blue_logL[t] = logn;
-    }
-    if (nlines * n > pl->blue_buf_elems) {
-        rt_sync(st);
-        rt_free(pl->blue_buf);
-        pl->blue_buf = nullptr;
-        pl->blue_buf_elems = 0;
-        if (rt_malloc(&pl->blue_buf, nlines * n * sizeof(cplx<T>))) return NB2_ERR_CUDA;
-        pl->blue_buf_elems = nlines * n;
-    }
-    cplx<T>* buf = (cplx<T>*)pl->blue_buf;
-    const long long grid = vec_grid(nlines * n);
+    const bool pow2 = (n & (n - 1)) == 0;
     int rc;
-    typename BlueGather<T>::Params gp{in, buf, nullptr, outer, n, inner, n, forward, grid};
+    if (!pow2 && (rc = blue_prepare<T>(pl, t, n, st))) return rc;
+    const int logL = pow2 ? ilog2ll(n) : pl->blue_logL[t];
+    const long long L = 1ll << logL;
+    if ((rc = grow<T>(&pl->blue_buf, &pl->blue_buf_elems, nlines * L, st))) return rc;
+    cplx<T>* buf = (cplx<T>*)pl->blue_buf;
+    const cplx<T>* w = pow2 ? nullptr : (const cplx<T>*)pl->blue_w[t];
+    const long long gridL = vec_grid(nlines * L), gridN = vec_grid(nlines * n);
+    typename BlueGather<T>::Params gp{in, buf, w, outer, n, inner, L, forward, gridL};
     if ((rc = blue_gather<T>(gp, st))) return rc;
-    if ((rc = run_rows_c2c<T>(buf, buf, pl->blue_tw[t], logn, nlines, forward ? 0 : 1, forward ? 0 : 1, 1.0, st))) return rc;
-    typename BlueScatter<T>::Params sp{buf, out, nullptr, outer, n, inner, n, forward, grid};
+    if (pow2) {
+        if ((rc = lines_fft<T>(pl, buf, nlines, logL, forward, st))) return rc;
+    } else {
+        if ((rc = lines_fft<T>(pl, buf, nlines, logL, 1, st))) return rc;
+        typename BlueMulConj<T>::Params mp{buf, (const cplx<T>*)pl->blue_B[t], nlines, L, forward, gridL};
+        if ((rc = rt_launch<BlueMulConj<T>>(gridL, kVecThreads, 0, st, mp))) return rc;
+        if ((rc = lines_fft<T>(pl, buf, nlines, logL, 1, st))) return rc;
+    }
+    typename BlueScatter<T>::Params sp{buf, out, w, outer, n, inner, L, forward, gridN};
     return blue_scatter<T>(sp, st);
 }
 
-template <typename T>
-int blue_axis(nb2_plan* pl, int t, const cplx<T>* in, cplx<T>* out, long long outer, long long n, long long inner,
-              int forward, rt_stream st) {
-    if ((n & (n - 1)) == 0) return pow2_axis<T>(pl, t, in, out, outer, n, inner, forward, st);
-    const long long nlines = outer * inner;
-    int rc = blue_prepare<T>(pl, t, n, nlines, st);
-    if (rc) return rc;
-    const int logL = pl->blue_logL[t];
-    const long long L = 1ll << logL;
-    cplx<T>* buf = (cplx<T>*)pl->blue_buf;
-    const long long gridL = vec_grid(nlines * L), gridN = vec_grid(nlines * n);
-    typename BlueGather<T>::Params gp{in, buf, (const cplx<T>*)pl->blue_w[t], outer, n, inner, L, forward, gridL};
-    if ((rc = blue_gather<T>(gp, st))) return rc;
-    if ((rc = run_rows_c2c<T>(buf, buf, pl->blue_tw[t], logL, nlines, 0, 0, 1.0, st))) return rc;
-    typename BlueMulConj<T>::Params mp{buf, (const cplx<T>*)pl->blue_B[t], nlines, L, forward, gridL};
-    if ((rc = rt_launch<BlueMulConj<T>>(gridL, kVecThreads, 0, st, mp))) return rc;
-    if ((rc = run_rows_c2c<T>(buf, buf, pl->blue_tw[t], logL, nlines, 0, 0, 1.0, st))) return rc;
-    typename BlueScatter<T>::Params sp{buf, out, (const cplx<T>*)pl->blue_w[t], outer, n, inner, L, forward, gridN};
-    return blue_scatter<T>(sp, st);
+inline bool line_axis_takes(long long n) {
+    if (n < kBlueMinN) return false;
+    if ((n & (n - 1)) == 0) return ilog2ll(n) <= kLineMaxLog;
+    return blue_logl(n) <= kBlueMaxLogL;
 }
 
 // transform work buffer `a` over all plan axes; result pointer returned in *res (a or b)
@@ -325,12 +371,11 @@ int generic_axes(nb2_plan* pl, cplx<T>* a, cplx<T>* b, int forward, rt_stream st
         const int ax = pl->axes[t];
         {
             const long long n = pl->shape[ax];
-            const bool pow2 = (n & (n - 1)) == 0 && n <= (1ll << kBlueMaxLogL);
-            if (n >= kBlueMinN && (pow2 || blue_logl(n) <= kBlueMaxLogL) && pl->knob_bluestein) {
+            if (line_axis_takes(n) && pl->knob_bluestein) {
                 long long outer = 1, inner = 1;
                 for (int i = 0; i < ax; ++i) outer *= pl->shape[i];
                 for (int i = ax + 1; i < pl->ndim; ++i) inner *= pl->shape[i];
-                const int rc = blue_axis<T>(pl, t, a, b, outer, n, inner, forward, st);
+                const int rc = line_axis<T>(pl, t, a, b, outer, n, inner, forward, st);
                 if (rc) return rc;
                 std::swap(a, b);
                 continue;
@@ -683,9 +728,10 @@ int nb2_plan_destroy(nb2_plan* pl) {
         rt_free(pl->roots[t]);
         rt_free(pl->blue_w[t]);
         rt_free(pl->blue_B[t]);
-        rt_free(pl->blue_tw[t]);
     }
+    for (int l = 0; l < 16; ++l) rt_free(pl->line_tw[l]);
     rt_free(pl->blue_buf);
+    rt_free(pl->fs_buf);
     delete pl;
     return NB2_OK;
 }

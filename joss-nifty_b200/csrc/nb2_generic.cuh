@@ -7,6 +7,8 @@
 // roofline-graded.
 #pragma once
 
+#include <cmath>
+
 #include "nb2_common.cuh"
 
 namespace nb2 {
@@ -251,6 +253,62 @@ struct BlueScatter {
             cplx<T> w = p.w[k];
             if (!p.forward) w.im = -w.im;
             p.out[e] = (w * mk<T>(y.re, -y.im)) * s;
+        }
+    }
+};
+
+NB2_HD void sincospi_hd(double x, double* sn, double* cs) {
+#if defined(__CUDA_ARCH__)
+    sincospi(x, sn, cs);
+#else
+    *sn = std::sin(3.14159265358979323846 * x);
+    *cs = std::cos(3.14159265358979323846 * x);
+#endif
+}
+
+// Per line: (R x C) row-major matrix -> (C x R), optionally times the four-step twiddle W_n^(r c), n = R C
+// (sign by direction) -- the transpositions of the four-step transform of lines longer than the row kernel takes.
+// 32 x 32 shared-memory tiles, one CTA per (line, row-tile, column-tile), 256 threads.
+template <typename T>
+struct LineTranspose {
+    static constexpr int NPHASES = 2;
+    static constexpr int MAX_THREADS = 256;
+    static constexpr int MIN_BLOCKS = 1;
+    struct Params {
+        const cplx<T>* in;
+        cplx<T>* out;
+        long long nlines, R, C;
+        int twiddle;     // 0: plain; 1: multiply by exp(-+ 2 pi i r c / (R C))
+        int forward;
+    };
+    static size_t smem_bytes(int) { return 32 * 33 * sizeof(cplx<T>); }
+    NB2_HDC static bool enabled(int) { return true; }
+    static long long grid(const Params& p) { return p.nlines * ((p.R + 31) / 32) * ((p.C + 31) / 32); }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int nthreads, char* smem_raw) {
+        cplx<T>* tile = reinterpret_cast<cplx<T>*>(smem_raw);
+        const long long tc = (p.C + 31) / 32, tr = (p.R + 31) / 32;
+        const long long ct = bid % tc, rt = (bid / tc) % tr, line = bid / (tc * tr);
+        const long long base = line * p.R * p.C;
+        const int tx = tid & 31;
+        for (int y = tid >> 5; y < 32; y += nthreads >> 5) {
+            if (PH == 0) {
+                const long long r = rt * 32 + y, c = ct * 32 + tx;
+                if (r < p.R && c < p.C) {
+                    cplx<T> v = p.in[base + r * p.C + c];
+                    if (p.twiddle) {
+                        const long long n = p.R * p.C, q = (r * c) % n;
+                        double sn, cs;
+                        sincospi_hd(-2.0 * double(q) / double(n), &sn, &cs);
+                        if (!p.forward) sn = -sn;
+                        v = v * mk<T>(T(cs), T(sn));
+                    }
+                    tile[y * 33 + tx] = v;
+                }
+            } else {
+                const long long c = ct * 32 + y, r = rt * 32 + tx;
+                if (r < p.R && c < p.C) p.out[base + c * p.R + r] = tile[tx * 33 + y];
+            }
         }
     }
 };

@@ -43,13 +43,15 @@ struct nb2_plan {
     void* work0 = nullptr;
     void* work1 = nullptr;  // complex scratch
     // Bluestein (chirp-z) tables of the generic path, per transformed axis, built on first use: chirp w[n], filter
-    // spectrum B[L], roots of the length-L contiguous transform; one padded line buffer shared by the axes
+    // spectrum B[L]; one padded line buffer shared by the axes
     void* blue_w[nb2::kMaxDim] = {nullptr};
     void* blue_B[nb2::kMaxDim] = {nullptr};
-    void* blue_tw[nb2::kMaxDim] = {nullptr};
     int blue_logL[nb2::kMaxDim] = {0};
-    void* blue_buf = nullptr;
+    void* line_tw[16] = {nullptr};      // roots of the contiguous-axis kernel per log2(line length)
+    void* blue_buf = nullptr;           // gathered (padded) lines
     long long blue_buf_elems = 0;
+    void* fs_buf = nullptr;             // four-step scratch for lines longer than the row kernel takes
+    long long fs_buf_elems = 0;
 };
 
 

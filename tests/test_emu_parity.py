@@ -251,6 +251,9 @@ def test_non_power_of_two_axes_bluestein():
     pc.check_hartley_shapes([((32, 6), None), ((4, 4, 32, 64), None), ((64, 3), (0,)), ((100, 64), None),
                              ((2, 2, 2, 2, 32), None)])
     pc.check_c2c_shapes([((64, 3), (0,)), ((4, 4, 32, 64), None), ((128, 5), None)], expect_fast=False)
+    # lines longer than the row kernel takes (four-step), as power-of-two axes and as padded chirp-z lines
+    pc.check_hartley_shapes([((2, 32768), None), ((20000,), None), ((3, 16384, 2), (1,)), ((5000, 3), (0,))])
+    pc.check_c2c_shapes([((65536,), None), ((9000,), None)], expect_fast=None)
 
 
 def test_generic_path_random_shapes():

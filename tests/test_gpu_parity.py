@@ -355,3 +355,7 @@ def test_non_power_of_two_axes_bluestein():
     pc.check_cf_vs_oracle((96, 100), (1 / 96, 1 / 100), np.float64, None)
     pc.check_hartley_shapes([((32, 6), None), ((16, 16, 32, 64), None), ((64, 3), (0,)), ((8192, 3), (0,)), ((100, 64), None)])
     pc.check_c2c_shapes([((64, 3), (0,)), ((4, 4, 32, 64), None), ((128, 5), None)], expect_fast=False)
+    # long lines: four-step transforms of 2^15 .. 2^20 points, chirp-z lines of 2^16 .. 2^21 points
+    pc.check_hartley_shapes([((2, 32768), None), ((20000,), None), ((3, 16384, 2), (1,)), ((5000, 3), (0,)),
+                             ((1 << 20,), None), ((1000003,), None)])
+    pc.check_c2c_shapes([((65536,), None), ((9000,), None), ((300000,), None)], expect_fast=None)

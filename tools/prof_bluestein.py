@@ -13,7 +13,7 @@ def tk(fn, reps=3):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / reps
 
-for shape in ((1000, 1000), (3000, 3000), (384, 384, 384), (100, 100, 100)):
+for shape in ((1000, 1000), (3000, 3000), (384, 384, 384), (100, 100, 100), (1 << 20,), (1000003,), (1 << 24,)):
     for dt in (torch.float32, torch.float64):
         a = torch.randn(shape, dtype=dt, device="cuda")
         pl = Plan(shape, None, dt)
