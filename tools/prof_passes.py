@@ -23,7 +23,8 @@ else:
 shape = tuple(n for sh, _ in subs for n in sh)
 tdt = torch.float32 if dt == "f32" else torch.float64
 cf, tab, M, j, x0 = bench.setup_problem(nb, torch, subs, offset, lik, tdt)
-plan = cf.plans[0]
+plan = cf.plans[0] if getattr(cf, "joint", None) is None else cf.joint
+PL = plan is not cf.plans[0]    # product of two spaces on the joint plan: the row pass combines differently
 first = 3 - len(shape)          # first strided pass of the transform
 a, b = x0, torch.empty_like(x0)
 cgm = sys.modules["niftyb200.cg"]
@@ -37,13 +38,15 @@ SYM = M.tab.sym and os.environ.get("PROF_SYM", "1") != "0"   # NB2_AMP_SYMMETRIC
 fieldpro = dict(amp_mode=M.tab.amp_mode, amp=M.tab.amp, scale=M.tab.azm, amp_sym=SYM)
 cases = [] if first else [("strided0", lambda: plan.run_pass(0, a, b))]
 cases += [("strided1", lambda: plan.run_pass(1, a, b)),
-         ("rows", lambda: plan.run_pass(2, a, b)), (f"strided{first}+amp", lambda: plan.run_pass(first, a, b, pro=pro)),
-         ("rows+mul", lambda: plan.run_pass(2, a, b, epi=epi_f)), ("rows+amp+add+dot", lambda: plan.run_pass(2, a, b, epi=epi_a)),
+         ("rows", lambda: plan.run_pass(2, a, b, product_last=PL)), (f"strided{first}+amp", lambda: plan.run_pass(first, a, b, pro=pro)),
+         ("rows+mul", lambda: plan.run_pass(2, a, b, epi=epi_f, product_last=PL)),
+         ("rows+amp+add+dot", lambda: plan.run_pass(2, a, b, epi=epi_a, product_last=PL)),
          (f"strided{first}+field", lambda: plan.run_pass(first, a, b, pro=PointOp(**fieldpro))),
          (f"strided{first}+field+update", lambda: plan.run_pass(first, a, b, pro=PointOp(**fieldpro, pre_add=j, pre_scale=0.5,
                                                                                        pre_out=a))),
          ("rows+field+add+dot", lambda: plan.run_pass(2, a, b, epi=PointOp(M.tab.amp_mode, M.tab.amp, M.tab.azm * cf.dvol,
-                                                                             add=x0, dot=x0, dot_out=curv, amp_sym=SYM))),
+                                                                             add=x0, dot=x0, dot_out=curv, amp_sym=SYM),
+                                                        product_last=PL)),
          ("cg_update", lambda: loop.vec.update(0, 0.0, loop.d, loop.q, j, loop.pos, loop.r)),
          ("axpby", lambda: loop.vec.axpby(1.0, loop.r, 1.0, b))]
 if os.environ.get("PROF_NCU"):
