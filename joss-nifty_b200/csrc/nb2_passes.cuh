@@ -95,7 +95,11 @@ struct StridedPass {
     static constexpr int NPHASES = 3;
     static constexpr bool BIG = (R1 >= 32 || R3 >= 32);
     static constexpr int MAX_THREADS = (BIG && sizeof(T) == 8) ? 256 : 512;
-    static constexpr int MIN_BLOCKS = sizeof(T) == 4 ? (BIG ? NB2_MINB256_F32 : NB2_MINB512_F32)
+    // three-step plans (2048 rows and more): a tile of useful width fills the shared memory of an SM, so a second
+    // resident CTA is out of reach anyway -- compile for one (128 registers: the streamed operands of the fused
+    // prologues are then fetched in batches instead of one dependent load after the other)
+    static constexpr bool LONG = (R2 > 1);
+    static constexpr int MIN_BLOCKS = sizeof(T) == 4 ? ((BIG || LONG) ? NB2_MINB256_F32 : NB2_MINB512_F32)
                                                      : (MAX_THREADS == 256 ? NB2_MINB256_F64 : NB2_MINB512_F64);
 
     struct Params {
