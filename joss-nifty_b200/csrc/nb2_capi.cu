@@ -340,6 +340,11 @@ int line_axis(nb2_plan* pl, int t, const cplx<T>* in, cplx<T>* out, long long ou
     if (!pow2 && (rc = blue_prepare<T>(pl, t, n, st))) return rc;
     const int logL = pow2 ? ilog2ll(n) : pl->blue_logL[t];
     const long long L = 1ll << logL;
+    if (pow2 && inner == 1 && logL <= kRowMaxLog) {     // contiguous power-of-two lines: the row kernel as it is
+        const void* tw;
+        if ((rc = line_table<T>(pl, logL, &tw))) return rc;
+        return run_rows_c2c<T>(in, out, tw, logL, nlines, forward ? 0 : 1, forward ? 0 : 1, 1.0, st);
+    }
     if ((rc = grow<T>(&pl->blue_buf, &pl->blue_buf_elems, nlines * L, st))) return rc;
     cplx<T>* buf = (cplx<T>*)pl->blue_buf;
     const cplx<T>* w = pow2 ? nullptr : (const cplx<T>*)pl->blue_w[t];
