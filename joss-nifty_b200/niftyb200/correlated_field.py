@@ -231,6 +231,56 @@ class _Fluctuations:
         lib.check(rc, "nb2_amplitude_jvp")
         return damp
 
+    # ---- chain derivatives for what the kernels do not cover (Matern spectra, user prior callables): the torch
+    # ops of :meth:`amplitude` differentiated by autograd -- O(n_bins), once per nonlinear evaluation
+    def leaf_names(self):
+        return [k for k in self.domain()]
+
+    def torch_context(self, pd, azm):
+        """Context of :meth:`vjp_torch` / :meth:`jvp_torch`: this sub-space's leaves as fp64 device tensors."""
+        return dict(torch=True, leaves={k: pd[k].detach().to(torch.float64) for k in self.leaf_names()}, azm=float(azm))
+
+    def _normalised(self, leaves, azm):
+        a = self.amplitude(leaves)
+        return torch.cat((a[:1], a[1:] / azm))
+
+    def vjp_torch(self, ctx, ampbar):
+        names = list(ctx["leaves"])
+        leaves = {k: ctx["leaves"][k].clone().requires_grad_(True) for k in names}
+        azm = torch.tensor(ctx["azm"], dtype=torch.float64, device=self.grid.device, requires_grad=True)
+        an = self._normalised(leaves, azm)
+        ab = ampbar.to(device=an.device, dtype=torch.float64)
+        grads = torch.autograd.grad(an, [leaves[k] for k in names] + [azm], grad_outputs=ab, allow_unused=True)
+        out = {}
+        for k, gk in zip(names, grads[:-1]):
+            gk = torch.zeros_like(leaves[k]) if gk is None else gk
+            out[k] = gk if gk.dim() else float(gk)
+        return out, 0.0 if grads[-1] is None else float(grads[-1])
+
+    def jvp_torch(self, ctx, t, dazm):
+        names = list(ctx["leaves"])
+        prim = tuple(ctx["leaves"][k] for k in names) + (torch.tensor(ctx["azm"], dtype=torch.float64,
+                                                                       device=self.grid.device),)
+        tang = []
+        for k in names:
+            v = t.get(k)
+            if v is None:
+                tang.append(torch.zeros_like(ctx["leaves"][k]))
+            else:
+                v = v if isinstance(v, torch.Tensor) else torch.as_tensor(np.asarray(v))
+                tang.append(v.to(device=self.grid.device, dtype=torch.float64).reshape(ctx["leaves"][k].shape))
+        tang.append(torch.tensor(float(dazm), dtype=torch.float64, device=self.grid.device))
+
+        def fn(*args):
+            return self._normalised(dict(zip(names, args[:-1])), args[-1])
+        return torch.autograd.functional.jvp(fn, prim, tuple(tang))[1]
+
+    def vjp(self, ctx, ampbar):
+        return self.vjp_torch(ctx, ampbar) if ctx.get("torch") else self.vjp_kernel(ctx, ampbar)
+
+    def jvp(self, ctx, t, dazm):
+        return self.jvp_torch(ctx, t, dazm) if ctx.get("torch") else self.jvp_kernel(ctx, t, dazm)
+
     def amplitude(self, p):
         """Un-normalised amplitude per power bin (fp64 device tensor)."""
         g, pr, pf = self.grid, self.priors, self.prefix
@@ -405,7 +455,7 @@ class CorrelatedField:
                 pd = {k: self._as_dev(v) for k, v in p.items() if not k.endswith("xi")}
             a = f.amplitude(pd)
             out.append(torch.cat((a[:1], a[1:] / azm)))
-            ctxs.append(None)
+            ctxs.append(f.torch_context(pd, azm) if isinstance(azm, float) else None)
         return out, azm, ctxs
 
     def tables(self, p):
@@ -423,7 +473,7 @@ class CorrelatedField:
         transform after an O(N) combine.  ``mul``: fused multiplier on the last store (likelihood weight)."""
         tab = self.tables(p) if tab is None else tab
         if getattr(tab, "chain", None) is None or any(c is None for c in tab.chain) or not isinstance(self._azm, _ScalarPrior):
-            raise NotImplementedError("jvp_latent: non-parametric spectra with standard (mean, std) priors")
+            raise NotImplementedError("jvp_latent: the zero-mode prior must be a standard (mean, std) prior")
         zl = _host_float(p[self.prefix + "zeromode"])
         azm = self._azm.value(zl)
         tz = t.get(self.prefix + "zeromode")
@@ -431,7 +481,7 @@ class CorrelatedField:
         ratio = None
         iso = self.single and self.grids[0].isotropic and self.plans[0].is_fast
         for f, g, ctx, a in zip(self.fl, self.grids, tab.chain, tab.amps):
-            damp = f.jvp_kernel(ctx, t, dazm)
+            damp = f.jvp(ctx, t, dazm)
             r = damp / a
             r[0] = 0.0                                           # amp[0] = totvol: constant
             if iso:     # the gather through the ksq table, as for the amplitude itself: no N-sized index
@@ -461,13 +511,13 @@ class CorrelatedField:
         scalar leaves) and the cotangent of ``offset_mean`` under the key ``"offset_mean"``."""
         tab = self.tables(p) if tab is None else tab
         if getattr(tab, "chain", None) is None or any(c is None for c in tab.chain) or not isinstance(self._azm, _ScalarPrior):
-            raise NotImplementedError("vjp_latent: non-parametric spectra with standard (mean, std) priors")
+            raise NotImplementedError("vjp_latent: the zero-mode prior must be a standard (mean, std) prior")
         xi = self._as_dev(p[self.prefix + "xi"], self.dtype).contiguous()
         yb = self._as_dev(ybar, self.dtype).contiguous()
         xibar, ampbars, azmbar, offbar = self.vjp(yb, tab, xi, convention=convention)
         out = {self.prefix + "xi": xibar, "offset_mean": offbar}
         for f, ctx, ab in zip(self.fl, tab.chain, ampbars):
-            leaves, azm_chain = f.vjp_kernel(ctx, ab)
+            leaves, azm_chain = f.vjp(ctx, ab)
             out.update(leaves)
             azmbar += azm_chain
         zl = _host_float(p[self.prefix + "zeromode"])

@@ -432,6 +432,46 @@ def check_cf_latent_vjp_directional(shape, dist, kind="power", seed=5):
         assert rel(host(a), b) <= 1e-13
 
 
+MATERN_KW = dict(scale=(1.0, 0.3), cutoff=(4.0, 1.0), loglogslope=(-4.0, 0.5))
+
+
+def check_matern_latent_derivatives(shape, dist, kind="amplitude", renorm=True, seed=6):
+    """Matern spectra (re/correlated_field.py:186-213) run the O(n_bins) chain with torch ops; its VJP / JVP come
+    from autograd.  <ybar, d cf(p)[t]> == <vjp_latent(ybar), t> == <ybar, jvp_latent(t)> with the directional
+    derivative by central differences of the ORACLE model, and the full-latent metric built on them is symmetric."""
+    mk, mo = nb.CorrelatedFieldMaker("", dtype=torch.float64), ocf.CorrelatedFieldMaker("")
+    for m in (mk, mo):
+        m.set_amplitude_total_offset(0.5, (1e-1, 3e-2))
+        m.add_fluctuations_matern(shape, dist, **MATERN_KW, renormalize_amplitude=renorm, non_parametric_kind=kind)
+    cf, co = mk.finalize(), mo.finalize()
+    rng = np.random.default_rng(seed)
+    p = cf.init(seed)
+    assert rel(cf(p), co(p)) <= 1e-12
+    t = {k: rng.standard_normal(np.shape(v)) for k, v in p.items()}
+    ybar = rng.standard_normal(shape)
+    adj = cf.vjp_latent(ybar, p)
+    lhs = 0.0
+    for k in cf.domain:
+        a = adj[k]
+        a = host(a) if isinstance(a, torch.Tensor) else np.asarray(a)
+        lhs += float(np.vdot(a, t[k]))
+    eps = 1e-6
+    yp = co({k: p[k] + eps * t[k] for k in p})
+    ym = co({k: p[k] - eps * t[k] for k in p})
+    rhs = float(np.vdot(ybar, (yp - ym) / (2 * eps)))
+    assert abs(lhs - rhs) <= 2e-7 * max(abs(lhs), abs(rhs)), (shape, kind, lhs, rhs)
+    jv = host(cf.jvp_latent(t, p))
+    assert rel(jv, (yp - ym) / (2 * eps)) <= 1e-6
+    mid = float(np.vdot(ybar, jv))
+    assert abs(lhs - mid) <= 1e-10 * max(abs(lhs), abs(mid))
+    # the full-latent metric on top of the chain derivatives
+    lay = nb.LatentLayout(cf)
+    M = nb.LatentMetric(cf, p, dev(np.exp(0.3 * rng.standard_normal(shape))))
+    u, v = dev(rng.normal(size=lay.size)), dev(rng.normal(size=lay.size))
+    a, b = float(torch.dot(u, M(v))), float(torch.dot(M(u), v))
+    assert abs(a - b) <= 1e-10 * max(abs(a), abs(b))
+
+
 def check_cf_vs_oracle(shape, dist, dt=np.float64, expect_mode=None, seed=3):
     tdt = torch.float64 if dt == np.float64 else torch.float32
     cf, co = make_pair(shape, dist, tdt)

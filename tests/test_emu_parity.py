@@ -270,3 +270,9 @@ def test_generic_path_random_shapes():
         cases.append((shape, tuple(sorted(rng.choice(nd, size=k, replace=False).tolist()))))
     pc.check_hartley_shapes(cases)
     pc.check_c2c_shapes(cases[:12], expect_fast=None)
+
+
+def test_matern_latent_derivatives():
+    pc.check_matern_latent_derivatives((16, 16), (1 / 16, 1 / 16))
+    pc.check_matern_latent_derivatives((8, 8, 8), (1 / 8,) * 3, kind="power", renorm=False)
+    pc.check_matern_latent_derivatives((24,), (0.1,), kind="power")

@@ -359,3 +359,8 @@ def test_non_power_of_two_axes_bluestein():
     pc.check_hartley_shapes([((2, 32768), None), ((20000,), None), ((3, 16384, 2), (1,)), ((5000, 3), (0,)),
                              ((1 << 20,), None), ((1000003,), None)])
     pc.check_c2c_shapes([((65536,), None), ((9000,), None), ((300000,), None)], expect_fast=None)
+
+
+def test_matern_latent_derivatives():
+    pc.check_matern_latent_derivatives((64, 64), (1 / 64, 1 / 64))
+    pc.check_matern_latent_derivatives((16, 16, 16), (1 / 16,) * 3, kind="power", renorm=False)
