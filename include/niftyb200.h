@@ -305,6 +305,11 @@ int nb2_cg_decide(double* state, int* gate, int stage, void* stream);
 /* Every later launch of this library on the calling host thread checks `*gate` on the device first and
  * returns at once if it is non-zero.  NULL switches the check off.  The pointer must stay valid. */
 int nb2_set_launch_gate(const int* gate);
+/* Single-process loops: while set, a reduction of this library (calling host thread) whose result lands in
+ * state[NB2_CG_CURV] (the curvature dot of a transform epilogue) or state[NB2_CG_SUMS..+2] (nb2_cg_update_dev) runs
+ * the matching nb2_cg_decide stage in the SAME launch, so an iteration needs two launches less.  Do not use it when
+ * the sums are all-reduced between ranks before the decision.  (NULL, NULL) switches it off. */
+int nb2_set_cg_fusion(double* state, int* gate);
 /* nb2_cg_update with alpha = state[NB2_CG_ALPHA] read on the device; the sums go to state[NB2_CG_SUMS..]. */
 int nb2_cg_update_dev(int dtype, int64_t n, int mode, double* state, const void* d, const void* q, const void* b,
                       void* x, void* r, void* stream);

@@ -75,8 +75,23 @@ int pitch_of(int logn) {
     if (!d.r1) return 0;
     return d.r1 * d.r2 * d.r3 + d.r1 * d.r2 + (d.r2 > 1 ? d.r1 : 0);
 }
+// nb2_set_cg_fusion: reductions that land in the CG state of the calling thread also run the scalar step
+struct CgFusion {
+    double* state = nullptr;
+    int* gate = nullptr;
+};
+CgFusion& cg_fusion() {
+    static thread_local CgFusion f;
+    return f;
+}
 int launch_final_reduce(const double* partials, long long nparts, int nv, double* out, rt_stream st) {
-    FinalReduce::Params fp{partials, nparts, nv, out};
+    FinalReduce::Params fp{partials, nparts, nv, out, nullptr, nullptr, 0};
+    const CgFusion& f = cg_fusion();
+    if (f.state && out == f.state + NB2_CG_CURV && nv == 1) {
+        fp.cg_state = f.state, fp.cg_gate = f.gate, fp.cg_stage = 0;
+    } else if (f.state && out == f.state + NB2_CG_SUMS && nv == 3) {
+        fp.cg_state = f.state, fp.cg_gate = f.gate, fp.cg_stage = 1;
+    }
     return rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
 }
 }  // namespace nb2
@@ -437,12 +452,7 @@ int eltwise(nb2_plan* pl, const T* in, T* out, const nb2_pointop* op, rt_stream 
             last_error() = "nb2_pointop.dot set without dot_out";
             return NB2_ERR_ARG;
         }
-        FinalReduce::Params fp;
-        fp.partials = pl->partials;
-        fp.nparts = grid;
-        fp.nv = 1;
-        fp.out = op->dot_out;
-        rc = rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
+        rc = launch_final_reduce(pl->partials, grid, 1, op->dot_out, st);
     }
     return rc;
 }
@@ -1067,8 +1077,7 @@ static int cg_update_impl(int dtype, int64_t n, int mode, double alpha, const do
         return NB2_ERR_ARG;
     }
     if (rc) return rc;
-    FinalReduce::Params fp{ctx().partials, grid, 3, sums_dev};
-    return rt_launch<FinalReduce>(1, kVecThreads, FinalReduce::smem_bytes(kVecThreads), st, fp);
+    return launch_final_reduce(ctx().partials, grid, 3, sums_dev, st);
 }
 
 int nb2_cg_update(int dtype, int64_t n, int mode, double alpha, const void* d, const void* q, const void* b,
@@ -1196,6 +1205,16 @@ int nb2_los_adjoint(int dtype, int ndim, const int64_t* shape, const double* dis
 
 int nb2_set_launch_gate(const int* gate) {
     launch_gate() = gate;
+    return NB2_OK;
+}
+
+int nb2_set_cg_fusion(double* state, int* gate) {
+    if ((state == nullptr) != (gate == nullptr)) {
+        last_error() = "nb2_set_cg_fusion: state and gate must both be set or both be NULL";
+        return NB2_ERR_ARG;
+    }
+    cg_fusion().state = state;
+    cg_fusion().gate = gate;
     return NB2_OK;
 }
 

@@ -237,6 +237,64 @@ struct Dot {
 };
 
 // ---------------------------------------------------------------- final reduction of per-CTA partials (single CTA)
+// ---------------------------------------------------------------- device-resident CG: the scalar logic of one step
+// cg_single_step of the reference (src/re/conjugate_gradient.py:266-313), evaluated by one thread on the
+// scalars in `state` (layout: NB2_CG_* of include/niftyb200.h).  Comparisons involving NaN are false, as
+// with jnp.where.
+NB2_HD void cg_decide_step(double* s, int* gate, int stage) {
+    double info = s[NB2_CG_INFO];
+    if (stage == 0) {
+        const double curv = s[NB2_CG_CURV];
+        if (curv == 0.0) info = -1;                                   // :272-273
+        const double alpha = s[NB2_CG_GAMMA] / curv;                  // :274
+        if (alpha < 0.0) info = -1;                                   // :275-276
+        s[NB2_CG_ALPHA] = alpha;
+        s[NB2_CG_INFO] = info;
+        return;
+    }
+    const double i = s[NB2_CG_ITER] + 1.0;                            // :269
+    const double previous_gamma = s[NB2_CG_GAMMA], previous_energy = s[NB2_CG_ENERGY];
+    const double gamma = s[NB2_CG_SUMS], xr = s[NB2_CG_SUMS + 1], xb = s[NB2_CG_SUMS + 2];
+    const double miniter = s[NB2_CG_MINITER], maxiter = s[NB2_CG_MAXITER];
+    if (gamma >= 0.0 && gamma <= s[NB2_CG_TINY] && info != -1) info = 0;            // :292-294
+    if (s[NB2_CG_RESNORM] >= 0.0) {                                                  // :295-299 (norm_ord 2)
+        if (sqrt(gamma) < s[NB2_CG_RESNORM] && i >= miniter && info != -1) info = 0;
+    }
+    const double energy = 0.5 * (xr - xb);                                           // :303
+    const double energy_diff = previous_energy - energy;
+    if (energy_diff < -s[NB2_CG_EPS] * fabs(energy)) info = -1;                      // :305-307
+    const double absdelta = s[NB2_CG_ABSDELTA];
+    if (absdelta == absdelta) {                                                      // :308-312
+        if (energy_diff < absdelta && i >= miniter && info != -1) info = 0;
+    }
+    if (i >= maxiter && info != -1) info = i;                                        // :313
+    const double ratio = gamma / previous_gamma;
+    s[NB2_CG_BETA] = ratio > 0.0 ? ratio : (ratio != ratio ? ratio : 0.0);           // jnp.maximum(0, .) :315
+    s[NB2_CG_GAMMA] = gamma;
+    s[NB2_CG_ENERGY] = energy;
+    s[NB2_CG_ITER] = i;
+    s[NB2_CG_INFO] = info;
+    *gate = info >= -1.0 ? 1 : 0;                                                    // continue_condition :263-264
+}
+
+struct CgDecide {
+    static constexpr int NPHASES = 1;
+    static constexpr int MAX_THREADS = 32;
+    static constexpr int MIN_BLOCKS = 1;
+    struct Params {
+        double* state;
+        int* gate;
+        int stage;
+    };
+    static size_t smem_bytes(int) { return 0; }
+    NB2_HDC static bool enabled(int) { return true; }
+    template <int PH>
+    NB2_HD static void phase(const Params& p, long long bid, int tid, int, char*) {
+        if (bid != 0 || tid != 0) return;
+        cg_decide_step(p.state, p.gate, p.stage);
+    }
+};
+
 // out[v] = sum_c partials[c * nv + v], fixed order.
 struct FinalReduce {
     static constexpr int NPHASES = 3;
@@ -247,6 +305,11 @@ struct FinalReduce {
         long long nparts;
         int nv;  // <= 4
         double* out;
+        // device-resident CG: the scalar step that consumes these sums runs in the same launch (stage 0 after the
+        // curvature, stage 1 after the sums of CgUpdate); nullptr = off
+        double* cg_state;
+        int* cg_gate;
+        int cg_stage;
     };
     static size_t smem_bytes(int nthreads) { return size_t(4) * nthreads * sizeof(double); }
     NB2_HDC static bool enabled(int) { return true; }
@@ -264,72 +327,21 @@ struct FinalReduce {
             double tmp[4];
             block_reduce_B<4>(red, tid, nthreads, tmp);
 #if defined(__CUDA_ARCH__)
-            if (tid == 0)
+            if (tid == 0) {
                 for (int v = 0; v < p.nv; ++v) p.out[v] = tmp[v];
+                if (p.cg_state) cg_decide_step(p.cg_state, p.cg_gate, p.cg_stage);
+            }
 #endif
         } else {
 #if !defined(__CUDA_ARCH__)
             double tmp[4];
             block_reduce_C<4>(red, tid, nthreads, tmp);
-            if (tid == 0)
+            if (tid == 0) {
                 for (int v = 0; v < p.nv; ++v) p.out[v] = tmp[v];
+                if (p.cg_state) cg_decide_step(p.cg_state, p.cg_gate, p.cg_stage);
+            }
 #endif
         }
-    }
-};
-
-// ---------------------------------------------------------------- device-resident CG: the scalar logic of one step
-// cg_single_step of the reference (src/re/conjugate_gradient.py:266-313), evaluated by one thread on the
-// scalars in `state` (layout: NB2_CG_* of include/niftyb200.h).  Comparisons involving NaN are false, as
-// with jnp.where.
-struct CgDecide {
-    static constexpr int NPHASES = 1;
-    static constexpr int MAX_THREADS = 32;
-    static constexpr int MIN_BLOCKS = 1;
-    struct Params {
-        double* state;
-        int* gate;
-        int stage;
-    };
-    static size_t smem_bytes(int) { return 0; }
-    NB2_HDC static bool enabled(int) { return true; }
-    template <int PH>
-    NB2_HD static void phase(const Params& p, long long bid, int tid, int, char*) {
-        if (bid != 0 || tid != 0) return;
-        double* s = p.state;
-        double info = s[NB2_CG_INFO];
-        if (p.stage == 0) {
-            const double curv = s[NB2_CG_CURV];
-            if (curv == 0.0) info = -1;                                   // :272-273
-            const double alpha = s[NB2_CG_GAMMA] / curv;                  // :274
-            if (alpha < 0.0) info = -1;                                   // :275-276
-            s[NB2_CG_ALPHA] = alpha;
-            s[NB2_CG_INFO] = info;
-            return;
-        }
-        const double i = s[NB2_CG_ITER] + 1.0;                            // :269
-        const double previous_gamma = s[NB2_CG_GAMMA], previous_energy = s[NB2_CG_ENERGY];
-        const double gamma = s[NB2_CG_SUMS], xr = s[NB2_CG_SUMS + 1], xb = s[NB2_CG_SUMS + 2];
-        const double miniter = s[NB2_CG_MINITER], maxiter = s[NB2_CG_MAXITER];
-        if (gamma >= 0.0 && gamma <= s[NB2_CG_TINY] && info != -1) info = 0;            // :292-294
-        if (s[NB2_CG_RESNORM] >= 0.0) {                                                  // :295-299 (norm_ord 2)
-            if (sqrt(gamma) < s[NB2_CG_RESNORM] && i >= miniter && info != -1) info = 0;
-        }
-        const double energy = 0.5 * (xr - xb);                                           // :303
-        const double energy_diff = previous_energy - energy;
-        if (energy_diff < -s[NB2_CG_EPS] * fabs(energy)) info = -1;                      // :305-307
-        const double absdelta = s[NB2_CG_ABSDELTA];
-        if (absdelta == absdelta) {                                                      // :308-312
-            if (energy_diff < absdelta && i >= miniter && info != -1) info = 0;
-        }
-        if (i >= maxiter && info != -1) info = i;                                        // :313
-        const double ratio = gamma / previous_gamma;
-        s[NB2_CG_BETA] = ratio > 0.0 ? ratio : (ratio != ratio ? ratio : 0.0);           // jnp.maximum(0, .) :315
-        s[NB2_CG_GAMMA] = gamma;
-        s[NB2_CG_ENERGY] = energy;
-        s[NB2_CG_ITER] = i;
-        s[NB2_CG_INFO] = info;
-        *p.gate = info >= -1.0 ? 1 : 0;                                                  // continue_condition :263-264
     }
 };
 

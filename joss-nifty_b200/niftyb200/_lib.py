@@ -98,6 +98,7 @@ class Library:
         "nb2_los_adjoint": (c_int, [c_int, c_int, POINTER(c_int64), POINTER(c_double), c_int64, c_int, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
                                     c_void_p, c_void_p]),
         "nb2_cg_decide": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+        "nb2_set_cg_fusion": (c_int, [c_void_p, c_void_p]),
         "nb2_set_launch_gate": (c_int, [c_void_p]),
         "nb2_cg_update_dev": (c_int, [c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                       c_void_p]),

@@ -524,6 +524,8 @@ class _DeviceCG:
         self.alpha = self.state[_lib.CG_ALPHA:_lib.CG_ALPHA + 1]
         self.sums = self.state[_lib.CG_SUMS:_lib.CG_SUMS + 3]
         self.fused = getattr(mat, "fused_direction_update", False)
+        # single process: the scalar step runs inside the launch of the reduction that feeds it (nb2_set_cg_fusion)
+        self.fuse_decide = self.comm is None and bool(getattr(mat, "fuses_cg_decide", False))
         self.poll = max(1, int(poll))
         if use_graph is None:
             use_graph = dev.type == "cuda" and self.comm is None
@@ -550,7 +552,8 @@ class _DeviceCG:
             mat.apply_with_curvature(self.d, out=self.q, pre=pre, curv_out=self.curv)     # :270-271
         else:
             mat.apply_with_curvature(self.d, out=self.q, curv_out=self.curv)
-        self._decide(0)                                   # alpha = gamma / curv (:272-276)
+        if not self.fuse_decide:
+            self._decide(0)                               # alpha = gamma / curv (:272-276)
         if i % N_RESET == 0:                              # :277-290 exact residual
             lib.check(lib.nb2_axpby_dev(self.code, self.n, -1.0, _ptr(lib, self.alpha), _ptr(lib, self.d), 1.0, None,
                                         _ptr(lib, self.pos), _stream(self.pos)), "nb2_axpby_dev")
@@ -563,7 +566,8 @@ class _DeviceCG:
                                         _stream(self.pos)), "nb2_cg_update_dev")
         if self.comm is not None:
             self.comm.allreduce_(self.sums)
-        self._decide(1)                                   # :291-315 + continue_condition
+        if not self.fuse_decide:
+            self._decide(1)                               # :291-315 + continue_condition
 
     def _regular(self, i):
         """Iterations with the pending update and no reset are identical launches: replay a graph."""
@@ -587,10 +591,21 @@ class _DeviceCG:
             else:
                 self._iteration(self.i)
 
+    def hooks(self, on):
+        """Launch gate (and, single process, the fused scalar step) of the calling thread on / off."""
+        lib = self.lib
+        if on:
+            lib.check(lib.nb2_set_launch_gate(_ptr(lib, self.gate)), "nb2_set_launch_gate")
+            if self.fuse_decide:
+                lib.check(lib.nb2_set_cg_fusion(_ptr(lib, self.state), _ptr(lib, self.gate)), "nb2_set_cg_fusion")
+        else:
+            lib.nb2_set_launch_gate(None)
+            lib.nb2_set_cg_fusion(None, None)
+
     def run(self):
         lib = self.lib
         info = int(self.state[_lib.CG_INFO].item())
-        lib.check(lib.nb2_set_launch_gate(_ptr(lib, self.gate)), "nb2_set_launch_gate")
+        self.hooks(True)
         try:
             while info < -1 and self.i < self.maxiter:
                 self.enqueue(1)
@@ -598,7 +613,7 @@ class _DeviceCG:
                 if self.i >= min(self.miniter, self.maxiter) and (self.i % self.poll == 0 or self.i == self.maxiter):
                     info = int(self.state[_lib.CG_INFO].item())
         finally:
-            lib.nb2_set_launch_gate(None)
+            self.hooks(False)
         st = self.state.cpu().numpy()
         nit, info = int(st[_lib.CG_ITER]), int(st[_lib.CG_INFO])
         nfev = self.nfev0 + nit + nit // N_RESET
@@ -636,12 +651,11 @@ class CGLoop:
 
     def run(self, n):
         if self.dev is not None:
-            lib = self.dev.lib
-            lib.check(lib.nb2_set_launch_gate(_ptr(lib, self.dev.gate)), "nb2_set_launch_gate")
+            self.dev.hooks(True)
             try:
                 self.dev.enqueue(n)
             finally:
-                lib.nb2_set_launch_gate(None)
+                self.dev.hooks(False)
             return self
         mat, vec, j = self.mat, self.vec, self.j
         for _ in range(n):

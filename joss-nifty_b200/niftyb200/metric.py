@@ -54,6 +54,9 @@ class CFMetric:
         # apply_with_curvature(curv_out=..., pre=(r, device beta)) makes no host read-back: static_cg may keep
         # its whole loop on the device
         self.device_resident_cg = True
+        # the curvature is reduced exactly once per apply, by this library, into `curv_out`: the scalar step of the
+        # device-resident CG may ride on that launch (nb2_set_cg_fusion)
+        self.fuses_cg_decide = True
         # the CG loops hand their pending direction update d <- r + beta d to apply_with_curvature(pre=...)
         # (NIFTYB200_FUSED_AXPBY=0: keep the separate axpby kernel -- A/B measurements)
         self.fused_direction_update = (bool(getattr(cf, "fuses_direction_update", False))
@@ -123,6 +126,7 @@ class SampledCFMetric:
         self.napply = 0
         # with samples on other ranks the curvature needs the all-reduced result: computed afterwards, on the host side
         self.device_resident_cg = comm is None and self.n_local > 0
+        self.fuses_cg_decide = self.device_resident_cg
 
     def __call__(self, t, out=None):
         return self._apply(t, out, None, None)[0]
